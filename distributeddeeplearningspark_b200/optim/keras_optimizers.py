@@ -1,0 +1,157 @@
+"""Keras-2 form Adam / Adagrad / SGD over a flat parameter space, one fused launch per step.
+
+The reference names its worker optimizers by string — ``'adam'``
+(/root/reference/ddl_mnist_aztk.py:195, /root/reference/ddl_nyiso_aztk.py:255) and
+``'adagrad'`` (ddl_nyiso_aztk.py:207) — so the update rules are Keras':
+
+    Adam:    lr_t = lr*sqrt(1-b2^t)/(1-b1^t);  p -= lr_t*m/(sqrt(v)+eps),  eps = 1e-7
+    Adagrad: a += g^2;                         p -= lr*g/(sqrt(a)+eps),    lr = 0.01
+
+On CUDA the whole step is one hand-written kernel over the flat buffers
+(``ops.optimizer``), with the step counter kept in device memory so a captured
+CUDA graph replays correctly.  On CPU the same math runs as flat torch ops.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Iterable, Optional
+
+import torch
+
+from .flat import FlatSpace
+
+
+class _FlatOptimizer:
+    kind = 'base'
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], comm=None, flat: Optional[FlatSpace] = None):
+        self.flat = flat if flat is not None else FlatSpace(list(params), comm=comm)
+        self.device = self.flat.device
+        self.step_count = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self.grad_scale = 1.0  # folded into the update kernel (e.g. 1/backward_passes)
+        self._native = None
+        if self.device.type == 'cuda':
+            from ..ops import optimizer as native
+            self._native = native
+
+    # torch.optim-like surface ----------------------------------------------
+    @property
+    def param_groups(self):
+        return [{'params': self.flat.params, **self.hyper()}]
+
+    def zero_grad(self, set_to_none: bool = False) -> None:
+        self.flat.zero_grads()
+
+    def hyper(self) -> Dict[str, float]:
+        return {}
+
+    def slots(self) -> Dict[str, torch.Tensor]:
+        return {}
+
+    def step(self) -> None:
+        if not self.flat.grads_attached():
+            self.flat.gather_stray_grads()
+        self._update()
+
+    def _update(self) -> None:  # pragma: no cover - interface
+        raise NotImplementedError
+
+    # checkpoint -------------------------------------------------------------
+    def state_dict(self) -> Dict:
+        return {'kind': self.kind, 'hyper': self.hyper(), 'step': int(self.step_count.item()),
+                'slots': {k: v.detach().cpu().clone() for k, v in self.slots().items()}}
+
+    def load_state_dict(self, sd: Dict) -> None:
+        if sd['kind'] != self.kind:
+            raise ValueError(f"optimizer kind mismatch: {sd['kind']} vs {self.kind}")
+        self.step_count.fill_(int(sd['step']))
+        for k, v in self.slots().items():
+            v.copy_(sd['slots'][k].to(v.device))
+
+
+class KerasAdam(_FlatOptimizer):
+    kind = 'adam'
+
+    def __init__(self, params, lr=1e-3, beta_1=0.9, beta_2=0.999, epsilon=1e-7, comm=None, flat=None):
+        super().__init__(params, comm=comm, flat=flat)
+        self.lr, self.beta_1, self.beta_2, self.epsilon = lr, beta_1, beta_2, epsilon
+        self.m = torch.zeros_like(self.flat.flat_params)
+        self.v = torch.zeros_like(self.flat.flat_params)
+
+    def hyper(self):
+        return {'lr': self.lr, 'beta_1': self.beta_1, 'beta_2': self.beta_2, 'epsilon': self.epsilon}
+
+    def slots(self):
+        return {'m': self.m, 'v': self.v}
+
+    def _update(self):
+        f = self.flat
+        if self._native is not None:
+            self._native.adam_step(f.flat_params, f.flat_grads, self.m, self.v, self.step_count,
+                                   self.lr, self.beta_1, self.beta_2, self.epsilon, self.grad_scale)
+            return
+        self.step_count += 1
+        t = int(self.step_count.item())
+        lr_t = self.lr * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
+        g = f.flat_grads * self.grad_scale if self.grad_scale != 1.0 else f.flat_grads
+        self.m.mul_(self.beta_1).add_(g, alpha=1 - self.beta_1)
+        self.v.mul_(self.beta_2).addcmul_(g, g, value=1 - self.beta_2)
+        f.flat_params.addcdiv_(self.m, self.v.sqrt().add_(self.epsilon), value=-lr_t)
+
+
+class KerasAdagrad(_FlatOptimizer):
+    kind = 'adagrad'
+
+    def __init__(self, params, lr=0.01, epsilon=1e-7, comm=None, flat=None):
+        super().__init__(params, comm=comm, flat=flat)
+        self.lr, self.epsilon = lr, epsilon
+        self.acc = torch.zeros_like(self.flat.flat_params)
+
+    def hyper(self):
+        return {'lr': self.lr, 'epsilon': self.epsilon}
+
+    def slots(self):
+        return {'accumulator': self.acc}
+
+    def _update(self):
+        f = self.flat
+        if self._native is not None:
+            self._native.adagrad_step(f.flat_params, f.flat_grads, self.acc, self.step_count,
+                                      self.lr, self.epsilon, self.grad_scale)
+            return
+        self.step_count += 1
+        g = f.flat_grads * self.grad_scale if self.grad_scale != 1.0 else f.flat_grads
+        self.acc.addcmul_(g, g)
+        f.flat_params.addcdiv_(g, self.acc.sqrt().add_(self.epsilon), value=-self.lr)
+
+
+class KerasSGD(_FlatOptimizer):
+    kind = 'sgd'
+
+    def __init__(self, params, lr=0.01, comm=None, flat=None):
+        super().__init__(params, comm=comm, flat=flat)
+        self.lr = lr
+
+    def hyper(self):
+        return {'lr': self.lr}
+
+    def _update(self):
+        f = self.flat
+        if self._native is not None:
+            self._native.sgd_step(f.flat_params, f.flat_grads, self.step_count, self.lr, self.grad_scale)
+            return
+        self.step_count += 1
+        f.flat_params.add_(f.flat_grads, alpha=-self.lr * self.grad_scale)
+
+
+_BY_NAME = {'adam': KerasAdam, 'adagrad': KerasAdagrad, 'sgd': KerasSGD}
+
+
+def get_optimizer(name_or_opt, params, comm=None, **kw):
+    """Resolve a Keras optimizer name (``'adam'``, ``'adagrad'``, ``'sgd'``) to a flat fused optimizer."""
+    if isinstance(name_or_opt, _FlatOptimizer):
+        return name_or_opt
+    key = str(name_or_opt).lower()
+    if key not in _BY_NAME:
+        raise ValueError(f'unsupported optimizer {name_or_opt!r}; have {sorted(_BY_NAME)}')
+    return _BY_NAME[key](params, comm=comm, **kw)

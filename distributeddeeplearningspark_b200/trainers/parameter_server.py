@@ -1,0 +1,75 @@
+"""Center-variable ("parameter server") back-ends for the ADAG / DynSGD trainers.
+
+dist-keras runs a socket parameter server thread in the Spark driver: workers
+``commit`` a residual (``center += residual; num_updates += 1`` under a mutex)
+and ``pull`` the center.  There is no server process
+here; the center variable is replicated on every rank:
+
+* ``CollectiveCenter`` — each communication round is one allreduce-SUM of the
+  ranks' residuals, applied to every replica (ADAG *sums* the workers'
+  normalised deltas; it does not average them).  Rounds are lock-step, which
+  makes the result deterministic; used on CPU/gloo, on one GPU, and wherever
+  multicast is unavailable.
+* ``MulticastCenter`` (``parallel.peer``) — the center lives in NVSwitch
+  multicast memory; a commit is a ``multimem.red.add`` of the scaled residual
+  (the switch applies it to every replica) and a pull is a local read, so ranks
+  progress without waiting for each other, like the original asynchronous server.
+
+``num_updates`` counts commits over all workers, like
+``trainer.parameter_server.num_updates`` (/root/reference/ddl_mnist_aztk.py:224).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from ..parallel.comm import Communicator, Sum
+
+
+class CollectiveCenter:
+    def __init__(self, comm: Communicator, flat_params: torch.Tensor, staleness_aware: bool = False):
+        self.comm = comm
+        self.staleness_aware = staleness_aware
+        self.center = flat_params.detach().clone()
+        self._delta = comm.alloc(flat_params.numel(), torch.float32) if flat_params.is_cuda \
+            else torch.zeros_like(flat_params)
+        self.local_commits = 0
+        self.rounds = 0
+
+    def commit_pull(self, flat_params: torch.Tensor, scale: float, active: bool = True) -> None:
+        """``center += sum_r scale_r * (W_r - center_at_last_pull)`` then ``W = center`` on every rank.
+
+        ``scale`` is 1/communication_window for ADAG and 1 for DynSGD; with ``staleness_aware``
+        the residual of rank r is additionally divided by (staleness + 1) where, in a lock-step
+        round, rank r's commit is the r-th to arrive (staleness = r)."""
+        if active:
+            s = scale / (self.comm.rank + 1) if self.staleness_aware else scale
+            torch.sub(flat_params, self.center, out=self._delta)
+            if s != 1.0:
+                self._delta.mul_(s)
+            self.local_commits += 1
+        else:
+            self._delta.zero_()
+        self.comm.allreduce_(self._delta, Sum)
+        self.center.add_(self._delta)
+        flat_params.copy_(self.center)
+        self.rounds += 1
+
+    def total_updates(self) -> int:
+        t = torch.tensor([self.local_commits], dtype=torch.float64, device=self.center.device)
+        if self.comm.size > 1:
+            t = t.float()
+            self.comm.allreduce_(t, Sum)
+        return int(round(float(t.item())))
+
+
+class ParameterServerView:
+    """What ``trainer.parameter_server`` exposes after training."""
+
+    def __init__(self, num_updates: int = 0, center=None):
+        self.num_updates = num_updates
+        self.center_variable = center
+
+    def get_model(self):
+        return self.center_variable

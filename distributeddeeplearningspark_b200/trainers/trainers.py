@@ -1,0 +1,269 @@
+"""Trainer facades with the dist-keras constructor/usage shape the reference scripts use.
+
+    trainer = ADAG(keras_model=model, worker_optimizer='adam', loss='categorical_crossentropy',
+                   num_workers=8, batch_size=16, communication_window=5, num_epoch=5,
+                   features_col='matrix', label_col='label_encoded')
+    trained = trainer.train(training_set)
+    trainer.get_training_time(); trainer.parameter_server.num_updates
+
+(/root/reference/ddl_mnist_aztk.py:216-224, /root/reference/ddl_nyiso_aztk.py:207-218,255-261;
+``DynSGD`` at ddl_nyiso_aztk.py:212-215; the "SingleWorker" comparison at ddl_mnist_aztk.py:215.)
+
+``train`` fans out through ``spark.run`` — one rank per partition/GPU — and each
+rank runs the fused step engine over its partition.  ``AllreduceTrainer`` is the
+synchronous Horovod-style path (``DistributedOptimizer``) with the same facade.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import tempfile
+import time
+from typing import Dict, List, Optional, Sequence
+
+import numpy as np
+import torch
+
+from .. import runtime
+from ..data.feeder import DeviceFeeder
+from ..data.frame import DataFrame
+from ..models.sequential import Sequential, deserialize_model, serialize_model
+from ..utils.logging import get_logger
+from .engine import StepEngine
+from .parameter_server import CollectiveCenter, ParameterServerView
+
+
+# ----------------------------------------------------------------------------
+# partition staging (driver -> ranks)
+# ----------------------------------------------------------------------------
+def _feature_dtype(a: np.ndarray) -> np.dtype:
+    return np.uint8 if a.dtype == np.uint8 else np.float32
+
+
+def stage_partitions(df: DataFrame, features_col: str, label_col: str, n: int, root: Optional[str] = None) -> str:
+    """Write partition i's feature/label columns as ``.npy`` files ranks can mmap (driver side)."""
+    base = root or ('/dev/shm' if os.path.isdir('/dev/shm') else None)
+    d = tempfile.mkdtemp(prefix='ddls_parts_', dir=base)
+    for i in range(n):
+        idx = df.partition_indices(i, n)
+        x = np.asarray(df[features_col])[idx]
+        y = np.asarray(df[label_col])[idx]
+        np.save(os.path.join(d, f'x{i}.npy'), np.ascontiguousarray(x, dtype=_feature_dtype(x)))
+        np.save(os.path.join(d, f'y{i}.npy'), np.ascontiguousarray(y, dtype=np.float32))
+    return d
+
+
+def load_partition(d: str, i: int):
+    return np.load(os.path.join(d, f'x{i}.npy'), mmap_mode='r'), np.load(os.path.join(d, f'y{i}.npy'), mmap_mode='r')
+
+
+# ----------------------------------------------------------------------------
+# worker bodies (run inside each rank)
+# ----------------------------------------------------------------------------
+def _worker(spec: Dict) -> Dict:
+    runtime.init()
+    rank, size = runtime.rank(), runtime.size()
+    dev = runtime.device()
+    comm = runtime.communicator()
+    if spec.get('seed') is not None:
+        torch.manual_seed(spec['seed'] + rank)
+    model = deserialize_model(spec['model']).to(dev)
+    x, y = load_partition(spec['parts'], rank)
+    mode = spec['mode']
+    engine = StepEngine(model, optimizer=spec['worker_optimizer'], loss=spec['loss'], device=dev,
+                        comm=comm if mode == 'allreduce' else None, distributed=(mode == 'allreduce'),
+                        optimizer_kwargs=spec.get('optimizer_kwargs'))
+    flat = engine.optimizer.flat if hasattr(engine.optimizer, 'flat') else engine.optimizer.inner.flat
+    if size > 1:
+        comm.broadcast_(flat.flat_params, 0)
+    feeder = DeviceFeeder({'x': np.asarray(x), 'y': np.asarray(y)}, spec['batch_size'], dev,
+                          num_epoch=spec['num_epoch'], shuffle=spec.get('shuffle', False),
+                          seed=spec.get('seed') or 0, carry_over=True)
+    window = int(spec.get('communication_window', 1))
+    center = None
+    if mode in ('adag', 'dynsgd') :
+        center = CollectiveCenter(comm, flat.flat_params, staleness_aware=(mode == 'dynsgd'))
+    n_batches = len(feeder)
+    if mode in ('adag', 'dynsgd'):
+        my_rounds = n_batches // window
+        max_rounds = max(comm.allgather_object(my_rounds))
+    elif mode == 'allreduce':
+        # lock-step collectives: every rank must run the same number of steps
+        n_batches = min(comm.allgather_object(n_batches))
+    losses: List[torch.Tensor] = []
+    t0 = time.perf_counter()
+    it = 0
+    for batch in feeder:
+        if it >= n_batches:
+            break
+        xb = batch['x']
+        if xb.dtype != torch.float32:
+            xb = xb.float()
+        losses.append(engine.step(xb, batch['y']))
+        it += 1
+        if center is not None and it % window == 0:
+            center.commit_pull(flat.flat_params, 1.0 / window if mode == 'adag' else 1.0, active=True)
+    if center is not None:
+        for _ in range(max_rounds - my_rounds):  # keep peers' collectives matched
+            center.commit_pull(flat.flat_params, 0.0, active=False)
+        flat.flat_params.copy_(center.center)
+        num_updates = center.total_updates()
+    else:
+        num_updates = it * (size if mode == 'allreduce' else 1)
+    if dev.type == 'cuda':
+        torch.cuda.synchronize(dev)
+    elapsed = time.perf_counter() - t0
+    hist = torch.stack(losses).float().cpu().tolist() if losses else []
+    out = {'rank': rank, 'history': hist, 'num_updates': num_updates, 'elapsed': elapsed, 'steps': it}
+    if rank == 0:
+        out['weights'] = model.get_weights()
+        if spec.get('checkpoint'):
+            from ..ckpt import save_checkpoint
+            save_checkpoint(spec['checkpoint'], model, engine.optimizer)
+    return out
+
+
+# ----------------------------------------------------------------------------
+# facades
+# ----------------------------------------------------------------------------
+class Trainer:
+    """Base: holds the serialised master model and the training hyper-parameters."""
+
+    mode = 'single'
+
+    def __init__(self, keras_model: Sequential, loss: str, worker_optimizer: str = 'adam', metrics=('accuracy',),
+                 features_col: str = 'features', label_col: str = 'label', batch_size: int = 32, num_epoch: int = 1,
+                 num_workers: int = 1, backend=None, seed: Optional[int] = None, checkpoint: Optional[str] = None,
+                 optimizer_kwargs: Optional[dict] = None):
+        self.master_model = serialize_model(keras_model)
+        self.loss = loss
+        self.worker_optimizer = worker_optimizer
+        self.metrics = list(metrics)
+        self.features_column = features_col
+        self.label_column = label_col
+        self.batch_size = int(batch_size)
+        self.num_epoch = int(num_epoch)
+        self.num_workers = int(num_workers)
+        self.backend = backend
+        self.seed = seed
+        self.checkpoint = checkpoint
+        self.optimizer_kwargs = optimizer_kwargs
+        self.history: List[List[float]] = []
+        self.training_time_start = 0.0
+        self.training_time_end = 0.0
+        self.parameter_server = ParameterServerView()
+        self.worker_results: List[Dict] = []
+
+    # dist-keras surface --------------------------------------------------
+    def record_training_start(self):
+        self.training_time_start = time.time()
+
+    def record_training_end(self):
+        self.training_time_end = time.time()
+
+    def get_training_time(self) -> float:
+        return self.training_time_end - self.training_time_start
+
+    def get_history(self):
+        return self.history
+
+    def get_averaged_history(self):
+        if not self.history:
+            return []
+        n = min(len(h) for h in self.history)
+        return np.mean(np.asarray([h[:n] for h in self.history]), axis=0).tolist()
+
+    def has_history(self) -> bool:
+        return any(len(h) for h in self.history)
+
+    # ---------------------------------------------------------------- train
+    def _spec(self, parts_dir: str) -> Dict:
+        return {'mode': self.mode, 'model': self.master_model, 'parts': parts_dir, 'loss': self.loss,
+                'worker_optimizer': self.worker_optimizer, 'batch_size': self.batch_size,
+                'num_epoch': self.num_epoch, 'seed': self.seed, 'checkpoint': self.checkpoint,
+                'optimizer_kwargs': self.optimizer_kwargs}
+
+    def train(self, dataframe: DataFrame, shuffle: bool = False) -> Sequential:
+        from .. import spark
+        n = self.num_workers
+        if shuffle:
+            dataframe = dataframe.shuffle(self.seed)
+        dataframe = dataframe.repartition(n).cache()
+        parts_dir = stage_partitions(dataframe, self.features_column, self.label_column, n)
+        spec = self._spec(parts_dir)
+        spec['shuffle'] = False
+        backend = self.backend
+        if backend is None and n == 1:
+            backend = 'inprocess'
+        self.record_training_start()
+        try:
+            results = spark.run(_worker, args=(spec,), num_proc=n, backend=backend)
+        finally:
+            self.record_training_end()
+            shutil.rmtree(parts_dir, ignore_errors=True)
+        self.worker_results = results
+        self.history = [r['history'] for r in results]
+        model = deserialize_model(self.master_model)
+        model.set_weights(results[0]['weights'])
+        self.parameter_server = ParameterServerView(self._count_updates(results), model)
+        get_logger().info('%s: %d worker(s), %d updates, %.3f s', type(self).__name__, n,
+                          self.parameter_server.num_updates, self.get_training_time())
+        return model
+
+    def _count_updates(self, results) -> int:
+        return int(results[0]['num_updates'])
+
+
+class SingleTrainer(Trainer):
+    """One worker, plain sequential minibatch descent (dist-keras ``SingleTrainer``)."""
+
+    mode = 'single'
+
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), features_col='features',
+                 label_col='label', num_epoch=1, batch_size=32, **kw):
+        kw.pop('num_workers', None)
+        super().__init__(keras_model, loss, worker_optimizer, metrics, features_col, label_col, batch_size,
+                         num_epoch, num_workers=1, **kw)
+
+
+class DistributedTrainer(Trainer):
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), num_workers=2, batch_size=32,
+                 features_col='features', label_col='label', num_epoch=1, **kw):
+        super().__init__(keras_model, loss, worker_optimizer, metrics, features_col, label_col, batch_size,
+                         num_epoch, num_workers, **kw)
+
+
+class ADAG(DistributedTrainer):
+    """Accumulated-gradient normalisation: every ``communication_window`` local steps each worker
+    commits ``(W - W_pulled) / communication_window`` to the center variable and pulls it."""
+
+    mode = 'adag'
+
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), num_workers=2, batch_size=32,
+                 features_col='features', label_col='label', num_epoch=1, communication_window=12, **kw):
+        super().__init__(keras_model, worker_optimizer, loss, metrics, num_workers, batch_size, features_col,
+                         label_col, num_epoch, **kw)
+        self.communication_window = int(communication_window)
+
+    def _spec(self, parts_dir):
+        s = super()._spec(parts_dir)
+        s['communication_window'] = self.communication_window
+        return s
+
+
+class DynSGD(ADAG):
+    """Staleness-aware variant: the center scales each residual by 1/(staleness + 1)."""
+
+    mode = 'dynsgd'
+
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), num_workers=2, batch_size=32,
+                 features_col='features', label_col='label', num_epoch=1, communication_window=5, **kw):
+        super().__init__(keras_model, worker_optimizer, loss, metrics, num_workers, batch_size, features_col,
+                         label_col, num_epoch, communication_window, **kw)
+
+
+class AllreduceTrainer(DistributedTrainer):
+    """Synchronous data parallelism: ``DistributedOptimizer`` averages gradients every step
+    (the Horovod-shaped product path of BASELINE.json)."""
+
+    mode = 'allreduce'
