@@ -1,0 +1,101 @@
+import numpy as np
+import pytest
+import torch
+
+from distributeddeeplearningspark_b200.data import (DataFrame, MinMaxTransformer, OneHotTransformer,
+                                                     ReshapeTransformer, make_nyiso_windows, mnist_like_frame,
+                                                     nyiso_like_frame, split_train_test)
+from distributeddeeplearningspark_b200.models import mnist_cnn, nyiso_gru, nyiso_lstm
+from distributeddeeplearningspark_b200.spark import LocalBarrierBackend
+from distributeddeeplearningspark_b200.trainers import (ADAG, AccuracyEvaluator, AllreduceTrainer, DynSGD,
+                                                         ModelPredictor, SingleTrainer, evaluate_accuracy, get_MAPE)
+
+ENV_BACKEND = dict(timeout=600)
+
+
+def _nyiso_frames(n_hours=700):
+    df = nyiso_like_frame(n_hours, seed=1)
+    lo, hi = df.agg_min('HourAvgLoad'), df.agg_max('HourAvgLoad')
+    df = MinMaxTransformer(0, 1, df.agg_min('temperature'), df.agg_max('temperature'), 'temperature', 'NormTemp',
+                           is_vector=False).transform(df)
+    df = MinMaxTransformer(0, 1, lo, hi, 'HourAvgLoad', 'NormLoad', is_vector=False).transform(df)
+    tr, te = split_train_test(make_nyiso_windows(df), 120)
+    return tr, te, lo, hi
+
+
+def test_single_trainer_learns_and_predicts_mape(monkeypatch):
+    monkeypatch.setenv('DDLS_FORCE_CPU', '1')
+    tr, te, lo, hi = _nyiso_frames()
+    model = nyiso_gru(units=16, seed=0)
+    t = SingleTrainer(keras_model=model, worker_optimizer='adam', loss='mean_squared_error', num_epoch=6,
+                      batch_size=32, features_col='feature_matrix', label_col='labels',
+                      optimizer_kwargs={'lr': 0.01})
+    trained = t.train(tr)
+    h = t.get_history()[0]
+    assert len(h) == (tr.count() * 6) // 32
+    assert np.mean(h[-10:]) < 0.5 * np.mean(h[:10])
+    assert t.get_training_time() > 0 and t.parameter_server.num_updates == len(h)
+    pred = ModelPredictor(keras_model=trained, features_col='feature_matrix').predict(te.limit(24))
+    pred = MinMaxTransformer(n_min=lo, n_max=hi, o_min=0.0, o_max=1.0, input_col='prediction',
+                             output_col='prediction2', is_vector=True).transform(pred)
+    mape = get_MAPE(pred['labels2'].tolist(), pred['prediction2'].tolist())
+    assert 0 <= mape < 25.0
+
+
+def _update_count(rows_per_worker, epochs, batch, window):
+    return sum(((r * epochs) // batch) // window for r in rows_per_worker)
+
+
+def test_update_count_formula_reproduces_notebook_1425():
+    # 4 workers x 20 epochs x window 5 x batch 32 -> 1425 (ddl_nyiso_hdi.ipynb:608,817)
+    assert _update_count([2856, 2850, 2850, 2850], 20, 32, 5) == 1425
+
+
+@pytest.mark.parametrize('cls', [ADAG, DynSGD])
+def test_adag_two_workers_gloo_update_counter_and_center(cls):
+    tr, te, lo, hi = _nyiso_frames(560)                     # 415 training windows
+    n = tr.count()
+    model = nyiso_lstm(units=8, seed=0)
+    t = cls(keras_model=model, worker_optimizer='adam', loss='mean_squared_error', num_workers=2, batch_size=16,
+            communication_window=5, num_epoch=2, features_col='feature_matrix', label_col='labels',
+            backend=LocalBarrierBackend(**ENV_BACKEND), seed=0)
+    t.backend_env = None
+    import os
+    os.environ['DDLS_FORCE_CPU'] = '1'
+    try:
+        trained = t.train(tr)
+    finally:
+        os.environ.pop('DDLS_FORCE_CPU', None)
+    rows = [len(tr.partition_indices(i, 2)) for i in range(2)]
+    assert t.parameter_server.num_updates == _update_count(rows, 2, 16, 5)
+    assert len(t.get_history()) == 2 and all(len(h) == (r * 2) // 16 for h, r in zip(t.get_history(), rows))
+    w0 = model.get_weights()
+    w1 = trained.get_weights()
+    assert any(np.abs(a - b).max() > 1e-4 for a, b in zip(w0, w1))     # center moved
+    assert all(np.isfinite(a).all() for a in w1)
+
+
+def test_allreduce_trainer_mnist_two_ranks_and_accuracy_eval():
+    df = mnist_like_frame(640, seed=0)
+    df = OneHotTransformer(10, 'label', 'label_encoded').transform(df)
+    df = MinMaxTransformer(0.0, 1.0, 0.0, 250.0, 'features', 'features_normalized').transform(df)
+    df = ReshapeTransformer('features_normalized', 'matrix', (28, 28, 1)).transform(df)
+    import os
+    os.environ['DDLS_FORCE_CPU'] = '1'
+    try:
+        t = AllreduceTrainer(keras_model=mnist_cnn(seed=0), worker_optimizer='adam',
+                             loss='categorical_crossentropy', num_workers=2, batch_size=32, num_epoch=2,
+                             features_col='matrix', label_col='label_encoded',
+                             backend=LocalBarrierBackend(**ENV_BACKEND))
+        trained = t.train(df)
+        acc = evaluate_accuracy(trained, df.limit(200), features='matrix')
+    finally:
+        os.environ.pop('DDLS_FORCE_CPU', None)
+    assert acc > 0.5                                         # synthetic classes are separable
+    h = t.get_averaged_history()
+    assert h[-1] < h[0]
+
+
+def test_accuracy_evaluator_counts():
+    df = DataFrame({'prediction_index': np.array([1.0, 2, 3, 4]), 'label': np.array([1, 2, 0, 4])})
+    assert AccuracyEvaluator('prediction_index', 'label').evaluate(df) == 0.75
