@@ -1,0 +1,257 @@
+#!/usr/bin/env python
+"""Headline benchmark: training throughput of the reference's workloads on N B200 GPUs of one node.
+
+    python bench.py --gpus 1 --steps 200 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus 8 --steps 200 --warmup 20
+
+Default model/config = BASELINE.json config 2: the MNIST Keras-style CNN of
+/root/reference/ddl_mnist_aztk.py:180-196, synthetic 28x28 images, per-rank batch 128, Adam,
+categorical cross-entropy, synchronous data parallelism (``DistributedOptimizer``).  ``--model
+nyiso_lstm|nyiso_gru|stacked_lstm`` selects BASELINE.json configs 3/4.
+
+Prints ONE JSON line on rank 0:
+  value        whole-job images(or samples)/s, device-timed with CUDA events, max over ranks, inputs
+               already on the device and rotating through a pool larger than L2
+  e2e          the same metric through the public API including, every step, the pinned-host -> device
+               copy of that step's inputs and a device -> host read of the loss
+  gpu_launches hand-written kernels of this library launched inside the timed region
+``--impl reference`` reports why the unmodified reference cannot run here; ``--impl standin`` runs the
+PyTorch + cuDNN/cuBLAS + NCCL stand-in from ``baseline/``.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+# Published numbers (derived from ddl_nyiso_hdi.ipynb:608-609,817-818): aggregate samples/s of the
+# reference's 4-CPU-worker HDInsight runs.  The MNIST script records no number.
+PUBLISHED = {'nyiso_gru': 228000.0 / 88.475, 'nyiso_lstm': 228000.0 / 99.254, 'mnist_cnn': None, 'stacked_lstm': None}
+
+MODEL_DEFAULTS = {
+    'mnist_cnn': dict(batch=128, unit='images/s', metric='mnist_cnn_train_images_per_sec', seq=784),
+    'nyiso_lstm': dict(batch=32, unit='samples/s', metric='nyiso_lstm_train_samples_per_sec', seq=25),
+    'nyiso_gru': dict(batch=32, unit='samples/s', metric='nyiso_gru_train_samples_per_sec', seq=25),
+    'stacked_lstm': dict(batch=512, unit='samples/s', metric='stacked_lstm_h1024_train_samples_per_sec', seq=168),
+}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference', 'standin'])
+    ap.add_argument('--model', default=os.environ.get('DDLS_BENCH_MODEL', 'mnist_cnn'), choices=sorted(MODEL_DEFAULTS))
+    ap.add_argument('--batch-per-rank', type=int, default=None)
+    ap.add_argument('--no-graph', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--comm', default=None, help='peer (default on GPUs) | nccl')
+    return ap.parse_args()
+
+
+def reference_arm(args):
+    """The unmodified reference cannot be installed or run on this image (recorded in DESIGN.md):
+    /root/reference has no setup.py/pyproject.toml, and it needs pyspark + a JVM, dist-keras, Keras and
+    TensorFlow, none of which are installed or in /opt/wheelhouse."""
+    why = ("reference is three Spark/dist-keras/Keras scripts with no setup.py or pyproject.toml (pip: 'not "
+           "installable'); pyspark, a JVM, distkeras, keras and tensorflow are absent from the image and wheelhouse")
+    try:
+        sys.path.insert(0, os.path.join(ROOT, 'baseline', '_ref'))
+        import pyspark  # noqa: F401
+        import distkeras  # noqa: F401
+        why = 'pyspark/distkeras import succeeded unexpectedly; reference arm not wired'
+    except Exception:
+        pass
+    print(json.dumps({'impl': 'reference', 'unavailable': why}))
+    return 0
+
+
+def make_batches(model_name, batch, n_batches, seed, device):
+    """Synthetic data of the reference's shapes, generated once on the host (pinned)."""
+    import numpy as np
+    import torch
+    from distributeddeeplearningspark_b200.data import mnist_like_arrays, nyiso_windows_arrays
+    if model_name == 'mnist_cnn':
+        px, lab = mnist_like_arrays(batch * n_batches, seed=seed)
+        return {'pixels': torch.from_numpy(px), 'labels': torch.from_numpy(lab)}
+    seq = MODEL_DEFAULTS[model_name]['seq']
+    x, y = nyiso_windows_arrays(batch * n_batches, seq_len=seq, seed=seed)
+    return {'x': torch.from_numpy(x), 'y': torch.from_numpy(y)}
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        return reference_arm(args)
+
+    import torch
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200 import _native
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    from distributeddeeplearningspark_b200.utils import ClockSampler
+
+    if not torch.cuda.is_available():
+        print(json.dumps({'impl': args.impl, 'unavailable': 'no CUDA device visible'}))
+        return 0
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            print(json.dumps({'impl': args.impl, 'unavailable':
+                              f'--gpus {args.gpus} must be launched with torch.distributed.run (one rank per GPU)'}))
+            return 0
+    if args.comm:
+        os.environ['DDLS_COMM'] = args.comm
+    ddls.init()
+    rank, size, dev = ddls.rank(), ddls.size(), ddls.device()
+    md = MODEL_DEFAULTS[args.model]
+    B = args.batch_per_rank or md['batch']
+    K, W = args.steps, max(3, args.warmup)
+    use_graph = not args.no_graph
+
+    if args.impl == 'standin':
+        sys.path.insert(0, os.path.join(ROOT, 'baseline'))
+        import standin
+        return standin.run(args, ddls, md, B, K, W)
+
+    torch.manual_seed(1234)
+    model = getattr(ddls.models, args.model)(seed=1234).to(dev)
+    loss_name = model.loss_name
+    opt_name = model.optimizer_name
+    comm = ddls.runtime.communicator()
+    base_opt = ddls.optim.get_optimizer(opt_name, model.parameters(), comm=comm)
+    base_opt.zero_grads_in_step = True
+    ddls.broadcast_parameters(base_opt, root_rank=0)
+    dopt = ddls.DistributedOptimizer(base_opt) if size > 1 else base_opt
+    engine = StepEngine(model, optimizer=dopt, loss=loss_name, device=dev, use_cuda_graph=use_graph)
+
+    # ---- data: a device pool larger than L2 for the kernel-only number; pinned host for e2e ------------
+    is_mnist = args.model == 'mnist_cnn'
+    bytes_per_batch = B * (784 * 4 + 10 * 4) if is_mnist else B * (md['seq'] + 1) * 4
+    pool_n = max(8, min(4096, (160 << 20) // bytes_per_batch + 1))
+    host = make_batches(args.model, B, pool_n, seed=rank, device=dev)
+    from distributeddeeplearningspark_b200.ops.preprocess import mnist_preprocess
+    pool_x, pool_y = [], []
+    if is_mnist:
+        px = host['pixels'].to(dev); lab = host['labels'].to(dev)
+        x_all, y_all = mnist_preprocess(px, lab)
+        pool_x = list(x_all.split(B)); pool_y = list(y_all.split(B))
+        del px
+    else:
+        pool_x = list(host['x'].to(dev).split(B)); pool_y = list(host['y'].to(dev).split(B))
+    pool_bytes = sum(t.numel() * t.element_size() for t in pool_x + pool_y)
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if size > 1:
+            ddls.barrier()
+            torch.cuda.synchronize(dev)
+
+    # ---- launches per step (counted on one eager step; a graph replays exactly these) --------------------
+    for i in range(W):
+        engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
+    sync_all()
+    if engine.use_cuda_graph and engine._graph is None:
+        for i in range(4):
+            engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
+        sync_all()
+    c0 = _native.launch_count()
+    engine._eager_step(pool_x[0], pool_y[0])
+    per_step_launches = _native.launch_count() - c0
+    sync_all()
+
+    # ---- kernel-only: device-resident inputs, CUDA events, max over ranks ---------------------------------
+    sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=100).start() if rank == 0 else None
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sync_all()
+    ev0.record()
+    for i in range(K):
+        engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
+    ev1.record()
+    sync_all()
+    ms = ev0.elapsed_time(ev1)
+    t = torch.tensor([ms], device=dev)
+    if size > 1:
+        import torch.distributed as dist
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    last_loss = float(engine.step(pool_x[0], pool_y[0]).item())
+
+    # ---- end to end: pinned host -> H2D every step, device -> host loss read every step -------------------
+    e2e = None
+    if not args.no_e2e:
+        n_host = min(pool_n, 512)
+        if is_mnist:
+            hp = host['pixels'][:n_host * B].reshape(n_host, B, 784).pin_memory()
+            hl = host['labels'][:n_host * B].reshape(n_host, B).pin_memory()
+            d_px = torch.empty((B, 784), dtype=torch.uint8, device=dev)
+            d_lab = torch.empty((B,), dtype=torch.int64, device=dev)
+            d_x = torch.empty((B, 28, 28, 1), dtype=torch.float32, device=dev)
+            d_y = torch.empty((B, 10), dtype=torch.float32, device=dev)
+            h2d = B * 784 + B * 8
+        else:
+            hx = host['x'][:n_host * B].reshape(n_host, B, md['seq'], 1).pin_memory()
+            hy = host['y'][:n_host * B].reshape(n_host, B, 1).pin_memory()
+            d_x = torch.empty((B, md['seq'], 1), dtype=torch.float32, device=dev)
+            d_y = torch.empty((B, 1), dtype=torch.float32, device=dev)
+            h2d = B * (md['seq'] + 1) * 4
+        loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+        def e2e_step(i):
+            j = i % n_host
+            if is_mnist:
+                d_px.copy_(hp[j], non_blocking=True); d_lab.copy_(hl[j], non_blocking=True)
+                mnist_preprocess(d_px, d_lab, out_x=d_x, out_y=d_y)
+            else:
+                d_x.copy_(hx[j], non_blocking=True); d_y.copy_(hy[j], non_blocking=True)
+            loss = engine.step(d_x, d_y)
+            loss_host.copy_(loss.reshape(1), non_blocking=True)
+            torch.cuda.current_stream(dev).synchronize()
+            return float(loss_host[0])
+
+        for i in range(W):
+            e2e_step(i)
+        sync_all()
+        t0 = time.perf_counter()
+        for i in range(K):
+            e2e_step(i)
+        sync_all()
+        e2e_s = time.perf_counter() - t0
+        te = torch.tensor([e2e_s], device=dev)
+        if size > 1:
+            import torch.distributed as dist
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+        e2e_s = float(te.item())
+        e2e = {'value': B * size * K / e2e_s, 'unit': md['unit'], 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
+               'ms_per_step': 1e3 * e2e_s / K}
+
+    clocks = sampler.stop() if sampler is not None else None
+    value = B * size * K / (ms / 1e3)
+    pub = PUBLISHED.get(args.model)
+    out = {
+        'metric': md['metric'], 'value': value, 'unit': md['unit'], 'n_gpus': size, 'steps': K, 'warmup': W,
+        'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'weak',
+        'vs_baseline': (value / pub) if pub else None, 'dtype': 'bf16 tensor-core operands, fp32 accumulate/master',
+        'data': 'synthetic', 'impl': 'ours',
+        'config': {'model': args.model, 'global_batch': B * size, 'per_rank_batch': B, 'seq_len': md['seq'],
+                   'parallelism': f'dp{size}', 'optimizer': opt_name, 'loss': loss_name,
+                   'comm': type(comm).__name__, 'cuda_graph': bool(engine.use_cuda_graph and engine._graph is not None),
+                   'l2': f'inputs rotate through a {pool_bytes >> 20} MB device pool (> 126 MB L2)'
+                         if pool_bytes > (126 << 20) else f'{pool_bytes >> 20} MB input pool (smaller than L2)'},
+        'e2e': e2e, 'gpu_launches': int(per_step_launches * K), 'gpu_launches_per_step': int(per_step_launches),
+        'clocks': clocks, 'final_loss': last_loss,
+    }
+    if rank == 0:
+        print(json.dumps(out))
+    ddls.shutdown()
+    return 0
+
+
+if __name__ == '__main__':
+    sys.exit(main())

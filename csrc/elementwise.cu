@@ -1,0 +1,159 @@
+// Fused elementwise kernels: Keras-form Adam / Adagrad / SGD over the flat parameter space (K12/K13 of
+// SURVEY.md §2.5) and the MNIST MinMax + reshape + one-hot preprocessing pass (K14).
+// Update rules follow Keras 2 as named by the reference ('adam' /root/reference/ddl_mnist_aztk.py:195,
+// 'adagrad' /root/reference/ddl_nyiso_aztk.py:207); the step counter lives in device memory so a captured
+// CUDA graph replays the right bias correction.
+#include "common.cuh"
+#include "../include/ddls_b200.h"
+
+namespace ddls {
+
+constexpr int EW_THREADS = 256;
+
+static inline int ew_grid(size_t n_vec) {
+  size_t b = (n_vec + EW_THREADS - 1) / EW_THREADS;
+  const size_t cap = 148 * 8;
+  return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
+}
+
+// step[0] = completed steps, step[1] = arrival ticket.  Every block reads step[0] on entry; the last
+// block to finish publishes step[0]+1, so no block can observe the new value mid-kernel.
+DDLS_DEVINL void publish_step(int* step, int t) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(step + 1), 1u);
+    if (ticket == gridDim.x - 1) {
+      step[0] = t;
+      step[1] = 0;
+      __threadfence();
+    }
+  }
+}
+
+__global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p, float4* __restrict__ g,
+                                                          float4* __restrict__ m, float4* __restrict__ v, int* step,
+                                                          size_t n4, float lr, float b1, float b2, float eps,
+                                                          float gs, int zero_grads) {
+  const int t = *reinterpret_cast<volatile int*>(step) + 1;
+  const float lr_t = lr * sqrtf(1.0f - powf(b2, (float)t)) / (1.0f - powf(b1, (float)t));
+  const float ob1 = 1.0f - b1, ob2 = 1.0f - b2;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 gi = g[i], mi = m[i], vi = v[i], pi = p[i];
+    gi.x *= gs; gi.y *= gs; gi.z *= gs; gi.w *= gs;
+    mi.x = b1 * mi.x + ob1 * gi.x; mi.y = b1 * mi.y + ob1 * gi.y; mi.z = b1 * mi.z + ob1 * gi.z; mi.w = b1 * mi.w + ob1 * gi.w;
+    vi.x = b2 * vi.x + ob2 * gi.x * gi.x; vi.y = b2 * vi.y + ob2 * gi.y * gi.y;
+    vi.z = b2 * vi.z + ob2 * gi.z * gi.z; vi.w = b2 * vi.w + ob2 * gi.w * gi.w;
+    pi.x -= lr_t * mi.x / (sqrtf(vi.x) + eps); pi.y -= lr_t * mi.y / (sqrtf(vi.y) + eps);
+    pi.z -= lr_t * mi.z / (sqrtf(vi.z) + eps); pi.w -= lr_t * mi.w / (sqrtf(vi.w) + eps);
+    m[i] = mi; v[i] = vi; p[i] = pi;
+    if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  publish_step(step, t);
+}
+
+__global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict__ p, float4* __restrict__ g,
+                                                             float4* __restrict__ a, int* step, size_t n4, float lr,
+                                                             float eps, float gs, int zero_grads) {
+  const int t = *reinterpret_cast<volatile int*>(step) + 1;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 gi = g[i], ai = a[i], pi = p[i];
+    gi.x *= gs; gi.y *= gs; gi.z *= gs; gi.w *= gs;
+    ai.x += gi.x * gi.x; ai.y += gi.y * gi.y; ai.z += gi.z * gi.z; ai.w += gi.w * gi.w;
+    pi.x -= lr * gi.x / (sqrtf(ai.x) + eps); pi.y -= lr * gi.y / (sqrtf(ai.y) + eps);
+    pi.z -= lr * gi.z / (sqrtf(ai.z) + eps); pi.w -= lr * gi.w / (sqrtf(ai.w) + eps);
+    a[i] = ai; p[i] = pi;
+    if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  publish_step(step, t);
+}
+
+__global__ void __launch_bounds__(EW_THREADS) sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, int* step,
+                                                         size_t n4, float lr, float gs, int zero_grads) {
+  const int t = *reinterpret_cast<volatile int*>(step) + 1;
+  const float a = lr * gs;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    float4 gi = g[i], pi = p[i];
+    pi.x -= a * gi.x; pi.y -= a * gi.y; pi.z -= a * gi.z; pi.w -= a * gi.w;
+    p[i] = pi;
+    if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  publish_step(step, t);
+}
+
+__global__ void __launch_bounds__(EW_THREADS) mnist_preprocess_kernel(const uint8_t* __restrict__ pix,
+                                                                      const int64_t* __restrict__ labels,
+                                                                      float* __restrict__ x, float* __restrict__ onehot,
+                                                                      int n, int npix, int classes, float o_min,
+                                                                      float scale, float n_min) {
+  const size_t total4 = (size_t)n * npix / 4;
+  const uchar4* pix4 = reinterpret_cast<const uchar4*>(pix);
+  float4* x4 = reinterpret_cast<float4*>(x);
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total4; i += stride) {
+    uchar4 u = pix4[i];
+    x4[i] = make_float4(((float)u.x - o_min) * scale + n_min, ((float)u.y - o_min) * scale + n_min,
+                        ((float)u.z - o_min) * scale + n_min, ((float)u.w - o_min) * scale + n_min);
+  }
+  if (onehot != nullptr) {
+    const size_t tot = (size_t)n * classes;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < tot; i += stride) {
+      const int r = (int)(i / classes), c = (int)(i % classes);
+      onehot[i] = (labels[r] == c) ? 1.0f : 0.0f;
+    }
+  }
+}
+
+static int check_flat(const void* a, size_t n, const char* who) {
+  if ((reinterpret_cast<uintptr_t>(a) & 15) != 0 || (n & 3) != 0) {
+    set_last_error("%s: flat buffers must be 16-byte aligned with a length multiple of 4 (got n=%zu)", who, n);
+    return 1;
+  }
+  return 0;
+}
+
+}  // namespace ddls
+
+using namespace ddls;
+
+extern "C" int ddls_adam_step(float* params, float* grads, float* m, float* v, int* step, size_t n, float lr,
+                              float beta1, float beta2, float eps, float grad_scale, int zero_grads, void* stream) {
+  if (n == 0) return 0;
+  if (check_flat(params, n, "ddls_adam_step") || check_flat(grads, n, "ddls_adam_step")) return 1;
+  adam_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(m),
+      reinterpret_cast<float4*>(v), step, n / 4, lr, beta1, beta2, eps, grad_scale, zero_grads);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "adam_kernel launch");
+}
+
+extern "C" int ddls_adagrad_step(float* params, float* grads, float* acc, int* step, size_t n, float lr, float eps,
+                                 float grad_scale, int zero_grads, void* stream) {
+  if (n == 0) return 0;
+  if (check_flat(params, n, "ddls_adagrad_step") || check_flat(grads, n, "ddls_adagrad_step")) return 1;
+  adagrad_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(acc), step, n / 4,
+      lr, eps, grad_scale, zero_grads);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "adagrad_kernel launch");
+}
+
+extern "C" int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, float grad_scale,
+                             int zero_grads, void* stream) {
+  if (n == 0) return 0;
+  if (check_flat(params, n, "ddls_sgd_step") || check_flat(grads, n, "ddls_sgd_step")) return 1;
+  sgd_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), step, n / 4, lr, grad_scale, zero_grads);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "sgd_kernel launch");
+}
+
+extern "C" int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* labels, float* x, float* onehot, int n,
+                                     int npix, int classes, float o_min, float scale, float n_min, void* stream) {
+  if (n <= 0) return 0;
+  if (((size_t)n * npix) % 4 != 0) { set_last_error("ddls_mnist_preprocess: n*npix must be a multiple of 4"); return 1; }
+  mnist_preprocess_kernel<<<ew_grid((size_t)n * npix / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      pixels, labels, x, onehot, n, npix, classes, o_min, scale, n_min);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "mnist_preprocess_kernel launch");
+}

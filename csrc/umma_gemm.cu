@@ -1,0 +1,242 @@
+// General bf16 GEMM on the 5th-gen tensor cores (tcgen05.mma, accumulators in TMEM).
+//
+//   C[M,N] (+)= A · Bᵀ-style product with selectable operand majors:
+//     A_MN = false: A is [M,K] row-major (K contiguous)      A_MN = true: A is [K,M] row-major (M contiguous)
+//     B_MN = false: B is [N,K] row-major (K contiguous)      B_MN = true: B is [K,N] row-major (N contiguous)
+//
+// Operands are staged global -> shared by the CTA's threads straight into the UMMA SWIZZLE_NONE
+// canonical layouts (no swizzle ⇒ a 16-byte vector per thread lands conflict-free), double buffered
+// against the asynchronous MMAs with mbarriers; one elected thread issues tcgen05.mma; the
+// epilogue reads TMEM with tcgen05.ld and fuses bias / ReLU / bf16 cast / split-K reduction.
+//
+// Used for: Dense layers of arbitrary size, the stacked-LSTM input projection, weight-gradient GEMMs
+// (MN-major operands), and as the validation vehicle for the descriptor encodings every other
+// tcgen05 kernel in this library relies on.  The reference has no GEMM of its own (Keras→TF Eigen on
+// CPU).
+#include "common.cuh"
+#include "../include/ddls_b200.h"
+
+namespace ddls {
+
+constexpr int GEMM_BM = 128;
+constexpr int GEMM_KC = 64;       // K elements per pipeline stage
+constexpr int GEMM_THREADS = 128;
+
+struct GemmParams {
+  const __nv_bfloat16* A;
+  const __nv_bfloat16* B;
+  void* C;
+  const float* bias;
+  int M, N, K;
+  int lda, ldb, ldc;
+  int k_per_split;
+  uint32_t flags;     // DDLS_GEMM_* bits
+  uint32_t debug;     // bit0: swap LBO/SBO in A desc, bit1: same for B (descriptor validation only)
+};
+
+// Stage a [rows x GEMM_KC] K-major tile: smem layout [KC/8][rows][8].
+template <int ROWS>
+DDLS_DEVINL void stage_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int row0, int nrows, int k0, int kend,
+                              bool vec_ok) {
+  // warp-level mapping: lane = (kc_local = lane/8, r_local = lane%8) ⇒ 8 rows x 64 B per warp access
+  constexpr int KCH = GEMM_KC / 8;
+  for (int idx = threadIdx.x; idx < ROWS * KCH; idx += GEMM_THREADS) {
+    int blk = idx >> 5, lane = idx & 31;
+    int rblk = blk % (ROWS / 8), kblk = blk / (ROWS / 8);
+    int r = rblk * 8 + (lane & 7);
+    int kc = kblk * 4 + (lane >> 3);
+    int gr = row0 + r, gk = k0 + kc * 8;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (gr < nrows && gk < kend) {
+      const __nv_bfloat16* src = g + (size_t)gr * ld + gk;
+      if (vec_ok && gk + 8 <= kend) {
+        v = *reinterpret_cast<const uint4*>(src);
+      } else {
+        __nv_bfloat16 t[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) t[e] = (gk + e < kend) ? src[e] : __float2bfloat16(0.f);
+        v = *reinterpret_cast<uint4*>(t);
+      }
+    }
+    *reinterpret_cast<uint4*>(smem + kc * (ROWS * 16) + r * 16) = v;
+  }
+}
+
+// Stage a [GEMM_KC x COLS] tile given MN-contiguous global data: smem layout [KC/8][COLS/8][8 k][8 mn].
+template <int COLS>
+DDLS_DEVINL void stage_mnmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int col0, int ncols, int k0, int kend,
+                               bool vec_ok) {
+  // lane = (k_local = lane%8, mng_local = lane/8): quarter-warps write 128 contiguous bytes
+  constexpr int MNG = COLS / 8;
+  for (int idx = threadIdx.x; idx < GEMM_KC * MNG; idx += GEMM_THREADS) {
+    int blk = idx >> 5, lane = idx & 31;
+    int gblk = blk % (MNG / 4), kblk = blk / (MNG / 4);
+    int mng = gblk * 4 + (lane >> 3);
+    int k = kblk * 8 + (lane & 7);
+    int gk = k0 + k, gc = col0 + mng * 8;
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (gk < kend && gc < ncols) {
+      const __nv_bfloat16* src = g + (size_t)gk * ld + gc;
+      if (vec_ok && gc + 8 <= ncols) {
+        v = *reinterpret_cast<const uint4*>(src);
+      } else {
+        __nv_bfloat16 t[8];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) t[e] = (gc + e < ncols) ? src[e] : __float2bfloat16(0.f);
+        v = *reinterpret_cast<uint4*>(t);
+      }
+    }
+    *reinterpret_cast<uint4*>(smem + (k >> 3) * (COLS * 16) + mng * 128 + (k & 7) * 16) = v;
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int A_BYTES = GEMM_BM * GEMM_KC * 2;
+  constexpr int B_BYTES = BN * GEMM_KC * 2;
+  uint8_t* sA[2] = {smem, smem + A_BYTES};
+  uint8_t* sB[2] = {smem + 2 * A_BYTES, smem + 2 * A_BYTES + B_BYTES};
+  __shared__ uint64_t mma_done[2];
+  __shared__ uint32_t tmem_base_s;
+  constexpr uint32_t TM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * GEMM_BM, n0 = blockIdx.y * BN;
+  const int kbeg = blockIdx.z * p.k_per_split;
+  const int kend = min(p.K, kbeg + p.k_per_split);
+
+  if (warp == 0) tmem_alloc(&tmem_base_s, TM_COLS);
+  if (threadIdx.x == 32) {
+    mbar_init(&mma_done[0], 1);
+    mbar_init(&mma_done[1], 1);
+    mbar_fence_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+
+  const bool a_vec = ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) && (p.lda % 8 == 0);
+  const bool b_vec = ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0) && (p.ldb % 8 == 0);
+  constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
+
+  const int nkb = (kend - kbeg + GEMM_KC - 1) / GEMM_KC;
+  uint32_t waits[2] = {0, 0};  // completed-phase counters per stage (parity = count & 1)
+  for (int kb = 0; kb < nkb; ++kb) {
+    const int s = kb & 1;
+    if (kb >= 2) {  // the MMAs that read this stage two iterations ago must have drained
+      mbar_wait(&mma_done[s], waits[s] & 1);
+      ++waits[s];
+    }
+    const int k0 = kbeg + kb * GEMM_KC;
+    if (A_MN) stage_mnmajor<GEMM_BM>(sA[s], p.A, p.lda, m0, p.M, k0, kend, a_vec);
+    else      stage_kmajor<GEMM_BM>(sA[s], p.A, p.lda, m0, p.M, k0, kend, a_vec);
+    if (B_MN) stage_mnmajor<BN>(sB[s], p.B, p.ldb, n0, p.N, k0, kend, b_vec);
+    else      stage_kmajor<BN>(sB[s], p.B, p.ldb, n0, p.N, k0, kend, b_vec);
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      tc_fence_after();
+      const uint32_t a_base = smem_u32(sA[s]), b_base = smem_u32(sB[s]);
+      // both staged layouts: K-group stride (LBO) = extent*16 B, 8-row / 8-element group stride (SBO) = 128 B
+      uint32_t a_lbo = GEMM_BM * 16u, a_sbo = 128u;
+      uint32_t b_lbo = BN * 16u, b_sbo = 128u;
+      if (p.debug & 1u) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; }
+      if (p.debug & 2u) { uint32_t t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
+#pragma unroll
+      for (int ks = 0; ks < GEMM_KC / 16; ++ks) {
+        // one UMMA consumes K=16 = two 8-wide K groups; both layouts advance by 2 K-groups per step
+        const uint32_t a_adv = ks * 2 * (GEMM_BM * 16u);
+        const uint32_t b_adv = ks * 2 * (BN * 16u);
+        umma_bf16(tmem_d, umma_desc(a_base + a_adv, a_lbo, a_sbo), umma_desc(b_base + b_adv, b_lbo, b_sbo), idesc,
+                  (kb | ks) != 0);
+      }
+      umma_commit(&mma_done[s]);
+    }
+  }
+  // drain every outstanding commit (stage s received ceil((nkb - s) / 2) commits)
+  for (int s = 0; s < 2; ++s) {
+    const uint32_t commits = (nkb + 1 - s) / 2;
+    while (waits[s] < commits) {
+      mbar_wait(&mma_done[s], waits[s] & 1);
+      ++waits[s];
+    }
+  }
+  tc_fence_after();
+
+  // ---- epilogue: thread (warp w, lane l) owns output row m0 + 32*w + l ---------------------
+  const int row = m0 + warp * 32 + lane;
+  const uint32_t t_row = tmem_d + (static_cast<uint32_t>(warp * 32) << 16);
+  const bool relu = p.flags & DDLS_GEMM_RELU, has_bias = (p.flags & DDLS_GEMM_BIAS) && blockIdx.z == 0;
+  const bool out_bf16 = p.flags & DDLS_GEMM_OUT_BF16, atomic = p.flags & DDLS_GEMM_ATOMIC_ADD;
+#pragma unroll 1
+  for (int c0 = 0; c0 < BN; c0 += 16) {
+    uint32_t v[16];
+    tmem_ld16(t_row + c0, v);
+    tmem_ld_wait();
+    if (row < p.M) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        const int col = n0 + c0 + j;
+        if (col < p.N) {
+          float x = __uint_as_float(v[j]);
+          if (has_bias) x += p.bias[col];
+          if (relu) x = fmaxf(x, 0.f);
+          const size_t o = (size_t)row * p.ldc + col;
+          if (atomic) atomicAdd(reinterpret_cast<float*>(p.C) + o, x);
+          else if (out_bf16) reinterpret_cast<__nv_bfloat16*>(p.C)[o] = __float2bfloat16(x);
+          else reinterpret_cast<float*>(p.C)[o] = x;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_d, TM_COLS);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const GemmParams& p, int splits, cudaStream_t st) {
+  auto kern = umma_gemm_kernel<BN, A_MN, B_MN>;
+  const int smem = 2 * (GEMM_BM * GEMM_KC * 2) + 2 * (BN * GEMM_KC * 2);
+  DDLS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  dim3 grid((p.M + GEMM_BM - 1) / GEMM_BM, (p.N + BN - 1) / BN, splits);
+  kern<<<grid, GEMM_THREADS, smem, st>>>(p);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "umma_gemm launch");
+}
+
+template <bool A_MN, bool B_MN>
+static int dispatch_bn(const GemmParams& p, int splits, cudaStream_t st) {
+  if (p.N <= 32) return launch_gemm<32, A_MN, B_MN>(p, splits, st);
+  if (p.N <= 64) return launch_gemm<64, A_MN, B_MN>(p, splits, st);
+  if (p.N <= 128 || (p.N % 256 != 0 && p.N % 128 == 0)) return launch_gemm<128, A_MN, B_MN>(p, splits, st);
+  return launch_gemm<256, A_MN, B_MN>(p, splits, st);
+}
+
+}  // namespace ddls
+
+extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda,
+                              int ldb, int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags,
+                              unsigned debug, void* stream) {
+  using namespace ddls;
+  if (M <= 0 || N <= 0 || K <= 0) { set_last_error("ddls_gemm_bf16: empty problem"); return 1; }
+  GemmParams p;
+  p.A = static_cast<const __nv_bfloat16*>(A); p.B = static_cast<const __nv_bfloat16*>(B); p.C = C; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.flags = flags; p.debug = debug;
+  int splits = split_k < 1 ? 1 : split_k;
+  int kps = (K + splits - 1) / splits;
+  kps = (kps + GEMM_KC - 1) / GEMM_KC * GEMM_KC;
+  splits = (K + kps - 1) / kps;
+  p.k_per_split = kps;
+  if (splits > 1) {
+    if (flags & (DDLS_GEMM_OUT_BF16 | DDLS_GEMM_RELU)) {
+      set_last_error("ddls_gemm_bf16: split-K needs fp32 accumulate output without ReLU"); return 1;
+    }
+    p.flags |= DDLS_GEMM_ATOMIC_ADD;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (a_mn_major) return b_mn_major ? dispatch_bn<true, true>(p, splits, st) : dispatch_bn<true, false>(p, splits, st);
+  return b_mn_major ? dispatch_bn<false, true>(p, splits, st) : dispatch_bn<false, false>(p, splits, st);
+}

@@ -27,8 +27,10 @@ class _FlatOptimizer:
     def __init__(self, params: Iterable[torch.nn.Parameter], comm=None, flat: Optional[FlatSpace] = None):
         self.flat = flat if flat is not None else FlatSpace(list(params), comm=comm)
         self.device = self.flat.device
-        self.step_count = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._step_buf = torch.zeros(2, dtype=torch.int32, device=self.device)  # [steps, kernel ticket]
+        self.step_count = self._step_buf[:1]
         self.grad_scale = 1.0  # folded into the update kernel (e.g. 1/backward_passes)
+        self.zero_grads_in_step = False  # fused kernels can clear gradients after consuming them
         self._native = None
         if self.device.type == 'cuda':
             from ..ops import optimizer as native
@@ -88,7 +90,8 @@ class KerasAdam(_FlatOptimizer):
         f = self.flat
         if self._native is not None:
             self._native.adam_step(f.flat_params, f.flat_grads, self.m, self.v, self.step_count,
-                                   self.lr, self.beta_1, self.beta_2, self.epsilon, self.grad_scale)
+                                   self.lr, self.beta_1, self.beta_2, self.epsilon, self.grad_scale,
+                                   self.zero_grads_in_step)
             return
         self.step_count += 1
         t = int(self.step_count.item())
@@ -117,7 +120,7 @@ class KerasAdagrad(_FlatOptimizer):
         f = self.flat
         if self._native is not None:
             self._native.adagrad_step(f.flat_params, f.flat_grads, self.acc, self.step_count,
-                                      self.lr, self.epsilon, self.grad_scale)
+                                      self.lr, self.epsilon, self.grad_scale, self.zero_grads_in_step)
             return
         self.step_count += 1
         g = f.flat_grads * self.grad_scale if self.grad_scale != 1.0 else f.flat_grads
@@ -138,7 +141,8 @@ class KerasSGD(_FlatOptimizer):
     def _update(self):
         f = self.flat
         if self._native is not None:
-            self._native.sgd_step(f.flat_params, f.flat_grads, self.step_count, self.lr, self.grad_scale)
+            self._native.sgd_step(f.flat_params, f.flat_grads, self.step_count, self.lr, self.grad_scale,
+                                  self.zero_grads_in_step)
             return
         self.step_count += 1
         f.flat_params.add_(f.flat_grads, alpha=-self.lr * self.grad_scale)

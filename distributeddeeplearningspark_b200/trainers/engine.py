@@ -75,6 +75,9 @@ class StepEngine:
         self._static_loss: Optional[torch.Tensor] = None
         self._warm = 0
         self.steps = 0
+        inner = getattr(self.optimizer, 'inner', self.optimizer)
+        # the fused optimizer kernels can clear the gradient buffer after consuming it
+        self._skip_zero = self.cuda and bool(getattr(inner, 'zero_grads_in_step', False))
 
     # -- one eager step ------------------------------------------------------
     def _loss(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
@@ -86,7 +89,8 @@ class StepEngine:
         return self.loss_fn(self.model(x), y)
 
     def _eager_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        self.optimizer.zero_grad()
+        if not self._skip_zero:
+            self.optimizer.zero_grad()
         loss = self._loss(x, y)
         loss.backward()
         self.optimizer.step()

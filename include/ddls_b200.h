@@ -1,0 +1,55 @@
+/* C ABI of libddls_b200.so — hand-written sm_100a kernels and the peer-memory runtime.
+ *
+ * Every function returns 0 on success and a non-zero code on failure; ddls_last_error() then
+ * returns a thread-local message.  Pointers are raw device pointers unless noted; `stream` is a
+ * cudaStream_t passed as void* (NULL = legacy default stream).  Citations name the place in the
+ * reference whose behaviour the kernel reproduces.
+ */
+#ifndef DDLS_B200_H_
+#define DDLS_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* ddls_last_error(void);
+int ddls_version(void);
+/* Number of kernels this library has launched in this process (bench.py reports it). */
+unsigned long long ddls_launch_count(void);
+
+/* ---- generic tcgen05 GEMM ------------------------------------------------------------------ */
+#define DDLS_GEMM_RELU 1u
+#define DDLS_GEMM_BIAS 2u
+#define DDLS_GEMM_OUT_BF16 4u
+#define DDLS_GEMM_ATOMIC_ADD 8u
+/* C[M,N] = op(A)·op(B)ᵀ (+bias, ReLU, cast).  a_mn_major=0: A is [M,K] row-major; 1: A is [K,M]
+ * row-major.  Same for B over N.  split_k>1 accumulates fp32 partials with red.add into a
+ * caller-zeroed C.  (Keras Dense / matmul, /root/reference/ddl_mnist_aztk.py:189-191.) */
+int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
+                   int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags, unsigned debug,
+                   void* stream);
+
+/* ---- fused optimizers over a flat fp32 parameter space --------------------------------------
+ * Keras-2 update rules named by the reference ('adam' ddl_mnist_aztk.py:195, ddl_nyiso_aztk.py:255;
+ * 'adagrad' ddl_nyiso_aztk.py:207).  `step` is a device int32 counter the kernel increments, so a
+ * captured CUDA graph replays correctly.  grad_scale multiplies the gradient first (1/N, 1/passes).
+ * If zero_grads != 0 the gradient buffer is cleared after use (saves a memset launch). */
+int ddls_adam_step(float* params, float* grads, float* m, float* v, int* step, size_t n, float lr, float beta1,
+                   float beta2, float eps, float grad_scale, int zero_grads, void* stream);
+int ddls_adagrad_step(float* params, float* grads, float* acc, int* step, size_t n, float lr, float eps,
+                      float grad_scale, int zero_grads, void* stream);
+int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, float grad_scale, int zero_grads,
+                  void* stream);
+
+/* ---- on-device preprocessing (MinMax + reshape + one-hot, ddl_mnist_aztk.py:126-144) ---------- */
+/* pixels uint8 [n,784] -> x fp32 [n,28,28,1] = (p - o_min)*scale + n_min ; labels int64 [n] -> onehot fp32 [n,classes] */
+int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* labels, float* x, float* onehot, int n, int npix,
+                          int classes, float o_min, float scale, float n_min, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DDLS_B200_H_ */
