@@ -92,7 +92,12 @@ class StepEngine:
         if not self._skip_zero:
             self.optimizer.zero_grad()
         loss = self._loss(x, y)
-        loss.backward()
+        if self.cuda:
+            from ..ops.heads import unit_seed
+            with unit_seed():
+                loss.backward()
+        else:
+            loss.backward()
         self.optimizer.step()
         return loss.detach()
 

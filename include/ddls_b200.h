@@ -49,6 +49,39 @@ int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, fl
 int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* labels, float* x, float* onehot, int n, int npix,
                           int classes, float o_min, float scale, float n_min, void* stream);
 
+/* ---- persistent LSTM(128) recurrence, tcgen05 (Keras LSTM, /root/reference/ddl_nyiso_aztk.py:249-251) ---
+ * x [B,T] fp32 (input dim 1), w_ih [4H], w_hh [H,4H], bias [4H] in Keras layout, gate order i,f,c,o.
+ * out [B,H] (last step) or [B,T,H].  When save_for_backward: hs [T,B,H] bf16, gates [T,B,H,4] bf16
+ * (post-activation), cs [T,B,H] fp32.  tile = batch rows per CTA (0 = auto; 32/64/128). */
+int ddls_lstm128_forward(const float* x, const float* w_ih, const float* w_hh, const float* bias, float* out,
+                         void* hs, void* gates, float* cs, int B, int T, int return_sequences,
+                         int save_for_backward, int tile, void* stream);
+/* BPTT.  dout [B,H] or [B,T,H].  Writes dz [T,B,4H] bf16 (gate pre-activation gradients, for the
+ * recurrent weight-gradient GEMM) and ACCUMULATES d_wih [4H], d_bias [4H] (caller zeroes them). */
+int ddls_lstm128_backward(const float* dout, const float* x, const float* w_hh, const void* gates, const float* cs,
+                          void* dz, float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile,
+                          void* stream);
+
+/* ---- persistent GRU(128) recurrence, tcgen05 (Keras GRU reset_after=False, ddl_nyiso_aztk.py:201-203) ----
+ * Gate order z,r,h.  When save_for_backward: hs [T,B,H] bf16 (h_t), rh [T,B,H] bf16 (r_t*h_{t-1}),
+ * gates [T,B,H] float4 (z, r, hh, h_{t-1}). */
+int ddls_gru128_forward(const float* x, const float* w_ih, const float* w_hh, const float* bias, float* out, void* hs,
+                        void* rh, void* gates, int B, int T, int return_sequences, int save_for_backward, int tile,
+                        void* stream);
+/* BPTT.  Writes da [T,B,3H] bf16 = d(az), d(ar), d(ah); ACCUMULATES d_wih [3H], d_bias [3H]. */
+int ddls_gru128_backward(const float* dout, const float* x, const float* w_hh, const void* gates, void* da,
+                         float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile, void* stream);
+
+/* ---- fused output heads (forward + backward in one launch) -------------------------------------- */
+/* Dense(H->O, linear) + Keras mean_squared_error (ddl_nyiso_aztk.py:203,207).  y == NULL: pred only.
+ * Caller zeroes loss[1], dwd [H,O], dbd [O]; the kernel accumulates into them. */
+int ddls_dense_mse(const float* h, const float* wd, const float* bd, const float* y, float* pred, float* loss,
+                   float* dh, float* dwd, float* dbd, int B, int H, int O, void* stream);
+/* Dense(F->C) + softmax + categorical_crossentropy (ddl_mnist_aztk.py:191-196).  onehot == NULL:
+ * probabilities only.  Caller zeroes loss[1], dw [F,C], db [C]. */
+int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, const float* onehot, float* probs,
+                            float* loss, float* da, float* dw, float* db, int B, int F, int C, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
