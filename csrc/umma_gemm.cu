@@ -23,21 +23,44 @@ constexpr int GEMM_KC = 64;       // K elements per pipeline stage
 constexpr int GEMM_THREADS = 128;
 
 struct GemmParams {
-  const __nv_bfloat16* A;
-  const __nv_bfloat16* B;
+  const void* A;      // bf16, or fp32 when DDLS_GEMM_A_F32 (converted while staging)
+  const void* B;      // bf16, or fp32 when DDLS_GEMM_B_F32
   void* C;
   const float* bias;
   int M, N, K;
   int lda, ldb, ldc;
   int k_per_split;
   uint32_t flags;     // DDLS_GEMM_* bits
-  uint32_t debug;     // bit0: swap LBO/SBO in A desc, bit1: same for B (descriptor validation only)
+  float* workspace;   // split-K partials [splits][M][N] fp32 (DDLS_GEMM_SPLITK_WS)
 };
+
+// 8 consecutive elements starting at `src` (bf16 or fp32 in memory) -> one 16-byte bf16 vector.
+// `n_valid` (1..8) elements are in range, the rest are zero-filled; `vec` says 16-byte vector loads are legal.
+DDLS_DEVINL uint4 load8_as_bf16(const void* base, size_t elem_off, int n_valid, bool is_f32, bool vec) {
+  if (!is_f32) {
+    const __nv_bfloat16* src = static_cast<const __nv_bfloat16*>(base) + elem_off;
+    if (vec && n_valid == 8) return *reinterpret_cast<const uint4*>(src);
+    __nv_bfloat16 t[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) t[e] = (e < n_valid) ? src[e] : __float2bfloat16(0.f);
+    return *reinterpret_cast<uint4*>(t);
+  }
+  const float* src = static_cast<const float*>(base) + elem_off;
+  float f[8];
+  if (vec && n_valid == 8) {
+    const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+    f[0] = a.x; f[1] = a.y; f[2] = a.z; f[3] = a.w; f[4] = b.x; f[5] = b.y; f[6] = b.z; f[7] = b.w;
+  } else {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) f[e] = (e < n_valid) ? src[e] : 0.f;
+  }
+  return make_uint4(pack_bf16x2(f[0], f[1]), pack_bf16x2(f[2], f[3]), pack_bf16x2(f[4], f[5]), pack_bf16x2(f[6], f[7]));
+}
 
 // Stage a [rows x GEMM_KC] K-major tile: smem layout [KC/8][rows][8].
 template <int ROWS>
-DDLS_DEVINL void stage_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int row0, int nrows, int k0, int kend,
-                              bool vec_ok) {
+DDLS_DEVINL void stage_kmajor(uint8_t* smem, const void* g, int ld, int row0, int nrows, int k0, int kend,
+                              bool vec_ok, bool is_f32) {
   // warp-level mapping: lane = (kc_local = lane/8, r_local = lane%8) ⇒ 8 rows x 64 B per warp access
   constexpr int KCH = GEMM_KC / 8;
   for (int idx = threadIdx.x; idx < ROWS * KCH; idx += GEMM_THREADS) {
@@ -47,25 +70,15 @@ DDLS_DEVINL void stage_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int
     int kc = kblk * 4 + (lane >> 3);
     int gr = row0 + r, gk = k0 + kc * 8;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (gr < nrows && gk < kend) {
-      const __nv_bfloat16* src = g + (size_t)gr * ld + gk;
-      if (vec_ok && gk + 8 <= kend) {
-        v = *reinterpret_cast<const uint4*>(src);
-      } else {
-        __nv_bfloat16 t[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) t[e] = (gk + e < kend) ? src[e] : __float2bfloat16(0.f);
-        v = *reinterpret_cast<uint4*>(t);
-      }
-    }
+    if (gr < nrows && gk < kend) v = load8_as_bf16(g, (size_t)gr * ld + gk, min(8, kend - gk), is_f32, vec_ok);
     *reinterpret_cast<uint4*>(smem + kc * (ROWS * 16) + r * 16) = v;
   }
 }
 
 // Stage a [GEMM_KC x COLS] tile given MN-contiguous global data: smem layout [KC/8][COLS/8][8 k][8 mn].
 template <int COLS>
-DDLS_DEVINL void stage_mnmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int col0, int ncols, int k0, int kend,
-                               bool vec_ok) {
+DDLS_DEVINL void stage_mnmajor(uint8_t* smem, const void* g, int ld, int col0, int ncols, int k0, int kend,
+                               bool vec_ok, bool is_f32) {
   // lane = (k_local = lane%8, mng_local = lane/8): quarter-warps write 128 contiguous bytes
   constexpr int MNG = COLS / 8;
   for (int idx = threadIdx.x; idx < GEMM_KC * MNG; idx += GEMM_THREADS) {
@@ -75,17 +88,7 @@ DDLS_DEVINL void stage_mnmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, in
     int k = kblk * 8 + (lane & 7);
     int gk = k0 + k, gc = col0 + mng * 8;
     uint4 v = make_uint4(0, 0, 0, 0);
-    if (gk < kend && gc < ncols) {
-      const __nv_bfloat16* src = g + (size_t)gk * ld + gc;
-      if (vec_ok && gc + 8 <= ncols) {
-        v = *reinterpret_cast<const uint4*>(src);
-      } else {
-        __nv_bfloat16 t[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) t[e] = (gc + e < ncols) ? src[e] : __float2bfloat16(0.f);
-        v = *reinterpret_cast<uint4*>(t);
-      }
-    }
+    if (gk < kend && gc < ncols) v = load8_as_bf16(g, (size_t)gk * ld + gc, min(8, ncols - gc), is_f32, vec_ok);
     *reinterpret_cast<uint4*>(smem + (k >> 3) * (COLS * 16) + mng * 128 + (k & 7) * 16) = v;
   }
 }
@@ -117,8 +120,9 @@ __global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
   tc_fence_after();
   const uint32_t tmem_d = tmem_base_s;
 
-  const bool a_vec = ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) && (p.lda % 8 == 0);
-  const bool b_vec = ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0) && (p.ldb % 8 == 0);
+  const bool a_f32 = p.flags & DDLS_GEMM_A_F32, b_f32 = p.flags & DDLS_GEMM_B_F32;
+  const bool a_vec = ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0) && (p.lda % (a_f32 ? 4 : 8) == 0);
+  const bool b_vec = ((reinterpret_cast<uintptr_t>(p.B) & 15) == 0) && (p.ldb % (b_f32 ? 4 : 8) == 0);
   constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
 
   const int nkb = (kend - kbeg + GEMM_KC - 1) / GEMM_KC;
@@ -130,20 +134,18 @@ __global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
       ++waits[s];
     }
     const int k0 = kbeg + kb * GEMM_KC;
-    if (A_MN) stage_mnmajor<GEMM_BM>(sA[s], p.A, p.lda, m0, p.M, k0, kend, a_vec);
-    else      stage_kmajor<GEMM_BM>(sA[s], p.A, p.lda, m0, p.M, k0, kend, a_vec);
-    if (B_MN) stage_mnmajor<BN>(sB[s], p.B, p.ldb, n0, p.N, k0, kend, b_vec);
-    else      stage_kmajor<BN>(sB[s], p.B, p.ldb, n0, p.N, k0, kend, b_vec);
+    if (A_MN) stage_mnmajor<GEMM_BM>(sA[s], p.A, p.lda, m0, p.M, k0, kend, a_vec, a_f32);
+    else      stage_kmajor<GEMM_BM>(sA[s], p.A, p.lda, m0, p.M, k0, kend, a_vec, a_f32);
+    if (B_MN) stage_mnmajor<BN>(sB[s], p.B, p.ldb, n0, p.N, k0, kend, b_vec, b_f32);
+    else      stage_kmajor<BN>(sB[s], p.B, p.ldb, n0, p.N, k0, kend, b_vec, b_f32);
     fence_proxy_async_smem();
     __syncthreads();
     if (threadIdx.x == 0) {
       tc_fence_after();
       const uint32_t a_base = smem_u32(sA[s]), b_base = smem_u32(sB[s]);
       // both staged layouts: K-group stride (LBO) = extent*16 B, 8-row / 8-element group stride (SBO) = 128 B
-      uint32_t a_lbo = GEMM_BM * 16u, a_sbo = 128u;
-      uint32_t b_lbo = BN * 16u, b_sbo = 128u;
-      if (p.debug & 1u) { uint32_t t = a_lbo; a_lbo = a_sbo; a_sbo = t; }
-      if (p.debug & 2u) { uint32_t t = b_lbo; b_lbo = b_sbo; b_sbo = t; }
+      const uint32_t a_lbo = GEMM_BM * 16u, a_sbo = 128u;
+      const uint32_t b_lbo = BN * 16u, b_sbo = 128u;
 #pragma unroll
       for (int ks = 0; ks < GEMM_KC / 16; ++ks) {
         // one UMMA consumes K=16 = two 8-wide K groups; both layouts advance by 2 K-groups per step
@@ -170,6 +172,25 @@ __global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
   const uint32_t t_row = tmem_d + (static_cast<uint32_t>(warp * 32) << 16);
   const bool relu = p.flags & DDLS_GEMM_RELU, has_bias = (p.flags & DDLS_GEMM_BIAS) && blockIdx.z == 0;
   const bool out_bf16 = p.flags & DDLS_GEMM_OUT_BF16, atomic = p.flags & DDLS_GEMM_ATOMIC_ADD;
+  if (p.flags & DDLS_GEMM_SPLITK_WS) {
+    // raw fp32 partial tile -> workspace[split][row][col]; bias/ReLU/cast happen in splitk_finish_kernel
+    float* ws = p.workspace + (size_t)blockIdx.z * p.M * p.N;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(t_row + c0, v);
+      tmem_ld_wait();
+      if (row < p.M) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          if (n0 + c0 + j < p.N) ws[(size_t)row * p.N + n0 + c0 + j] = __uint_as_float(v[j]);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc(tmem_d, TM_COLS);
+    return;
+  }
 #pragma unroll 1
   for (int c0 = 0; c0 < BN; c0 += 16) {
     uint32_t v[16];
@@ -184,7 +205,7 @@ __global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
           if (has_bias) x += p.bias[col];
           if (relu) x = fmaxf(x, 0.f);
           const size_t o = (size_t)row * p.ldc + col;
-          if (atomic) atomicAdd(reinterpret_cast<float*>(p.C) + o, x);
+          if (atomic) reinterpret_cast<float*>(p.C)[o] += x;   // one CTA owns each output when splits == 1
           else if (out_bf16) reinterpret_cast<__nv_bfloat16*>(p.C)[o] = __float2bfloat16(x);
           else reinterpret_cast<float*>(p.C)[o] = x;
         }
@@ -194,6 +215,27 @@ __global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_d, TM_COLS);
+}
+
+// Sum split-K partials and apply the fused epilogue.  One thread per 4 consecutive outputs of a row.
+__global__ void __launch_bounds__(256) splitk_finish_kernel(const float* __restrict__ ws, void* __restrict__ C,
+                                                            const float* __restrict__ bias, int M, int N, int ldc,
+                                                            int splits, uint32_t flags) {
+  const size_t total = (size_t)M * N;
+  const bool relu = flags & DDLS_GEMM_RELU, has_bias = flags & DDLS_GEMM_BIAS, out_bf16 = flags & DDLS_GEMM_OUT_BF16;
+  const bool accum = flags & DDLS_GEMM_ACCUMULATE;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    float acc = 0.f;
+#pragma unroll 8
+    for (int s = 0; s < splits; ++s) acc += ws[(size_t)s * total + i];
+    const int r = (int)(i / N), c = (int)(i - (size_t)r * N);
+    if (has_bias) acc += bias[c];
+    if (relu) acc = fmaxf(acc, 0.f);
+    const size_t o = (size_t)r * ldc + c;
+    if (out_bf16) static_cast<__nv_bfloat16*>(C)[o] = __float2bfloat16(acc);
+    else if (accum) static_cast<float*>(C)[o] += acc;
+    else static_cast<float*>(C)[o] = acc;
+  }
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -219,24 +261,38 @@ static int dispatch_bn(const GemmParams& p, int splits, cudaStream_t st) {
 
 extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda,
                               int ldb, int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags,
-                              unsigned debug, void* stream) {
+                              void* workspace, size_t workspace_bytes, void* stream) {
   using namespace ddls;
   if (M <= 0 || N <= 0 || K <= 0) { set_last_error("ddls_gemm_bf16: empty problem"); return 1; }
   GemmParams p;
-  p.A = static_cast<const __nv_bfloat16*>(A); p.B = static_cast<const __nv_bfloat16*>(B); p.C = C; p.bias = bias;
-  p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.flags = flags; p.debug = debug;
+  p.A = A; p.B = B; p.C = C; p.bias = bias;
+  p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.workspace = static_cast<float*>(workspace);
+  p.flags = flags & ~(DDLS_GEMM_ATOMIC_ADD | DDLS_GEMM_SPLITK_WS);
   int splits = split_k < 1 ? 1 : split_k;
   int kps = (K + splits - 1) / splits;
   kps = (kps + GEMM_KC - 1) / GEMM_KC * GEMM_KC;
   splits = (K + kps - 1) / kps;
   p.k_per_split = kps;
-  if (splits > 1) {
-    if (flags & (DDLS_GEMM_OUT_BF16 | DDLS_GEMM_RELU)) {
-      set_last_error("ddls_gemm_bf16: split-K needs fp32 accumulate output without ReLU"); return 1;
-    }
-    p.flags |= DDLS_GEMM_ATOMIC_ADD;
-  }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (a_mn_major) return b_mn_major ? dispatch_bn<true, true>(p, splits, st) : dispatch_bn<true, false>(p, splits, st);
-  return b_mn_major ? dispatch_bn<false, true>(p, splits, st) : dispatch_bn<false, false>(p, splits, st);
+  const unsigned epi = flags & (DDLS_GEMM_RELU | DDLS_GEMM_BIAS | DDLS_GEMM_OUT_BF16 | DDLS_GEMM_ACCUMULATE);
+  if (splits > 1) {
+    const size_t need = (size_t)splits * M * N * sizeof(float);
+    if (workspace == nullptr || workspace_bytes < need) {
+      set_last_error("ddls_gemm_bf16: split_k=%d needs a %zu-byte workspace (got %zu)", splits, need, workspace_bytes);
+      return 1;
+    }
+    p.flags = (p.flags & ~epi) | DDLS_GEMM_SPLITK_WS;
+  } else if (flags & DDLS_GEMM_ACCUMULATE) {
+    p.flags |= DDLS_GEMM_ATOMIC_ADD;   // single split accumulating into C
+  }
+  int rc;
+  if (a_mn_major) rc = b_mn_major ? dispatch_bn<true, true>(p, splits, st) : dispatch_bn<true, false>(p, splits, st);
+  else rc = b_mn_major ? dispatch_bn<false, true>(p, splits, st) : dispatch_bn<false, false>(p, splits, st);
+  if (rc || splits == 1) return rc;
+  const size_t total = (size_t)M * N;
+  int blocks = (int)((total + 255) / 256);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  splitk_finish_kernel<<<blocks, 256, 0, st>>>(p.workspace, C, bias, M, N, ldc, splits, epi);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "splitk_finish_kernel launch");
 }

@@ -42,6 +42,8 @@ def lib() -> ctypes.CDLL:
     _proto(L, 'ddls_last_error', [], c_char_p)
     _proto(L, 'ddls_version', [], c_int)
     _proto(L, 'ddls_launch_count', [], c_ulonglong)
+    if hasattr(L, 'ddls_cnn_conv2_wgrad_scratch_bytes'):
+        _proto(L, 'ddls_cnn_conv2_wgrad_scratch_bytes', [c_int], c_size_t)
     for name, args in _PROTOTYPES.items():
         if hasattr(L, name):
             _proto(L, name, args)
@@ -51,7 +53,7 @@ def lib() -> ctypes.CDLL:
 
 P = c_void_p
 _PROTOTYPES = {
-    'ddls_gemm_bf16': [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_uint, c_uint, P],
+    'ddls_gemm_bf16': [P, P, P, P, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_uint, P, c_size_t, P],
     'ddls_adam_step': [P, P, P, P, P, c_size_t, c_float, c_float, c_float, c_float, c_float, c_int, P],
     'ddls_adagrad_step': [P, P, P, P, c_size_t, c_float, c_float, c_float, c_int, P],
     'ddls_sgd_step': [P, P, P, c_size_t, c_float, c_float, c_int, P],

@@ -24,13 +24,18 @@ unsigned long long ddls_launch_count(void);
 #define DDLS_GEMM_RELU 1u
 #define DDLS_GEMM_BIAS 2u
 #define DDLS_GEMM_OUT_BF16 4u
-#define DDLS_GEMM_ATOMIC_ADD 8u
+#define DDLS_GEMM_ATOMIC_ADD 8u   /* internal */
+#define DDLS_GEMM_A_F32 16u       /* A is fp32 in memory (converted to bf16 while staging) */
+#define DDLS_GEMM_B_F32 32u       /* B is fp32 in memory */
+#define DDLS_GEMM_SPLITK_WS 64u   /* internal */
+#define DDLS_GEMM_ACCUMULATE 128u /* C += result (fp32 C) */
 /* C[M,N] = op(A)·op(B)ᵀ (+bias, ReLU, cast).  a_mn_major=0: A is [M,K] row-major; 1: A is [K,M]
- * row-major.  Same for B over N.  split_k>1 accumulates fp32 partials with red.add into a
- * caller-zeroed C.  (Keras Dense / matmul, /root/reference/ddl_mnist_aztk.py:189-191.) */
+ * row-major.  Same for B over N.  Operands are bf16, or fp32 with the *_F32 flags.  split_k>1 writes
+ * fp32 partial tiles to `workspace` (split_k*M*N*4 bytes of scratch) and a second kernel sums them
+ * and applies the epilogue — no atomics.  (Keras Dense / matmul, /root/reference/ddl_mnist_aztk.py:189-191.) */
 int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
-                   int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags, unsigned debug,
-                   void* stream);
+                   int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags, void* workspace,
+                   size_t workspace_bytes, void* stream);
 
 /* ---- fused optimizers over a flat fp32 parameter space --------------------------------------
  * Keras-2 update rules named by the reference ('adam' ddl_mnist_aztk.py:195, ddl_nyiso_aztk.py:255;
@@ -81,6 +86,27 @@ int ddls_dense_mse(const float* h, const float* wd, const float* bd, const float
  * probabilities only.  Caller zeroes loss[1], dw [F,C], db [C]. */
 int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, const float* onehot, float* probs,
                             float* loss, float* da, float* dw, float* db, int B, int F, int C, void* stream);
+
+/* ---- MNIST CNN trunk (/root/reference/ddl_mnist_aztk.py:180-190), NHWC, Keras kernel layouts --------
+ * conv1+ReLU: x [B,28,28,1] fp32 -> a1 [B,26,26,32] bf16. */
+int ddls_cnn_conv1_fwd(const float* x, const float* w1, const float* b1, void* a1, int B, void* stream);
+/* conv2+bias+ReLU+maxpool 2x2 (tcgen05 implicit GEMM): a1 -> pooled [B,12,12,32] bf16 + arg-max idx u8. */
+int ddls_cnn_conv2_pool_fwd(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
+                            void* stream);
+/* dz = da*(a>0) as bf16 [B,ldz] (zero padded) and db[f] += sum_b dz  (caller zeroes db). */
+int ddls_relu_bwd_bias(const float* da, const float* a, void* dz, float* db, int B, int F, int ldz, void* stream);
+/* max-pool + ReLU backward: dflat [B,12,12,32] bf16 -> dz2 [B,24,24,32] bf16; db2[c] += sum (caller zeroes). */
+int ddls_cnn_unpool_bwd(const void* dflat, const void* pooled, const void* pidx, void* dz2, float* db2, int B,
+                        void* stream);
+/* conv2 weight gradient dw2 [3,3,32,32] fp32 (tcgen05, split over pixels; partial tiles in `scratch`). */
+size_t ddls_cnn_conv2_wgrad_scratch_bytes(int B);
+int ddls_cnn_conv2_wgrad(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
+                         void* stream);
+/* conv2 data gradient fused with conv1's ReLU mask: dz1 [B,26,26,32] bf16. */
+int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream);
+/* conv1 gradients: dw1_db1 = [3*3*1*32 kernel gradient | 32 bias gradient] fp32; scratch B*320*4 bytes. */
+int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_db1, void* scratch, size_t scratch_bytes, int B,
+                         void* stream);
 
 #ifdef __cplusplus
 }
