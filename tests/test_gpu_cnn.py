@@ -22,6 +22,37 @@ def _model(dev, seed=0):
     return m
 
 
+class _RoundGrad(torch.autograd.Function):
+    """Identity whose gradient is rounded to bf16 (the kernels store activation gradients in bf16)."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.view_as(x)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g.bfloat16().float()
+
+
+def _bf(t):
+    return t.bfloat16().float()
+
+
+def _reference_trunk(m, x):
+    """fp32 PyTorch trunk with bf16 rounding at exactly the points where the kernels store bf16
+    (a1, conv2/dense weights as tensor-core operands, pooled, and the activation gradients), so ReLU
+    masks and pooling arg-max decisions are taken on the same values as in the kernels."""
+    import torch.nn.functional as F
+    c1, c2, d1 = m.layers[0], m.layers[2], m.layers[6]
+    z1 = F.conv2d(x.permute(0, 3, 1, 2), c1.kernel.permute(3, 2, 0, 1), c1.bias)
+    a1 = _bf(torch.relu(_RoundGrad.apply(z1)))
+    z2 = F.conv2d(a1, _bf(c2.kernel).permute(3, 2, 0, 1), c2.bias)
+    p = _bf(torch.relu(F.max_pool2d(z2, 2)))
+    flat = _RoundGrad.apply(p.permute(0, 2, 3, 1).reshape(x.shape[0], -1))
+    z3 = flat @ _bf(d1.kernel) + d1.bias
+    return torch.relu(_RoundGrad.apply(z3))
+
+
 @pytest.mark.parametrize('B', [128, 5, 37])
 def test_cnn_trunk_forward_backward_match_fp32(B):
     from distributeddeeplearningspark_b200.ops import cnn, fused
@@ -29,26 +60,29 @@ def test_cnn_trunk_forward_backward_match_fp32(B):
     m = _model(dev)
     torch.manual_seed(B)
     x = torch.rand(B, 28, 28, 1, device=dev)
-    ls = m.layers
-    a = x
-    for l in ls[:8]:
-        a = l(a)                               # torch reference trunk (fp32)
+    a = _reference_trunk(m, x)
     w = torch.randn_like(a)
     (a * w).sum().backward()
-    ref_grads = [p.grad.clone() for _, p in m.named_keras_weights()][:6]
+    ref_grads = [p.grad.clone() for _, p in m.named_keras_weights()[:6]]
     for _, p in m.named_keras_weights():
         p.grad = None
+    # sanity: the rounding-aware reference is itself close to the plain fp32 layers
+    plain = x
+    for l in m.layers[:8]:
+        plain = l(plain)
+    assert _rel(a.detach(), plain.detach()) < 2e-2
     plan = fused._plan(m)
     assert plan['kind'] == 'cnn' and cnn.native_available(plan, x)
     out = cnn.trunk(plan, x)
     assert out.shape == a.shape
-    assert _rel(out, a.detach()) < 2e-2, _rel(out, a.detach())
+    assert _rel(out, a.detach()) < 2e-3, _rel(out, a.detach())
     (out * w).sum().backward()
     names = ['conv1.k', 'conv1.b', 'conv2.k', 'conv2.b', 'dense1.k', 'dense1.b']
     grads = [p.grad for _, p in m.named_keras_weights()][:6]
     for n, g, r in zip(names, grads, ref_grads):
         assert g is not None and g.shape == r.shape, n
-        assert _rel(g, r) < 5e-2, (n, _rel(g, r))
+        l2 = float((g - r).norm() / (r.norm() + 1e-12))
+        assert l2 < 1e-2, (n, l2)
 
 
 def test_cnn_loss_and_probs_match_reference_path():
