@@ -1,0 +1,457 @@
+// Peer-memory collectives over NVLink 5 / NVSwitch (K15-K19 of SURVEY.md §2.5).
+//
+// Every rank maps every peer's symmetric heap (csrc/symm.cpp), so a collective is ONE kernel that
+// moves data with plain stores/loads on peer pointers (or `multimem.*` through the switch), fused with
+// the 1/N (or 1/window) scale and the bf16 <-> fp32 wire cast, and synchronises with epoch-numbered
+// flag words (`st.release.sys` / `ld.acquire.sys`) that live in the heaps:
+//
+//   one-shot  : push my whole message into a staging slot on every peer, one flag round, reduce locally
+//               in rank order (bit-identical result on every rank).  Latency-optimal; default for the
+//               200 KB - 4 MB gradients of the reference's models.
+//   two-shot  : reduce-scatter by push, reduce my slice, all-gather by push.  2(N-1)/N bytes per rank.
+//   nvls      : `multimem.ld_reduce` my slice through the switch + `multimem.st` broadcast.
+//   broadcast : root stores through the multicast mapping (or pushes to each peer).
+//   allgather : every rank pushes its chunk into every peer's output.
+//   adag      : center += scale*(w - w_pulled) via `multimem.red`, then pull (asynchronous, no barrier).
+//
+// All addresses are (heap base of rank r) + (symmetric offset), so the same kernel also runs in an
+// emulation mode on one GPU: blockIdx.y enumerates the emulated ranks inside a single cooperative
+// launch (never as separate launches that wait on each other).
+// The reference's equivalent is dist-keras' pickle-over-TCP commit/pull.
+#include <cstdio>
+
+#include "common.cuh"
+#include "../include/ddls_b200.h"
+
+namespace ddls {
+
+constexpr int MAXR = DDLS_MAX_RANKS;
+constexpr int COMM_THREADS = 512;
+constexpr int MAX_CHANNELS = DDLS_COMM_MAX_BLOCKS;
+
+struct CommCtx {
+  uint8_t* base[MAXR];   // local mappings of every rank's heap
+  uint8_t* mc_base;      // multicast mapping of the heaps (nullptr if unavailable)
+  int world;
+  int rank_base;         // this process' rank (0 in emulation mode, where blockIdx.y adds the rank)
+  uint64_t flags_off;    // uint32 [MAX_CHANNELS][MAXR] written by peers
+  uint64_t seq_off;      // uint32 [2]: {completed epochs, arrival ticket}
+  uint64_t timeout_ns;
+};
+
+DDLS_DEVINL uint64_t globaltimer_ns() {
+  uint64_t t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+
+// Flag barrier among same-index blocks of all ranks.  Called by the whole block; data written before the
+// call (by any thread of the block) is visible to peers' readers after their matching wait.
+DDLS_DEVINL void peer_barrier(const CommCtx& c, int rank, int channel, uint32_t epoch) {
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x < c.world) {
+    const int r = threadIdx.x;
+    uint32_t* remote = reinterpret_cast<uint32_t*>(c.base[r] + c.flags_off) + channel * MAXR + rank;
+    st_release_sys(remote, epoch);
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.base[rank] + c.flags_off) + channel * MAXR + r;
+    const uint64_t t0 = globaltimer_ns();
+    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
+      if (globaltimer_ns() - t0 > c.timeout_ns) {
+        printf("ddls comm: rank %d channel %d timed out waiting for rank %d at epoch %u (saw %u)\n", rank, channel, r,
+               epoch, ld_relaxed_sys(mine));
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+// Epoch protocol: the per-rank counter is even between collectives; every collective consumes two values
+// (e0+1 for its first flag round, e0+2 for its second, if any) and the staging parity (e0 >> 1) & 1 flips on
+// every call, so a fast rank pushing for call k+1 never lands in a slot a slow rank still reads for call k.
+// All blocks read the epoch counter on entry; the last block to leave advances it (cf. publish_step).
+DDLS_DEVINL uint32_t read_epoch(const CommCtx& c, int rank) {
+  return *reinterpret_cast<volatile uint32_t*>(c.base[rank] + c.seq_off);
+}
+DDLS_DEVINL void advance_epoch(const CommCtx& c, int rank, uint32_t new_value) {
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* seq = reinterpret_cast<uint32_t*>(c.base[rank] + c.seq_off);
+    __threadfence();
+    const uint32_t ticket = atomicAdd(seq + 1, 1u);
+    if (ticket == gridDim.x - 1) { seq[0] = new_value; seq[1] = 0; __threadfence(); }
+  }
+}
+
+template <typename Wire> struct WireOps;
+template <> struct WireOps<float> {
+  using vec = float4;                       // 4 elements per 16 B
+  static constexpr int EPV = 4;
+  DDLS_DEVINL static vec pack(const float* v) { return make_float4(v[0], v[1], v[2], v[3]); }
+  DDLS_DEVINL static void unpack(const vec& p, float* v) { v[0] = p.x; v[1] = p.y; v[2] = p.z; v[3] = p.w; }
+};
+template <> struct WireOps<__nv_bfloat16> {
+  using vec = uint2;                        // 4 elements per 8 B
+  static constexpr int EPV = 4;
+  DDLS_DEVINL static vec pack(const float* v) { return make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3])); }
+  DDLS_DEVINL static void unpack(const vec& p, float* v) {
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&p.x), b = *reinterpret_cast<const __nv_bfloat162*>(&p.y);
+    v[0] = __low2float(a); v[1] = __high2float(a); v[2] = __low2float(b); v[3] = __high2float(b);
+  }
+};
+
+struct ArParams {
+  uint64_t in_off, out_off;   // fp32 [n] in each heap (may alias)
+  uint64_t stage_off;         // staging [2 parities][world][n] wire elements
+  uint64_t n;                 // elements, multiple of 4
+  float scale;
+};
+
+// ---------------------------------------------------------------------------------------------------------
+// one-shot push allreduce
+// ---------------------------------------------------------------------------------------------------------
+template <typename Wire>
+__global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_kernel(CommCtx c, ArParams p) {
+  using W = WireOps<Wire>;
+  using V = typename W::vec;
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t e0 = read_epoch(c, rank);
+  const uint32_t epoch = e0 + 1;
+  const uint64_t nvec = p.n / 4;
+  const uint64_t per = (nvec + gridDim.x - 1) / gridDim.x;
+  const uint64_t lo = blockIdx.x * per, hi = min(nvec, lo + per);
+  const float4* in = reinterpret_cast<const float4*>(c.base[rank] + p.in_off);
+  const uint64_t slot_vecs = nvec;                       // one slot = n wire elements
+  const uint64_t parity_vecs = slot_vecs * c.world;
+  const uint64_t par = (e0 >> 1) & 1u;
+  // push my slice to every peer's staging slot [parity][rank]
+  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    const float4 x = in[i];
+    const float xv[4] = {x.x, x.y, x.z, x.w};
+    const V w = W::pack(xv);
+    for (int d = 1; d < c.world; ++d) {
+      const int r = (rank + d) % c.world;                // stagger destinations across ranks
+      V* dst = reinterpret_cast<V*>(c.base[r] + p.stage_off) + par * parity_vecs + (uint64_t)rank * slot_vecs + i;
+      *dst = w;
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, epoch);
+  const V* stage = reinterpret_cast<const V*>(c.base[rank] + p.stage_off) + par * parity_vecs;
+  float4* out = reinterpret_cast<float4*>(c.base[rank] + p.out_off);
+  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const float4 mine = in[i];
+    for (int r = 0; r < c.world; ++r) {                   // fixed rank order => identical bits on every rank
+      float v[4];
+      if (r == rank) {
+        const float mv[4] = {mine.x, mine.y, mine.z, mine.w};
+        const V w = W::pack(mv);                         // round my own contribution like the wire does
+        W::unpack(w, v);
+      } else {
+        W::unpack(stage[(uint64_t)r * slot_vecs + i], v);
+      }
+      acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3];
+    }
+    out[i] = make_float4(acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale);
+  }
+  advance_epoch(c, rank, e0 + 2);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// two-shot: reduce-scatter by push -> reduce own slice -> all-gather by push.  out must be symmetric.
+// ---------------------------------------------------------------------------------------------------------
+template <typename Wire>
+__global__ void __launch_bounds__(COMM_THREADS) allreduce_twoshot_kernel(CommCtx c, ArParams p) {
+  using W = WireOps<Wire>;
+  using V = typename W::vec;
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t e0 = read_epoch(c, rank);
+  const uint32_t epoch = e0 + 1;
+  const uint64_t nvec = p.n / 4;
+  // block slice, then rank sub-slice inside it
+  const uint64_t per_blk = (nvec + gridDim.x - 1) / gridDim.x;
+  const uint64_t blo = blockIdx.x * per_blk, bhi = min(nvec, blo + per_blk);
+  const uint64_t per_rank = (bhi > blo) ? ((bhi - blo) + c.world - 1) / c.world : 0;
+  const float4* in = reinterpret_cast<const float4*>(c.base[rank] + p.in_off);
+  const uint64_t par = (e0 >> 1) & 1u;
+  const uint64_t slot_vecs = nvec;
+  const uint64_t parity_vecs = slot_vecs * c.world;
+  for (int d = 1; d < c.world; ++d) {
+    const int r = (rank + d) % c.world;
+    const uint64_t lo = blo + r * per_rank, hi = min(bhi, lo + per_rank);
+    V* dst = reinterpret_cast<V*>(c.base[r] + p.stage_off) + par * parity_vecs + (uint64_t)rank * slot_vecs;
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+      const float4 x = in[i];
+      const float xv[4] = {x.x, x.y, x.z, x.w};
+      dst[i] = W::pack(xv);
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, epoch);
+  {
+    const uint64_t lo = blo + rank * per_rank, hi = min(bhi, lo + per_rank);
+    const V* stage = reinterpret_cast<const V*>(c.base[rank] + p.stage_off) + par * parity_vecs;
+    for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const float4 mine = in[i];
+      for (int r = 0; r < c.world; ++r) {
+        float v[4];
+        if (r == rank) {
+          const float mv[4] = {mine.x, mine.y, mine.z, mine.w};
+          W::unpack(W::pack(mv), v);
+        } else {
+          W::unpack(stage[(uint64_t)r * slot_vecs + i], v);
+        }
+        acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3];
+      }
+      const float4 res = make_float4(acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale);
+      for (int d = 0; d < c.world; ++d) {
+        const int r = (rank + d) % c.world;
+        reinterpret_cast<float4*>(c.base[r] + p.out_off)[i] = res;
+      }
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  advance_epoch(c, rank, epoch + 1);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// NVLS: in-switch reduction + multicast store.  in/out symmetric, bound to the multicast object.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c, ArParams p) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t epoch = read_epoch(c, rank) + 1;
+  const uint64_t nvec = p.n / 4;
+  const uint64_t per_blk = (nvec + gridDim.x - 1) / gridDim.x;
+  const uint64_t blo = blockIdx.x * per_blk, bhi = min(nvec, blo + per_blk);
+  const uint64_t per_rank = (bhi > blo) ? ((bhi - blo) + c.world - 1) / c.world : 0;
+  const uint64_t lo = blo + rank * per_rank, hi = min(bhi, lo + per_rank);
+  peer_barrier(c, rank, blockIdx.x, epoch);               // every rank's input is final
+  const float* mc_in = reinterpret_cast<const float*>(c.mc_base + p.in_off);
+  float* mc_out = reinterpret_cast<float*>(c.mc_base + p.out_off);
+  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    float4 v = multimem_ld_reduce_f32x4(mc_in + 4 * i);
+    v.x *= p.scale; v.y *= p.scale; v.z *= p.scale; v.w *= p.scale;
+    multimem_st_f32x4(mc_out + 4 * i, v);
+  }
+  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  advance_epoch(c, rank, epoch + 1);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// broadcast: root's buffer -> every rank's buffer at the same offset (16-byte vectors)
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(COMM_THREADS) broadcast_kernel(CommCtx c, uint64_t off, uint64_t nvec16, int root,
+                                                                 int use_mc) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t epoch = read_epoch(c, rank) + 1;
+  const uint64_t per = (nvec16 + gridDim.x - 1) / gridDim.x;
+  const uint64_t lo = blockIdx.x * per, hi = min(nvec16, lo + per);
+  peer_barrier(c, rank, blockIdx.x, epoch);               // receivers are done with the old contents
+  if (rank == root) {
+    const float4* src = reinterpret_cast<const float4*>(c.base[rank] + off);
+    if (use_mc && c.mc_base != nullptr) {
+      float* dst = reinterpret_cast<float*>(c.mc_base + off);
+      for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) multimem_st_f32x4(dst + 4 * i, src[i]);
+    } else {
+      for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+        const float4 v = src[i];
+        for (int d = 1; d < c.world; ++d)
+          reinterpret_cast<float4*>(c.base[(rank + d) % c.world] + off)[i] = v;
+      }
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  advance_epoch(c, rank, epoch + 1);
+}
+
+// allgather: out[r*chunk : (r+1)*chunk] on every rank = rank r's in (16-byte vectors; out symmetric)
+__global__ void __launch_bounds__(COMM_THREADS) allgather_kernel(CommCtx c, uint64_t in_off, uint64_t out_off,
+                                                                 uint64_t chunk_vec16) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t epoch = read_epoch(c, rank) + 1;
+  const uint64_t per = (chunk_vec16 + gridDim.x - 1) / gridDim.x;
+  const uint64_t lo = blockIdx.x * per, hi = min(chunk_vec16, lo + per);
+  const float4* src = reinterpret_cast<const float4*>(c.base[rank] + in_off);
+  peer_barrier(c, rank, blockIdx.x, epoch);
+  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    const float4 v = src[i];
+    for (int d = 0; d < c.world; ++d) {
+      const int r = (rank + d) % c.world;
+      reinterpret_cast<float4*>(c.base[r] + out_off)[(uint64_t)rank * chunk_vec16 + i] = v;
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  advance_epoch(c, rank, epoch + 1);
+}
+
+__global__ void __launch_bounds__(32) barrier_kernel(CommCtx c) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t epoch = read_epoch(c, rank) + 1;
+  peer_barrier(c, rank, 0, epoch);
+  advance_epoch(c, rank, epoch + 1);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// ADAG / DynSGD commit + pull against a center variable replicated in every heap (K19).
+//   delta = (w - pulled) * scale ;  center (all replicas) += delta  via multimem.red (or peer atomics)
+//   then w = pulled = local center replica.  No barrier: ranks run asynchronously, like the original
+//   parameter server.  `updates_off` is a replicated uint32 commit counter.
+// ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(COMM_THREADS) adag_commit_kernel(CommCtx c, float* __restrict__ w,
+                                                                   float* __restrict__ pulled, uint64_t center_off,
+                                                                   uint64_t updates_off, uint64_t n, float scale,
+                                                                   int staleness_aware, uint32_t* last_update) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint64_t nvec = n / 4;
+  float s = scale;
+  if (staleness_aware) {
+    const uint32_t now = ld_relaxed_sys(reinterpret_cast<const uint32_t*>(c.base[rank] + updates_off));
+    s = scale / (float)(now - *last_update + 1u);
+  }
+  float4* w4 = reinterpret_cast<float4*>(w);
+  float4* p4 = reinterpret_cast<float4*>(pulled);
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < nvec; i += (uint64_t)gridDim.x * blockDim.x) {
+    const float4 a = w4[i], b = p4[i];
+    const float4 d = make_float4((a.x - b.x) * s, (a.y - b.y) * s, (a.z - b.z) * s, (a.w - b.w) * s);
+    if (c.mc_base != nullptr) {
+      multimem_red_add_f32x4(reinterpret_cast<float*>(c.mc_base + center_off) + 4 * i, d);
+    } else {
+      for (int r = 0; r < c.world; ++r) {
+        float* dst = reinterpret_cast<float*>(c.base[r] + center_off) + 4 * i;
+        atomicAdd(dst + 0, d.x); atomicAdd(dst + 1, d.y); atomicAdd(dst + 2, d.z); atomicAdd(dst + 3, d.w);
+      }
+    }
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (blockIdx.x == 0 && threadIdx.x == 0) {
+    if (c.mc_base != nullptr) multimem_red_add_u32(reinterpret_cast<uint32_t*>(c.mc_base + updates_off), 1u);
+    else for (int r = 0; r < c.world; ++r) atomicAdd(reinterpret_cast<uint32_t*>(c.base[r] + updates_off), 1u);
+  }
+}
+
+__global__ void __launch_bounds__(COMM_THREADS) adag_pull_kernel(CommCtx c, float* __restrict__ w,
+                                                                 float* __restrict__ pulled, uint64_t center_off,
+                                                                 uint64_t updates_off, uint64_t n, uint32_t* last_update) {
+  const int rank = c.rank_base + blockIdx.y;
+  const float4* cen = reinterpret_cast<const float4*>(c.base[rank] + center_off);
+  float4* w4 = reinterpret_cast<float4*>(w);
+  float4* p4 = reinterpret_cast<float4*>(pulled);
+  for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n / 4; i += (uint64_t)gridDim.x * blockDim.x) {
+    const float4 v = cen[i];
+    w4[i] = v; p4[i] = v;
+  }
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+    *last_update = ld_relaxed_sys(reinterpret_cast<const uint32_t*>(c.base[rank] + updates_off));
+}
+
+static int make_ctx(const DdlsCommDesc* d, CommCtx* c) {
+  if (d->world < 1 || d->world > MAXR) { set_last_error("comm: world must be in [1,%d]", MAXR); return 1; }
+  for (int r = 0; r < MAXR; ++r) c->base[r] = r < d->world ? static_cast<uint8_t*>(d->base[r]) : nullptr;
+  c->mc_base = static_cast<uint8_t*>(d->mc_base);
+  c->world = d->world;
+  c->rank_base = d->emulate ? 0 : d->rank;
+  c->flags_off = d->flags_off;
+  c->seq_off = d->seq_off;
+  c->timeout_ns = d->timeout_ms ? (uint64_t)d->timeout_ms * 1000000ull : 20000000000ull;
+  return 0;
+}
+
+template <typename... Args>
+static int launch(const DdlsCommDesc* d, void (*kern)(Args...), int blocks, int threads, cudaStream_t st, Args... args) {
+  dim3 grid(blocks, d->emulate ? d->world : 1);
+  if (d->emulate) {
+    // emulated ranks spin on each other: all blocks must be co-resident => cooperative launch
+    void* ptrs[] = {(void*)&args...};
+    DDLS_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(threads), ptrs, 0, st));
+  } else {
+    kern<<<grid, threads, 0, st>>>(args...);
+  }
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "comm kernel launch");
+}
+
+static int pick_blocks(uint64_t n, int requested) {
+  if (requested > 0) return requested > MAX_CHANNELS ? MAX_CHANNELS : requested;
+  const uint64_t bytes = n * 4;
+  int b = (int)((bytes + (128 << 10) - 1) / (128 << 10));   // ~128 KB of payload per block
+  if (b < 1) b = 1;
+  if (b > MAX_CHANNELS) b = MAX_CHANNELS;
+  return b;
+}
+
+}  // namespace ddls
+
+using namespace ddls;
+
+extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64_t out_off,
+                                   uint64_t stage_off, uint64_t n, float scale, int wire_bf16, int blocks, void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  if (n == 0) return 0;
+  if (n % 4 != 0 || (in_off | out_off | stage_off) % 16 != 0) {
+    set_last_error("ddls_comm_allreduce: n must be a multiple of 4 and offsets 16-byte aligned");
+    return 1;
+  }
+  ArParams p{in_off, out_off, stage_off, n, scale};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = pick_blocks(n, blocks);
+  switch (algo) {
+    case DDLS_AR_ONESHOT:
+      return wire_bf16 ? launch(d, allreduce_oneshot_kernel<__nv_bfloat16>, nb, COMM_THREADS, st, c, p)
+                       : launch(d, allreduce_oneshot_kernel<float>, nb, COMM_THREADS, st, c, p);
+    case DDLS_AR_TWOSHOT:
+      return wire_bf16 ? launch(d, allreduce_twoshot_kernel<__nv_bfloat16>, nb, COMM_THREADS, st, c, p)
+                       : launch(d, allreduce_twoshot_kernel<float>, nb, COMM_THREADS, st, c, p);
+    case DDLS_AR_NVLS:
+      if (c.mc_base == nullptr) { set_last_error("ddls_comm_allreduce: NVLS needs a multicast mapping"); return 1; }
+      return launch(d, allreduce_nvls_kernel, nb, COMM_THREADS, st, c, p);
+  }
+  set_last_error("ddls_comm_allreduce: unknown algorithm %d", algo);
+  return 1;
+}
+
+extern "C" int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast,
+                                   int blocks, void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  if (bytes == 0) return 0;
+  if (bytes % 16 != 0 || off % 16 != 0) { set_last_error("ddls_comm_broadcast: 16-byte granularity required"); return 1; }
+  return launch(d, broadcast_kernel, pick_blocks(bytes / 4, blocks), COMM_THREADS, static_cast<cudaStream_t>(stream), c, off,
+                bytes / 16, root, use_multicast);
+}
+
+extern "C" int ddls_comm_allgather(const DdlsCommDesc* d, uint64_t in_off, uint64_t out_off, uint64_t chunk_bytes,
+                                   int blocks, void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  if (chunk_bytes == 0) return 0;
+  if (chunk_bytes % 16 != 0 || (in_off | out_off) % 16 != 0) { set_last_error("ddls_comm_allgather: 16-byte granularity required"); return 1; }
+  return launch(d, allgather_kernel, pick_blocks(chunk_bytes / 4, blocks), COMM_THREADS, static_cast<cudaStream_t>(stream),
+                c, in_off, out_off, chunk_bytes / 16);
+}
+
+extern "C" int ddls_comm_barrier(const DdlsCommDesc* d, void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  return launch(d, barrier_kernel, 1, 32, static_cast<cudaStream_t>(stream), c);
+}
+
+extern "C" int ddls_comm_adag_commit(const DdlsCommDesc* d, float* w, float* pulled, uint64_t center_off,
+                                     uint64_t updates_off, uint64_t n, float scale, int staleness_aware,
+                                     unsigned* last_update, void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  if (n % 4 != 0) { set_last_error("ddls_comm_adag_commit: n must be a multiple of 4"); return 1; }
+  int nb = (int)((n / 4 + COMM_THREADS - 1) / COMM_THREADS);
+  if (nb > 148) nb = 148;
+  if (nb < 1) nb = 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  dim3 grid(nb, 1);
+  adag_commit_kernel<<<grid, COMM_THREADS, 0, st>>>(c, w, pulled, center_off, updates_off, n, scale, staleness_aware,
+                                                     last_update);
+  adag_pull_kernel<<<grid, COMM_THREADS, 0, st>>>(c, w, pulled, center_off, updates_off, n, last_update);
+  count_launch(2);
+  return check_cuda(cudaGetLastError(), "adag kernels launch");
+}

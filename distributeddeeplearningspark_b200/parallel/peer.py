@@ -1,0 +1,390 @@
+"""Peer-memory communicator: symmetric VMM heap + hand-written NVLink/NVSwitch collectives.
+
+``PeerMemoryComm`` is the product path for gradient allreduce / parameter broadcast on GPUs
+(``csrc/symm.cpp`` + ``csrc/comm.cu``).  Set-up per rank:
+
+1. ``cuMemCreate`` one physical heap, export a POSIX fd, map it locally;
+2. swap fds with every peer over Unix sockets (``SCM_RIGHTS`` — the ranks are separate processes
+   spawned by the Spark-style launcher, so there is no common CUDA parent to inherit from);
+3. map every peer's heap; if the fabric supports it, create/import one multicast object, add all
+   devices, bind every heap and map the multicast view (``multimem.*``);
+4. the first 4 KB of each heap hold the flag words and the epoch counter.
+
+Tensors handed out by ``alloc`` live in the heap at the same offset on every rank (allocation calls
+must be made in the same order on all ranks), so collectives address peers as ``base[r] + offset``.
+``torch.distributed`` is used only to bootstrap (socket paths, barriers, python objects).
+
+``EmulatedPeerGroup`` runs the same kernels for ``world`` emulated ranks on ONE GPU inside a single
+cooperative launch (blockIdx.y = rank) — used by the single-GPU tests; it never launches kernels that
+wait on each other separately.
+"""
+from __future__ import annotations
+
+import array
+import ctypes
+import os
+import socket
+import tempfile
+import time
+from typing import Dict, List, Optional, Tuple
+
+import torch
+import torch.distributed as dist
+
+from .. import _native as N
+from ..utils.misc import env_int, env_str
+from .comm import Average, Communicator, ReduceOp, Sum
+
+MAX_RANKS = 8
+CONTROL_BYTES = 4096
+FLAGS_OFF = 0
+SEQ_OFF = 2048
+ALIGN = 256
+
+AR_ONESHOT, AR_TWOSHOT, AR_NVLS = 0, 1, 2
+
+
+class CommDesc(ctypes.Structure):
+    _fields_ = [('base', ctypes.c_void_p * MAX_RANKS), ('mc_base', ctypes.c_void_p), ('world', ctypes.c_int),
+                ('rank', ctypes.c_int), ('emulate', ctypes.c_int), ('timeout_ms', ctypes.c_uint),
+                ('flags_off', ctypes.c_uint64), ('seq_off', ctypes.c_uint64)]
+
+
+P, I, U64, F = N.c_void_p, N.c_int, ctypes.c_uint64, N.c_float
+DP = ctypes.POINTER(CommDesc)
+N.register('ddls_multicast_supported', [I])
+N.register('ddls_symm_granularity', [I, I, ctypes.POINTER(ctypes.c_size_t)])
+N.register('ddls_symm_create', [I, N.c_size_t, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(P), ctypes.POINTER(I)])
+N.register('ddls_symm_import', [I, I, N.c_size_t, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(P)])
+N.register('ddls_symm_unmap', [P, N.c_size_t, ctypes.c_ulonglong])
+N.register('ddls_mc_create', [I, N.c_size_t, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(I)])
+N.register('ddls_mc_import', [I, ctypes.POINTER(ctypes.c_ulonglong)])
+N.register('ddls_mc_add_device', [ctypes.c_ulonglong, I])
+N.register('ddls_mc_bind_and_map', [ctypes.c_ulonglong, ctypes.c_ulonglong, N.c_size_t, I, ctypes.POINTER(P)])
+N.register('ddls_comm_allreduce', [DP, I, U64, U64, U64, U64, F, I, I, P])
+N.register('ddls_comm_broadcast', [DP, U64, U64, I, I, I, P])
+N.register('ddls_comm_allgather', [DP, U64, U64, U64, I, P])
+N.register('ddls_comm_barrier', [DP, P])
+N.register('ddls_comm_adag_commit', [DP, P, P, U64, U64, U64, F, I, P, P])
+
+
+class _RawBuffer:
+    """Exposes a raw device address range to torch through ``__cuda_array_interface__``."""
+
+    def __init__(self, ptr: int, nbytes: int, owner=None):
+        self.ptr, self.nbytes, self.owner = ptr, nbytes, owner
+        self.__cuda_array_interface__ = {'shape': (nbytes,), 'typestr': '|u1', 'data': (ptr, False), 'version': 3,
+                                         'strides': None}
+
+
+def _tensor_from_ptr(ptr: int, nbytes: int, dtype: torch.dtype, device: torch.device, owner=None) -> torch.Tensor:
+    raw = torch.as_tensor(_RawBuffer(ptr, nbytes, owner), device=device)
+    return raw.view(dtype)
+
+
+class _HeapBase:
+    """Bump allocator + collective launchers shared by the real and the emulated communicator."""
+
+    def _init_heap(self, heap_bytes: int):
+        self.heap_bytes = heap_bytes
+        self._top = CONTROL_BYTES
+        self._stage_off = 0
+        self._stage_elems = 0
+
+    def _alloc_off(self, nbytes: int) -> int:
+        off = (self._top + ALIGN - 1) // ALIGN * ALIGN
+        if off + nbytes > self.heap_bytes:
+            raise MemoryError(f'symmetric heap exhausted: need {nbytes} B at {off} of {self.heap_bytes} '
+                              f'(raise DDLS_HEAP_MB)')
+        self._top = off + nbytes
+        return off
+
+    def _ensure_stage(self, n_elems: int, world: int) -> int:
+        """Staging region for push collectives: [2 parities][world][n] fp32 slots."""
+        if n_elems > self._stage_elems:
+            want = max(n_elems, 1 << 20)
+            self._stage_off = self._alloc_off(2 * world * want * 4)
+            self._stage_elems = want
+        return self._stage_off
+
+    def select_algo(self, nbytes: int, symmetric_out: bool, have_mc: bool) -> int:
+        one_max = env_int('DDLS_ONESHOT_MAX_BYTES', 1 << 20)
+        forced = env_str('DDLS_ALLREDUCE_ALGO', '')
+        if forced:
+            return {'oneshot': AR_ONESHOT, 'twoshot': AR_TWOSHOT, 'nvls': AR_NVLS}[forced]
+        if nbytes <= one_max or not symmetric_out:
+            return AR_ONESHOT
+        return AR_NVLS if have_mc else AR_TWOSHOT
+
+
+class PeerMemoryComm(Communicator, _HeapBase):
+    name = 'peer-memory'
+
+    def __init__(self, rank: int, size: int, device: torch.device, local_rank: int, local_size: int):
+        Communicator.__init__(self, rank, size, device)
+        if size > MAX_RANKS:
+            raise RuntimeError(f'peer-memory communicator supports up to {MAX_RANKS} ranks on one NVSwitch domain')
+        if local_size != size:
+            raise RuntimeError('peer-memory communicator needs all ranks on one node')
+        self.lib = N.lib()
+        self.dev_index = device.index or 0
+        for peer in range(torch.cuda.device_count()):
+            if peer != self.dev_index and not torch.cuda.can_device_access_peer(self.dev_index, peer):
+                raise RuntimeError(f'GPU {self.dev_index} cannot access GPU {peer} peer-to-peer')
+        torch.cuda.set_device(device)
+        gran = ctypes.c_size_t(0)
+        N.call('ddls_symm_granularity', self.dev_index, size, ctypes.byref(gran))
+        want = env_int('DDLS_HEAP_MB', 768) << 20
+        heap_bytes = (want + gran.value - 1) // gran.value * gran.value
+        self._init_heap(heap_bytes)
+        # 1. my heap
+        h = ctypes.c_ulonglong(0); p = P(0); fd = I(-1)
+        N.call('ddls_symm_create', self.dev_index, heap_bytes, ctypes.byref(h), ctypes.byref(p), ctypes.byref(fd))
+        self._handles: List[int] = [0] * size
+        self._bases: List[int] = [0] * size
+        self._handles[rank], self._bases[rank] = h.value, p.value
+        # 2. swap fds
+        peer_fds = self._exchange_fds(fd.value, tag='heap')
+        os.close(fd.value)
+        # 3. map peers
+        for r, pfd in peer_fds.items():
+            hh = ctypes.c_ulonglong(0); pp = P(0)
+            N.call('ddls_symm_import', self.dev_index, pfd, heap_bytes, ctypes.byref(hh), ctypes.byref(pp))
+            os.close(pfd)
+            self._handles[r], self._bases[r] = hh.value, pp.value
+        # zero my control region before anyone signals
+        self._heap_u8 = _tensor_from_ptr(self._bases[rank], heap_bytes, torch.uint8, device, owner=self)
+        self._heap_u8[:CONTROL_BYTES].zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(device_ids=[self.dev_index])
+        # 4. multicast
+        self.mc_base = 0
+        self._mc_handle = 0
+        if env_int('DDLS_DISABLE_MULTICAST', 0) == 0 and self.lib.ddls_multicast_supported(self.dev_index):
+            try:
+                self._setup_multicast(heap_bytes)
+            except Exception as e:  # noqa: BLE001 - multicast is an optimisation, P2P paths remain
+                from ..utils.logging import get_logger
+                get_logger().warning('multicast set-up failed (%s); NVLS paths disabled', e)
+                self.mc_base = 0
+        self.desc = CommDesc()
+        for r in range(size):
+            self.desc.base[r] = self._bases[r]
+        self.desc.mc_base = self.mc_base or None
+        self.desc.world, self.desc.rank, self.desc.emulate = size, rank, 0
+        self.desc.timeout_ms = env_int('DDLS_COMM_TIMEOUT_MS', 20000)
+        self.desc.flags_off, self.desc.seq_off = FLAGS_OFF, SEQ_OFF
+        self._scratch_off = self._alloc_off(64 << 20)   # staging for tensors that are not heap-resident
+        self._scratch_bytes = 64 << 20
+        dist.barrier(device_ids=[self.dev_index])
+
+    # ------------------------------------------------------------------ fd exchange
+    def _exchange_fds(self, my_fd: int, tag: str, only_from: Optional[int] = None) -> Dict[int, int]:
+        """All-to-all (or one-to-all from ``only_from``) transfer of a file descriptor."""
+        tmpdir = tempfile.gettempdir()
+        token = [None]
+        if self.rank == 0:
+            token[0] = f'{os.getpid()}_{int(time.time() * 1e6) & 0xffffffff:x}'
+        dist.broadcast_object_list(token, src=0)
+        path = lambda r: os.path.join(tmpdir, f'ddls_{token[0]}_{tag}_{r}.sock')
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        try:
+            os.unlink(path(self.rank))
+        except FileNotFoundError:
+            pass
+        srv.bind(path(self.rank))
+        srv.listen(self.size)
+        dist.barrier(device_ids=[self.dev_index])
+        received: Dict[int, int] = {}
+        senders = [only_from] if only_from is not None else list(range(self.size))
+        # send my fd to every peer that expects it
+        if only_from is None or only_from == self.rank:
+            for r in range(self.size):
+                if r == self.rank:
+                    continue
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.connect(path(r))
+                socket.send_fds(c, [self.rank.to_bytes(4, 'little')], [my_fd])
+                c.close()
+        expect = sum(1 for s in senders if s != self.rank)
+        srv.settimeout(60.0)
+        for _ in range(expect):
+            conn, _ = srv.accept()
+            msg, fds, _, _ = socket.recv_fds(conn, 4, 1)
+            received[int.from_bytes(msg, 'little')] = fds[0]
+            conn.close()
+        dist.barrier(device_ids=[self.dev_index])
+        srv.close()
+        try:
+            os.unlink(path(self.rank))
+        except FileNotFoundError:
+            pass
+        return received
+
+    def _setup_multicast(self, heap_bytes: int) -> None:
+        mch = ctypes.c_ulonglong(0)
+        if self.rank == 0:
+            fd = I(-1)
+            N.call('ddls_mc_create', self.size, heap_bytes, ctypes.byref(mch), ctypes.byref(fd))
+            self._exchange_fds(fd.value, tag='mc', only_from=0)
+            os.close(fd.value)
+        else:
+            got = self._exchange_fds(-1, tag='mc', only_from=0)
+            N.call('ddls_mc_import', got[0], ctypes.byref(mch))
+            os.close(got[0])
+        N.call('ddls_mc_add_device', mch.value, self.dev_index)
+        dist.barrier(device_ids=[self.dev_index])       # every device joined before anyone binds
+        p = P(0)
+        N.call('ddls_mc_bind_and_map', mch.value, self._handles[self.rank], heap_bytes, self.dev_index, ctypes.byref(p))
+        dist.barrier(device_ids=[self.dev_index])
+        self._mc_handle, self.mc_base = mch.value, p.value
+
+    # ------------------------------------------------------------------ memory
+    def alloc(self, numel: int, dtype: torch.dtype = torch.float32) -> torch.Tensor:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        off = self._alloc_off(max(nbytes, 16))
+        t = self._heap_u8[off:off + nbytes].view(dtype)
+        t.zero_()
+        return t
+
+    def offset_of(self, t: torch.Tensor) -> Optional[int]:
+        a = t.data_ptr()
+        base = self._bases[self.rank]
+        if base <= a and a + t.numel() * t.element_size() <= base + self.heap_bytes:
+            return a - base
+        return None
+
+    # ------------------------------------------------------------------ collectives
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def allreduce_(self, t: torch.Tensor, op: ReduceOp = Average, prescale: float = 1.0, wire_bf16: bool = False,
+                   algo: Optional[int] = None) -> torch.Tensor:
+        if t.dtype != torch.float32:
+            tmp = t.float()
+            self.allreduce_(tmp, op, prescale, wire_bf16, algo)
+            t.copy_(tmp)
+            return t
+        n = t.numel()
+        scale = prescale * ((1.0 / self.size) if op is Average else 1.0)
+        off = self.offset_of(t) if (n % 4 == 0 and t.is_contiguous()) else None
+        if off is not None and off % 16 == 0:
+            a = algo if algo is not None else self.select_algo(n * 4, True, bool(self.mc_base))
+            stage = self._ensure_stage(n, self.size) if a != AR_NVLS else 0
+            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, n, scale, int(wire_bf16), 0,
+                   self._stream())
+            return t
+        # not heap-resident: bounce through the scratch region (chunked)
+        flat = t.reshape(-1)
+        cap = self._scratch_bytes // 4
+        scratch = self._heap_u8[self._scratch_off:self._scratch_off + self._scratch_bytes].view(torch.float32)
+        for lo in range(0, n, cap):
+            m = min(cap, n - lo)
+            m4 = (m + 3) // 4 * 4
+            scratch[:m].copy_(flat[lo:lo + m])
+            if m4 > m:
+                scratch[m:m4].zero_()
+            a = algo if algo is not None else self.select_algo(m4 * 4, True, bool(self.mc_base))
+            stage = self._ensure_stage(m4, self.size) if a != AR_NVLS else 0
+            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, self._scratch_off, self._scratch_off, stage, m4,
+                   scale, int(wire_bf16), 0, self._stream())
+            flat[lo:lo + m].copy_(scratch[:m])
+        return t
+
+    def allreduce_bf16_wire_(self, g: torch.Tensor, _w: torch.Tensor, op: ReduceOp = Average) -> torch.Tensor:
+        """fp32 gradients, bf16 on the wire, fp32 accumulate — the cast is fused into the collective."""
+        return self.allreduce_(g, op, wire_bf16=True)
+
+    def broadcast_(self, t: torch.Tensor, root: int = 0) -> torch.Tensor:
+        nbytes = t.numel() * t.element_size()
+        off = self.offset_of(t) if t.is_contiguous() else None
+        if off is not None and off % 16 == 0 and nbytes % 16 == 0:
+            N.call('ddls_comm_broadcast', ctypes.byref(self.desc), off, nbytes, root, 1, 0, self._stream())
+            return t
+        flat = t.contiguous().view(-1).view(torch.uint8) if t.is_contiguous() else t.contiguous().view(torch.uint8).view(-1)
+        scratch = self._heap_u8[self._scratch_off:self._scratch_off + self._scratch_bytes]
+        for lo in range(0, nbytes, self._scratch_bytes):
+            m = min(self._scratch_bytes, nbytes - lo)
+            m16 = (m + 15) // 16 * 16
+            if self.rank == root:
+                scratch[:m].copy_(flat[lo:lo + m])
+            N.call('ddls_comm_broadcast', ctypes.byref(self.desc), self._scratch_off, m16, root, 1, 0, self._stream())
+            if self.rank != root:
+                flat[lo:lo + m].copy_(scratch[:m])
+        if not t.is_contiguous():
+            t.copy_(flat.view(t.dtype).view(t.shape))
+        return t
+
+    def allgather(self, t: torch.Tensor) -> torch.Tensor:
+        t = t.contiguous()
+        nbytes = t.numel() * t.element_size()
+        chunk = (nbytes + 15) // 16 * 16
+        if chunk * (self.size + 1) > self._scratch_bytes:
+            out = [torch.empty_like(t) for _ in range(self.size)]
+            dist.all_gather(out, t)
+            return torch.stack(out)
+        scratch = self._heap_u8[self._scratch_off:self._scratch_off + self._scratch_bytes]
+        scratch[:nbytes].copy_(t.view(-1).view(torch.uint8))
+        out_off = self._scratch_off + chunk
+        N.call('ddls_comm_allgather', ctypes.byref(self.desc), self._scratch_off, out_off, chunk, 0, self._stream())
+        res = scratch[chunk:chunk + chunk * self.size].view(self.size, chunk)[:, :nbytes].clone()
+        return res.view(torch.uint8).reshape(self.size, nbytes).view(t.dtype).reshape((self.size,) + tuple(t.shape))
+
+    def barrier(self) -> None:
+        N.call('ddls_comm_barrier', ctypes.byref(self.desc), self._stream())
+
+    def allgather_object(self, obj):
+        out = [None] * self.size
+        dist.all_gather_object(out, obj)
+        return out
+
+    def broadcast_object(self, obj, root: int = 0):
+        box = [obj]
+        dist.broadcast_object_list(box, src=root)
+        return box[0]
+
+    def close(self) -> None:
+        try:
+            torch.cuda.synchronize(self.device)
+        except Exception:
+            pass
+
+
+class EmulatedPeerGroup(_HeapBase):
+    """``world`` emulated ranks on one GPU: one plain device buffer per rank plays the heap, and every
+    collective is a single cooperative launch whose blockIdx.y enumerates the ranks."""
+
+    def __init__(self, world: int, device: torch.device, heap_bytes: int = 64 << 20, timeout_ms: int = 5000):
+        self.world, self.device = world, torch.device(device)
+        self._init_heap(heap_bytes)
+        self.heaps = [torch.zeros(heap_bytes, dtype=torch.uint8, device=self.device) for _ in range(world)]
+        self.desc = CommDesc()
+        for r in range(world):
+            self.desc.base[r] = self.heaps[r].data_ptr()
+        self.desc.mc_base = None
+        self.desc.world, self.desc.rank, self.desc.emulate = world, 0, 1
+        self.desc.timeout_ms = timeout_ms
+        self.desc.flags_off, self.desc.seq_off = FLAGS_OFF, SEQ_OFF
+        N.lib()
+
+    def alloc(self, numel: int, dtype=torch.float32) -> Tuple[int, List[torch.Tensor]]:
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        off = self._alloc_off(max(nbytes, 16))
+        return off, [h[off:off + nbytes].view(dtype) for h in self.heaps]
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def allreduce(self, off: int, n: int, algo: int, scale: float = 1.0, wire_bf16: bool = False, blocks: int = 0):
+        stage = self._ensure_stage(n, self.world)
+        N.call('ddls_comm_allreduce', ctypes.byref(self.desc), algo, off, off, stage, n, scale, int(wire_bf16), blocks,
+               self._stream())
+
+    def broadcast(self, off: int, nbytes: int, root: int, blocks: int = 0):
+        N.call('ddls_comm_broadcast', ctypes.byref(self.desc), off, nbytes, root, 0, blocks, self._stream())
+
+    def allgather(self, in_off: int, out_off: int, chunk_bytes: int, blocks: int = 0):
+        N.call('ddls_comm_allgather', ctypes.byref(self.desc), in_off, out_off, chunk_bytes, blocks, self._stream())
+
+    def barrier(self):
+        N.call('ddls_comm_barrier', ctypes.byref(self.desc), self._stream())

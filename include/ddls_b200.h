@@ -108,6 +108,49 @@ int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void*
 int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_db1, void* scratch, size_t scratch_bytes, int B,
                          void* stream);
 
+/* ---- symmetric peer-memory heap (CUDA VMM + optional NVSwitch multicast) -------------------------------
+ * Replaces dist-keras' pickle-over-TCP parameter exchange.  File descriptors returned
+ * here are passed between ranks by the caller (SCM_RIGHTS over a Unix socket). */
+int ddls_multicast_supported(int device);
+int ddls_symm_granularity(int device, int world, size_t* out);
+int ddls_symm_create(int device, size_t size, unsigned long long* handle_out, void** ptr_out, int* fd_out);
+int ddls_symm_import(int device, int fd, size_t size, unsigned long long* handle_out, void** ptr_out);
+int ddls_symm_unmap(void* ptr, size_t size, unsigned long long handle);
+int ddls_mc_create(int world, size_t size, unsigned long long* mc_handle_out, int* fd_out);
+int ddls_mc_import(int fd, unsigned long long* mc_handle_out);
+int ddls_mc_add_device(unsigned long long mc_handle, int device);
+int ddls_mc_bind_and_map(unsigned long long mc_handle, unsigned long long mem_handle, size_t size, int device,
+                         void** mc_ptr_out);
+
+/* ---- peer-memory collectives (one kernel each; offsets are symmetric offsets into the heaps) ---------- */
+#define DDLS_MAX_RANKS 8
+#define DDLS_COMM_MAX_BLOCKS 64
+#define DDLS_COMM_CONTROL_BYTES 4096 /* flags [64][8] u32 at offset 0, epoch counter at 2048 */
+typedef struct {
+  void* base[DDLS_MAX_RANKS]; /* this process' mappings of every rank's heap */
+  void* mc_base;              /* multicast mapping or NULL */
+  int world;
+  int rank;
+  int emulate;                /* 1: all ranks live on this device; one cooperative launch covers them */
+  unsigned timeout_ms;        /* flag-wait timeout (0 = 20 s); on expiry the kernel prints and traps */
+  uint64_t flags_off;
+  uint64_t seq_off;
+} DdlsCommDesc;
+enum { DDLS_AR_ONESHOT = 0, DDLS_AR_TWOSHOT = 1, DDLS_AR_NVLS = 2 };
+/* out = scale * sum_ranks(in) over fp32 [n].  stage_off: 2*world*n wire elements of scratch in each heap.
+ * wire_bf16: values cross NVLink as bf16 (fp32 accumulate).  blocks = 0 picks by size. */
+int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64_t out_off, uint64_t stage_off,
+                        uint64_t n, float scale, int wire_bf16, int blocks, void* stream);
+int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast, int blocks,
+                        void* stream);
+int ddls_comm_allgather(const DdlsCommDesc* d, uint64_t in_off, uint64_t out_off, uint64_t chunk_bytes, int blocks,
+                        void* stream);
+int ddls_comm_barrier(const DdlsCommDesc* d, void* stream);
+/* ADAG/DynSGD commit+pull against a center variable replicated at center_off in every heap
+ * (dist-keras ADAGWorker/ADAGParameterServer, /root/reference/ddl_mnist_aztk.py:216-219 via SURVEY.md E5/E6). */
+int ddls_comm_adag_commit(const DdlsCommDesc* d, float* w, float* pulled, uint64_t center_off, uint64_t updates_off,
+                          uint64_t n, float scale, int staleness_aware, unsigned* last_update, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,156 @@
+"""Peer-memory collectives.  Single-GPU tests emulate the ranks inside ONE cooperative launch
+(never as separate launches that wait on each other); multi-GPU tests run one process per GPU."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from distributeddeeplearningspark_b200.parallel.peer import AR_ONESHOT, AR_TWOSHOT, EmulatedPeerGroup
+
+
+@pytest.mark.parametrize('world', [2, 4, 8])
+@pytest.mark.parametrize('algo', [AR_ONESHOT, AR_TWOSHOT])
+@pytest.mark.parametrize('n,blocks', [(4, 1), (1000, 1), (66688, 0), (1048576 + 12, 0), (300000, 7)])
+def test_emulated_allreduce_matches_fp64_sum(world, algo, n, blocks):
+    dev = torch.device('cuda', 0)
+    g = EmulatedPeerGroup(world, dev, heap_bytes=(2 * world + 2) * max(n, 1 << 20) * 4 + (1 << 20))
+    off, bufs = g.alloc(n)
+    torch.manual_seed(n + world)
+    src = [torch.randn(n, device=dev) for _ in range(world)]
+    for b, s in zip(bufs, src):
+        b.copy_(s)
+    g.allreduce(off, n, algo, scale=1.0 / world, blocks=blocks)
+    torch.cuda.synchronize()
+    ref = (torch.stack(src).double().sum(0) / world).float()
+    for r in range(world):
+        torch.testing.assert_close(bufs[r], ref, rtol=1e-5, atol=1e-6)
+    for r in range(1, world):                       # rank-ordered summation => bit-identical replicas
+        assert torch.equal(bufs[0], bufs[r])
+
+
+def test_emulated_allreduce_bf16_wire_and_back_to_back_calls():
+    dev = torch.device('cuda', 0)
+    world, n = 4, 50000
+    g = EmulatedPeerGroup(world, dev)
+    off, bufs = g.alloc(n)
+    off2, bufs2 = g.alloc(4096)
+    torch.manual_seed(0)
+    for it in range(60):                            # alternating sizes/algorithms reuse flags and staging parity
+        src = [torch.randn(n, device=dev) for _ in range(world)]
+        for b, s in zip(bufs, src):
+            b.copy_(s)
+        algo = AR_ONESHOT if it % 3 else AR_TWOSHOT
+        g.allreduce(off, n, algo, scale=1.0, wire_bf16=(it % 2 == 0))
+        small = [torch.full((4096,), float(r + it), device=dev) for r in range(world)]
+        for b, s in zip(bufs2, small):
+            b.copy_(s)
+        g.allreduce(off2, 4096, AR_ONESHOT, scale=1.0)
+        torch.cuda.synchronize()
+        if it % 2 == 0:
+            ref = torch.stack([s.bfloat16().float() for s in src]).sum(0)
+            tol = dict(rtol=1e-5, atol=1e-5)
+        else:
+            ref = torch.stack(src).sum(0)
+            tol = dict(rtol=1e-5, atol=1e-5)
+        torch.testing.assert_close(bufs[1], ref, **tol)
+        assert torch.equal(bufs[0], bufs[3])
+        assert float(bufs2[2][0]) == sum(r + it for r in range(world))
+
+
+@pytest.mark.parametrize('world', [2, 8])
+def test_emulated_broadcast_every_root_and_allgather(world):
+    dev = torch.device('cuda', 0)
+    g = EmulatedPeerGroup(world, dev)
+    n = 70000
+    off, bufs = g.alloc(n)
+    for root in range(world):
+        for r, b in enumerate(bufs):
+            b.fill_(float(r + 1 + 10 * root))
+        g.broadcast(off, n * 4, root)
+        torch.cuda.synchronize()
+        for b in bufs:
+            assert float(b.min()) == float(b.max()) == float(root + 1 + 10 * root)
+    chunk = 4096
+    in_off, ins = g.alloc(chunk // 4)
+    out_off, outs = g.alloc(chunk // 4 * world)
+    for r, b in enumerate(ins):
+        b.fill_(float(r))
+    g.allgather(in_off, out_off, chunk)
+    g.barrier()
+    torch.cuda.synchronize()
+    ref = torch.arange(world, device=dev, dtype=torch.float32).repeat_interleave(chunk // 4)
+    for o in outs:
+        assert torch.equal(o, ref)
+
+
+# --------------------------------------------------------------------------------------------------------
+# real multi-process, multi-GPU
+# --------------------------------------------------------------------------------------------------------
+def _multi_rank_checks():
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, PeerMemoryComm
+    ddls.init()
+    r, n = ddls.rank(), ddls.size()
+    comm = ddls.runtime.communicator()
+    assert isinstance(comm, PeerMemoryComm), type(comm)
+    dev = ddls.device()
+    res = {'rank': r, 'mc': bool(comm.mc_base)}
+    algos = [AR_ONESHOT, AR_TWOSHOT] + ([AR_NVLS] if comm.mc_base else [])
+    for numel in (4, 66688, 1048576, 12 * 1048576):
+        t = comm.alloc(numel)
+        for algo in algos:
+            torch.manual_seed(100 + r)
+            t.copy_(torch.randn(numel, device=dev))
+            mine = t.clone()
+            comm.allreduce_(t, ddls.Sum, algo=algo)
+            gathered = [torch.empty_like(mine) for _ in range(n)]
+            import torch.distributed as dist
+            dist.all_gather(gathered, mine)
+            ref = torch.stack(gathered).double().sum(0).float()
+            err = float((t - ref).abs().max())
+            assert err < 1e-4 * max(1.0, float(ref.abs().max())), (numel, algo, err)
+            chk = [torch.empty_like(t) for _ in range(n)]
+            dist.all_gather(chk, t)
+            assert all(torch.equal(chk[0], c) for c in chk), ('replicas differ', numel, algo)
+    # non-heap tensor path + average + odd size
+    x = torch.full((1001,), float(r + 1), device=dev)
+    ddls.allreduce_(x)
+    assert abs(float(x[0]) - (n + 1) / 2.0) < 1e-6
+    # broadcast from every root (heap and non-heap tensors)
+    for root in range(n):
+        b = comm.alloc(4096); b.fill_(float(r))
+        comm.broadcast_(b, root)
+        assert float(b.min()) == float(b.max()) == float(root)
+        y = torch.full((777,), float(r), device=dev)
+        ddls.broadcast_(y, root)
+        assert float(y.max()) == float(root) == float(y.min())
+    g = ddls.allgather(torch.tensor([[float(r), 2.0 * r]], device=dev))
+    assert g.tolist() == [[float(i), 2.0 * i] for i in range(n)]
+    # synchronous training: identical weights on every rank after a few steps
+    model = ddls.models.nyiso_lstm(seed=r).to(dev)
+    opt = ddls.optim.KerasAdam(model.parameters(), comm=comm)
+    ddls.broadcast_parameters(opt, 0)
+    dopt = ddls.DistributedOptimizer(opt)
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    eng = StepEngine(model, optimizer=dopt, loss='mean_squared_error', device=dev, use_cuda_graph=True)
+    torch.manual_seed(r)
+    for _ in range(8):
+        eng.step(torch.rand(32, 25, 1, device=dev), torch.rand(32, 1, device=dev))
+    w = opt.flat.flat_params.clone()
+    ws = [torch.empty_like(w) for _ in range(n)]
+    import torch.distributed as dist
+    dist.all_gather(ws, w)
+    res['weights_equal'] = all(torch.equal(ws[0], v) for v in ws)
+    res['graph'] = eng._graph is not None
+    torch.cuda.synchronize()
+    return res
+
+
+@pytest.mark.multigpu
+def test_peer_memory_comm_multi_gpu():
+    from distributeddeeplearningspark_b200 import spark
+    from distributeddeeplearningspark_b200.spark import LocalBarrierBackend
+    n = min(torch.cuda.device_count(), 8)
+    out = spark.run(_multi_rank_checks, num_proc=n, backend=LocalBarrierBackend(timeout=600))
+    assert [o['rank'] for o in out] == list(range(n))
+    assert all(o['weights_equal'] for o in out) and all(o['graph'] for o in out)
