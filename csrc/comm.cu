@@ -360,6 +360,7 @@ static int make_ctx(const DdlsCommDesc* d, CommCtx* c) {
 
 template <typename... Args>
 static int launch(const DdlsCommDesc* d, void (*kern)(Args...), int blocks, int threads, cudaStream_t st, Args... args) {
+  if (d->emulate && blocks * d->world > 128) blocks = 128 / d->world;   // all emulated blocks must be co-resident
   dim3 grid(blocks, d->emulate ? d->world : 1);
   if (d->emulate) {
     // emulated ranks spin on each other: all blocks must be co-resident => cooperative launch

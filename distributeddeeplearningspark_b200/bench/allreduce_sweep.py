@@ -1,0 +1,86 @@
+"""Allreduce latency / bandwidth sweep, 4 KB .. 256 MB: this library's one-shot / two-shot / NVLS kernels vs NCCL.
+
+    python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 --master-port 29533 \
+        -m distributeddeeplearningspark_b200.bench.allreduce_sweep [--max-mb 256] [--out gpurun_out/sweep.json]
+
+BASELINE.json config 5.  Every number is device-timed with CUDA events on the launching stream and is
+the MAX over ranks; buffers are warm; each size is timed as the mean of ``iters`` back-to-back calls.
+Roofline per algorithm (link = 770 GB/s measured per direction per GPU, B200_PROFILING.md):
+one-shot moves (N-1)·S in per rank, two-shot 2(N-1)/N·S, NVLS ≈ S.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+
+import torch
+import torch.distributed as dist
+
+LINK_GBS = 770.0
+
+
+def _time(fn, iters, dev):
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(3):
+        fn()
+    torch.cuda.synchronize(dev)
+    dist.barrier(device_ids=[dev.index])
+    a.record()
+    for _ in range(iters):
+        fn()
+    b.record()
+    torch.cuda.synchronize(dev)
+    t = torch.tensor([a.elapsed_time(b) / iters * 1e3], device=dev)   # us
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--max-mb', type=int, default=256)
+    ap.add_argument('--out', default=None)
+    ap.add_argument('--graph', action='store_true', help='also time inside a CUDA graph (8 calls per replay)')
+    args = ap.parse_args()
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, PeerMemoryComm
+    os.environ.setdefault('DDLS_HEAP_MB', str(max(768, 20 * args.max_mb)))
+    ddls.init()
+    comm = ddls.runtime.communicator()
+    assert isinstance(comm, PeerMemoryComm), f'peer-memory communicator unavailable: {type(comm).__name__}'
+    r, n, dev = ddls.rank(), ddls.size(), ddls.device()
+    sizes = []
+    s = 4 << 10
+    while s <= args.max_mb << 20:
+        sizes.append(s); s *= 4
+    buf = comm.alloc((args.max_mb << 20) // 4)
+    nccl_buf = torch.empty((args.max_mb << 20) // 4, device=dev)
+    rows = []
+    for nbytes in sizes:
+        numel = nbytes // 4
+        t, tn = buf[:numel], nccl_buf[:numel]
+        iters = 200 if nbytes <= (1 << 20) else (50 if nbytes <= (32 << 20) else 10)
+        row = {'bytes': nbytes, 'nccl_us': _time(lambda: dist.all_reduce(tn), iters, dev)}
+        algos = [('oneshot', AR_ONESHOT), ('twoshot', AR_TWOSHOT)] + ([('nvls', AR_NVLS)] if comm.mc_base else [])
+        for name, a in algos:
+            if name == 'oneshot' and nbytes > (16 << 20):
+                continue
+            us = _time(lambda: comm.allreduce_(t, ddls.Sum, algo=a), iters, dev)
+            link_bytes = {'oneshot': (n - 1) * nbytes, 'twoshot': 2 * (n - 1) / n * nbytes, 'nvls': nbytes}[name]
+            row[name + '_us'] = us
+            row[name + '_roofline_frac'] = (link_bytes / (LINK_GBS * 1e3)) / us      # t_link / t_measured
+        best = min((row[k], k) for k in row if k.endswith('_us') and k != 'nccl_us')
+        row['best'] = best[1][:-3]; row['speedup_vs_nccl'] = row['nccl_us'] / best[0]
+        row['busbw_gbs_best'] = 2 * (n - 1) / n * nbytes / best[0] / 1e3
+        rows.append(row)
+        if r == 0:
+            print(json.dumps(row), flush=True)
+    if r == 0 and args.out:
+        os.makedirs(os.path.dirname(args.out) or '.', exist_ok=True)
+        with open(args.out, 'w') as f:
+            json.dump({'n_gpus': n, 'multicast': bool(comm.mc_base), 'link_gbs': LINK_GBS, 'rows': rows}, f, indent=1)
+    ddls.shutdown()
+
+
+if __name__ == '__main__':
+    main()
