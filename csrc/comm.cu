@@ -126,6 +126,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_kernel(CommCtx
   const uint64_t parity_vecs = slot_vecs * c.world;
   const uint64_t par = (e0 >> 1) & 1u;
   // push my slice to every peer's staging slot [parity][rank]
+#pragma unroll 4
   for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
     const float4 x = in[i];
     const float xv[4] = {x.x, x.y, x.z, x.w};
@@ -139,9 +140,11 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_kernel(CommCtx
   peer_barrier(c, rank, blockIdx.x, epoch);
   const V* stage = reinterpret_cast<const V*>(c.base[rank] + p.stage_off) + par * parity_vecs;
   float4* out = reinterpret_cast<float4*>(c.base[rank] + p.out_off);
+#pragma unroll 2
   for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     const float4 mine = in[i];
+#pragma unroll 8
     for (int r = 0; r < c.world; ++r) {                   // fixed rank order => identical bits on every rank
       float v[4];
       if (r == rank) {
@@ -229,6 +232,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c,
   peer_barrier(c, rank, blockIdx.x, epoch);               // every rank's input is final
   const float* mc_in = reinterpret_cast<const float*>(c.mc_base + p.in_off);
   float* mc_out = reinterpret_cast<float*>(c.mc_base + p.out_off);
+#pragma unroll 4
   for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
     float4 v = multimem_ld_reduce_f32x4(mc_in + 4 * i);
     v.x *= p.scale; v.y *= p.scale; v.z *= p.scale; v.w *= p.scale;
@@ -376,7 +380,7 @@ static int launch(const DdlsCommDesc* d, void (*kern)(Args...), int blocks, int 
 static int pick_blocks(uint64_t n, int requested) {
   if (requested > 0) return requested > MAX_CHANNELS ? MAX_CHANNELS : requested;
   const uint64_t bytes = n * 4;
-  int b = (int)((bytes + (128 << 10) - 1) / (128 << 10));   // ~128 KB of payload per block
+  int b = (int)((bytes + (32 << 10) - 1) / (32 << 10));     // ~32 KB of payload per block (4 x 16 B per thread)
   if (b < 1) b = 1;
   if (b > MAX_CHANNELS) b = MAX_CHANNELS;
   return b;

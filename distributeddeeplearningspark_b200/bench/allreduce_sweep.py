@@ -36,6 +36,33 @@ def _time(fn, iters, dev):
     return float(t.item())
 
 
+def _time_graph(fn, dev, calls=16, replays=20):
+    """Device time per call with host launch overhead removed: `calls` collectives per captured graph."""
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(side):
+        fn()
+    torch.cuda.current_stream(dev).wait_stream(side)
+    torch.cuda.synchronize(dev)
+    dist.barrier(device_ids=[dev.index])
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        for _ in range(calls):
+            fn()
+    g.replay()
+    torch.cuda.synchronize(dev)
+    dist.barrier(device_ids=[dev.index])
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for _ in range(replays):
+        g.replay()
+    b.record()
+    torch.cuda.synchronize(dev)
+    t = torch.tensor([a.elapsed_time(b) / (replays * calls) * 1e3], device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--max-mb', type=int, default=256)
@@ -68,8 +95,15 @@ def main():
             us = _time(lambda: comm.allreduce_(t, ddls.Sum, algo=a), iters, dev)
             link_bytes = {'oneshot': (n - 1) * nbytes, 'twoshot': 2 * (n - 1) / n * nbytes, 'nvls': nbytes}[name]
             row[name + '_us'] = us
+            if args.graph and nbytes <= (4 << 20):
+                row[name + '_graph_us'] = _time_graph(lambda: comm.allreduce_(t, ddls.Sum, algo=a), dev)
             row[name + '_roofline_frac'] = (link_bytes / (LINK_GBS * 1e3)) / us      # t_link / t_measured
-        best = min((row[k], k) for k in row if k.endswith('_us') and k != 'nccl_us')
+        if args.graph and nbytes <= (4 << 20):
+            try:
+                row['nccl_graph_us'] = _time_graph(lambda: dist.all_reduce(tn), dev)
+            except Exception as e:  # noqa: BLE001
+                row['nccl_graph_us'] = None
+        best = min((row[k], k) for k in row if k.endswith('_us') and not k.startswith('nccl') and 'graph' not in k)
         row['best'] = best[1][:-3]; row['speedup_vs_nccl'] = row['nccl_us'] / best[0]
         row['busbw_gbs_best'] = 2 * (n - 1) / n * nbytes / best[0] / 1e3
         rows.append(row)
