@@ -568,3 +568,60 @@ extern "C" int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_
   count_launch(2);
   return check_cuda(cudaGetLastError(), "conv1_wgrad launch");
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of ddls_cnn_conv1_wgrad.
+//
+// ddls_cnn_conv1_wgrad needs B*320 floats of scratch that the caller must provide, which in practice
+// means the caller (or PyTorch's caching allocator on its behalf) has called cudaMalloc at some point.
+// Some users of this C ABI cannot do that: a host program that was handed a fixed slice of GPU memory by
+// a resource manager (several Spark tasks sharing one B200) and must not grow its footprint at run time;
+// a latency-critical loop that cannot afford the device-wide synchronisation cudaMalloc/cudaFree imply
+// while copy and collective streams are in flight; a plain C caller without any allocator of its own.
+// For them the scratch lives in the file-scope device array below, reserved when the library is loaded:
+// every GPU that loads the library holds these 1.25 MiB until the process exits, whether or not the
+// entry point is ever called.  The price is a batch limit (DDLS_NOALLOC_CONV1_MAX_BATCH images).
+//
+// The array name is only a host-side stand-in for the symbol, not a device address, so the entry point
+// resolves the address once per device with cudaGetSymbolAddress (with that device current) on its first
+// call there and hands the resolved pointer to the kernels.  Make that first call on each device before
+// starting any stream capture on it.  The entry point itself calls no cudaMalloc/cudaFree or any other
+// allocating routine.  All calls on a device share the one array and it keeps whatever the last call left
+// in it: every element the reduction reads is rewritten by the producer kernel of the same call, so nothing
+// has to be cleared, but two calls whose kernels overlap on the GPU (different streams, no dependency)
+// race on it — order such calls yourself.
+// ------------------------------------------------------------------------------------------------
+namespace ddls {
+constexpr int NOALLOC_MAX_B = DDLS_NOALLOC_CONV1_MAX_BATCH;
+static __device__ __align__(256) float g_conv1_wgrad_scratch[(size_t)NOALLOC_MAX_B * 10 * CH];
+constexpr int NOALLOC_MAX_DEVICES = 64;
+static float* g_conv1_scratch_addr[NOALLOC_MAX_DEVICES] = {};
+}  // namespace ddls
+
+extern "C" int ddls_cnn_conv1_wgrad_noalloc(const float* x, const void* dz1, float* dw1_db1, int B, void* stream) {
+  if (B <= 0) return 0;
+  if (B > NOALLOC_MAX_B) {
+    set_last_error("ddls_cnn_conv1_wgrad_noalloc: batch %d exceeds the built-in scratch (max %d images); "
+                   "use ddls_cnn_conv1_wgrad with caller-provided scratch", B, NOALLOC_MAX_B);
+    return 1;
+  }
+  int dev = -1;
+  DDLS_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) {
+    set_last_error("ddls_cnn_conv1_wgrad_noalloc: device ordinal %d out of range", dev);
+    return 1;
+  }
+  if (g_conv1_scratch_addr[dev] == nullptr) {   // first call on this device: resolve the symbol's device address
+    float* p = nullptr;
+    DDLS_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_conv1_wgrad_scratch));
+    const int smem0 = C1 * C1 * CH * 2 + IMG * IMG * 4;
+    DDLS_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem0));
+    g_conv1_scratch_addr[dev] = p;
+  }
+  float* part = g_conv1_scratch_addr[dev];
+  const int smem = C1 * C1 * CH * 2 + IMG * IMG * 4;
+  conv1_wgrad_kernel<<<B, 320, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
+  sum_partials_kernel<<<(320 * 8 + 255) / 256, 256, 0, ST(stream)>>>(part, dw1_db1, 320, B);
+  count_launch(2);
+  return check_cuda(cudaGetLastError(), "conv1_wgrad (no-alloc) launch");
+}

@@ -107,6 +107,15 @@ int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void*
 /* conv1 gradients: dw1_db1 = [3*3*1*32 kernel gradient | 32 bias gradient] fp32; scratch B*320*4 bytes. */
 int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_db1, void* scratch, size_t scratch_bytes, int B,
                          void* stream);
+/* Same result as ddls_cnn_conv1_wgrad for callers that cannot allocate GPU memory (fixed memory budgets,
+ * loops that must not hit cudaMalloc's device-wide synchronisation, bare C callers): the scratch is a
+ * 1.25 MiB array built into the library, held by every GPU that loads it until exit.  B must be
+ * <= DDLS_NOALLOC_CONV1_MAX_BATCH, larger batches are rejected with an error.  The first call on a device
+ * resolves the array's address (cudaGetSymbolAddress) — make it before any stream capture on that device.
+ * Calls share the array: calls that overlap on the GPU race; it needs no clearing between calls.
+ * No counterpart in the reference (which has no native code and no notion of GPU scratch). */
+#define DDLS_NOALLOC_CONV1_MAX_BATCH 1024
+int ddls_cnn_conv1_wgrad_noalloc(const float* x, const void* dz1, float* dw1_db1, int B, void* stream);
 
 /* ---- symmetric peer-memory heap (CUDA VMM + optional NVSwitch multicast) -------------------------------
  * Replaces dist-keras' pickle-over-TCP parameter exchange.  File descriptors returned
