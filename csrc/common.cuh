@@ -247,3 +247,16 @@ DDLS_DEVINL void multimem_red_add_u32(uint32_t* mc_ptr, uint32_t v) {
 }
 
 }  // namespace ddls
+
+namespace ddls {
+// ---------------------------------------------------------------------------------------------
+// cp.async (LDGSTS): 16-byte global -> shared copies without register staging.  src_bytes < 16 zero-fills.
+// ---------------------------------------------------------------------------------------------
+DDLS_DEVINL void cp_async16(void* smem_dst, const void* gmem_src, uint32_t src_bytes) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src), "r"(src_bytes)
+               : "memory");
+}
+DDLS_DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+DDLS_DEVINL void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+}  // namespace ddls

@@ -16,6 +16,54 @@ static inline int ew_grid(size_t n_vec) {
   return static_cast<int>(b < 1 ? 1 : (b > cap ? cap : b));
 }
 
+// bf16 "shadow" copies of selected parameter matrices, refreshed by the same kernel that updates the fp32
+// masters (the fused cast of K12): tensor-core kernels then read 16-byte-aligned bf16 rows (ld padded to a
+// multiple of 8) instead of converting fp32 on every use.
+struct ShadowSet {
+  DdlsShadowSpec s[DDLS_MAX_SHADOWS];
+  int n;
+  unsigned long long lo, hi;   // union of the shadowed element ranges (cheap early-out)
+};
+
+DDLS_DEVINL void write_shadows(const ShadowSet& sh, size_t e0, const float (&v)[4]) {
+  if (sh.n == 0 || e0 + 4 <= sh.lo || e0 >= sh.hi) return;
+#pragma unroll 1
+  for (int k = 0; k < sh.n; ++k) {
+    const DdlsShadowSpec& sp = sh.s[k];
+    const size_t end = sp.begin + (size_t)sp.rows * sp.cols;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const size_t e = e0 + j;
+      if (e >= sp.begin && e < end) {
+        const size_t rel = e - sp.begin;
+        const uint32_t r = (uint32_t)(rel / sp.cols), c = (uint32_t)(rel - (size_t)r * sp.cols);
+        static_cast<__nv_bfloat16*>(sp.dst)[(size_t)r * sp.ld + c] = __float2bfloat16(v[j]);
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(EW_THREADS) refresh_shadows_kernel(const float4* __restrict__ p, size_t n4, ShadowSet sh) {
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+    if (4 * i + 4 <= sh.lo || 4 * i >= sh.hi) continue;
+    const float4 pi = p[i];
+    const float v[4] = {pi.x, pi.y, pi.z, pi.w};
+    write_shadows(sh, 4 * i, v);
+  }
+}
+
+static ShadowSet make_shadows(const DdlsShadowSpec* specs, int n) {
+  ShadowSet sh;
+  sh.n = 0; sh.lo = ~0ull; sh.hi = 0;
+  for (int k = 0; specs != nullptr && k < n && k < DDLS_MAX_SHADOWS; ++k) {
+    sh.s[sh.n++] = specs[k];
+    const unsigned long long b = specs[k].begin, e = b + (unsigned long long)specs[k].rows * specs[k].cols;
+    if (b < sh.lo) sh.lo = b;
+    if (e > sh.hi) sh.hi = e;
+  }
+  return sh;
+}
+
 // step[0] = completed steps, step[1] = arrival ticket.  Every block reads step[0] on entry; the last
 // block to finish publishes step[0]+1, so no block can observe the new value mid-kernel.
 DDLS_DEVINL void publish_step(int* step, int t) {
@@ -34,7 +82,7 @@ DDLS_DEVINL void publish_step(int* step, int t) {
 __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p, float4* __restrict__ g,
                                                           float4* __restrict__ m, float4* __restrict__ v, int* step,
                                                           size_t n4, float lr, float b1, float b2, float eps,
-                                                          float gs, int zero_grads) {
+                                                          float gs, int zero_grads, ShadowSet sh) {
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   const float lr_t = lr * sqrtf(1.0f - powf(b2, (float)t)) / (1.0f - powf(b1, (float)t));
   const float ob1 = 1.0f - b1, ob2 = 1.0f - b2;
@@ -48,13 +96,15 @@ __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p
     pi.z -= lr_t * mi.z / (sqrtf(vi.z) + eps); pi.w -= lr_t * mi.w / (sqrtf(vi.w) + eps);
     m[i] = mi; v[i] = vi; p[i] = pi;
     if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
+    write_shadows(sh, 4 * i, pv);
   }
   publish_step(step, t);
 }
 
 __global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict__ p, float4* __restrict__ g,
                                                              float4* __restrict__ a, int* step, size_t n4, float lr,
-                                                             float eps, float gs, int zero_grads) {
+                                                             float eps, float gs, int zero_grads, ShadowSet sh) {
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     float4 gi = g[i], ai = a[i], pi = p[i];
@@ -64,12 +114,14 @@ __global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict_
     pi.z -= lr * gi.z / (sqrtf(ai.z) + eps); pi.w -= lr * gi.w / (sqrtf(ai.w) + eps);
     a[i] = ai; p[i] = pi;
     if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
+    write_shadows(sh, 4 * i, pv);
   }
   publish_step(step, t);
 }
 
 __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, int* step,
-                                                         size_t n4, float lr, float gs, int zero_grads) {
+                                                         size_t n4, float lr, float gs, int zero_grads, ShadowSet sh) {
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   const float a = lr * gs;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -77,6 +129,8 @@ __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(float4* __restrict__ p,
     pi.x -= a * gi.x; pi.y -= a * gi.y; pi.z -= a * gi.z; pi.w -= a * gi.w;
     p[i] = pi;
     if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
+    write_shadows(sh, 4 * i, pv);
   }
   publish_step(step, t);
 }
@@ -117,33 +171,37 @@ static int check_flat(const void* a, size_t n, const char* who) {
 using namespace ddls;
 
 extern "C" int ddls_adam_step(float* params, float* grads, float* m, float* v, int* step, size_t n, float lr,
-                              float beta1, float beta2, float eps, float grad_scale, int zero_grads, void* stream) {
+                              float beta1, float beta2, float eps, float grad_scale, int zero_grads,
+                              const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
   if (n == 0) return 0;
   if (check_flat(params, n, "ddls_adam_step") || check_flat(grads, n, "ddls_adam_step")) return 1;
   adam_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(m),
-      reinterpret_cast<float4*>(v), step, n / 4, lr, beta1, beta2, eps, grad_scale, zero_grads);
+      reinterpret_cast<float4*>(v), step, n / 4, lr, beta1, beta2, eps, grad_scale, zero_grads,
+      make_shadows(shadows, n_shadows));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "adam_kernel launch");
 }
 
 extern "C" int ddls_adagrad_step(float* params, float* grads, float* acc, int* step, size_t n, float lr, float eps,
-                                 float grad_scale, int zero_grads, void* stream) {
+                                 float grad_scale, int zero_grads, const DdlsShadowSpec* shadows, int n_shadows,
+                                 void* stream) {
   if (n == 0) return 0;
   if (check_flat(params, n, "ddls_adagrad_step") || check_flat(grads, n, "ddls_adagrad_step")) return 1;
   adagrad_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
       reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(acc), step, n / 4,
-      lr, eps, grad_scale, zero_grads);
+      lr, eps, grad_scale, zero_grads, make_shadows(shadows, n_shadows));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "adagrad_kernel launch");
 }
 
 extern "C" int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, float grad_scale,
-                             int zero_grads, void* stream) {
+                             int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
   if (n == 0) return 0;
   if (check_flat(params, n, "ddls_sgd_step") || check_flat(grads, n, "ddls_sgd_step")) return 1;
   sgd_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
-      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), step, n / 4, lr, grad_scale, zero_grads);
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), step, n / 4, lr, grad_scale, zero_grads,
+      make_shadows(shadows, n_shadows));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "sgd_kernel launch");
 }
@@ -156,4 +214,14 @@ extern "C" int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* label
       pixels, labels, x, onehot, n, npix, classes, o_min, scale, n_min);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "mnist_preprocess_kernel launch");
+}
+
+extern "C" int ddls_refresh_shadows(const float* params, size_t n, const DdlsShadowSpec* shadows, int n_shadows,
+                                    void* stream) {
+  if (n == 0 || n_shadows <= 0) return 0;
+  if (check_flat(params, n, "ddls_refresh_shadows")) return 1;
+  refresh_shadows_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+      reinterpret_cast<const float4*>(params), n / 4, make_shadows(shadows, n_shadows));
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "refresh_shadows_kernel launch");
 }

@@ -2,8 +2,8 @@
 // the end of the graph (K5 / K11 of SURVEY.md §2.5).
 //   * Dense(H -> O, linear) + mean_squared_error   (/root/reference/ddl_nyiso_aztk.py:203,207,251,255)
 //   * Dense(F -> C) + softmax + categorical_crossentropy (/root/reference/ddl_mnist_aztk.py:191-196)
-// Each warp walks batch rows; per-lane weight-gradient partials stay in registers and are reduced with
-// one atomic per element at the end.  Scratch: none (outputs are accumulated into caller-zeroed buffers).
+// Both heads run as ONE CTA (the batches here are 32-1024 rows) and overwrite every output, so nothing has
+// to be zeroed beforehand and no atomics are used.
 #include "common.cuh"
 #include "../include/ddls_b200.h"
 
@@ -18,142 +18,181 @@ DDLS_DEVINL float warp_sum(float v) {
   return v;
 }
 
-// h [B,H] fp32, wd [H,O], bd [O], y [B,O] (may be null => inference: pred only)
-// zeroed by caller: loss[1], dwd [H,O], dbd [O].  H <= 32*4 per lane stride loop (any H).
-template <int O>
-__global__ void __launch_bounds__(HD_THREADS) dense_mse_kernel(const float* __restrict__ h, const float* __restrict__ wd,
-                                                               const float* __restrict__ bd, const float* __restrict__ y,
-                                                               float* __restrict__ pred, float* __restrict__ loss,
-                                                               float* __restrict__ dh, float* __restrict__ dwd,
-                                                               float* __restrict__ dbd, int B, int H) {
-  const int lane = threadIdx.x & 31;
-  const int warp_g = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int nwarps = (gridDim.x * blockDim.x) >> 5;
-  constexpr int MAXJ = 8;                 // supports H <= 256 per lane-strided loop
-  float w[MAXJ][O], gw[MAXJ][O];
+// Dense(F -> C) + softmax + categorical cross-entropy, forward AND backward, one CTA of 1024 threads.
+//   a [B,F] fp32 (the previous layer's output), w [F,C], bias [C], onehot [B,C] (null => probabilities only)
+// outputs (all overwritten, nothing needs zeroing):
+//   probs [B,C] (optional), loss[1], dw [F,C], db [C],
+//   da: gradient w.r.t. `a` — fp32 [B,F] (da_f32) or bf16 [B,ldz] zero-padded (da_bf16);
+//   with relu_input the ReLU of the previous layer is folded in: da *= (a > 0), and dprev_bias[f] = sum_b da.
+// Phase 1: one warp per row computes logits / softmax / d = (p - y)/B into shared memory.
+// Phase 2: thread (group g, feature f) walks rows b = g, g+4, ... with w[f][:] in registers, producing da,
+//          and accumulating dw[f][:] and dprev_bias[f]; the four groups are combined through shared memory.
+constexpr int XH_THREADS = 1024;
+constexpr int XH_MAXC = 16;
+__global__ void __launch_bounds__(XH_THREADS, 1) head_softmax_xent_kernel(
+    const float* __restrict__ a, const float* __restrict__ w, const float* __restrict__ bias,
+    const float* __restrict__ onehot, float* __restrict__ probs, float* __restrict__ loss, float* __restrict__ da_f32,
+    __nv_bfloat16* __restrict__ da_bf16, int ldz, float* __restrict__ dw, float* __restrict__ db,
+    float* __restrict__ dprev_bias, int B, int F, int C, int relu_input) {
+  extern __shared__ float sm[];
+  float* sw = sm;                               // [F][C]
+  float* sd = sw + F * C;                       // [B][C]   dL/dlogits
+  float* sacc = sd + B * C;                     // [4][F][C+1] group partials (dw | dprev_bias)
+  __shared__ float sloss[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < F * C; i += XH_THREADS) sw[i] = w[i];
+  __syncthreads();
+  const float invB = 1.0f / (float)B;
+  float lsum = 0.f;
+  for (int b = warp; b < B; b += XH_THREADS / 32) {
+    float z[XH_MAXC];
 #pragma unroll
-  for (int u = 0; u < MAXJ; ++u) {
-    const int j = lane + 32 * u;
+    for (int c = 0; c < XH_MAXC; ++c) z[c] = 0.f;
+    for (int f = lane; f < F; f += 32) {
+      const float av = a[(size_t)b * F + f];
 #pragma unroll
-    for (int o = 0; o < O; ++o) { w[u][o] = (j < H) ? wd[j * O + o] : 0.f; gw[u][o] = 0.f; }
+      for (int c = 0; c < XH_MAXC; ++c)
+        if (c < C) z[c] = fmaf(av, sw[f * C + c], z[c]);
+    }
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < XH_MAXC; ++c)
+      if (c < C) { z[c] = warp_sum(z[c]) + bias[c]; mx = fmaxf(mx, z[c]); }
+    float ssum = 0.f;
+#pragma unroll
+    for (int c = 0; c < XH_MAXC; ++c)
+      if (c < C) { z[c] = __expf(z[c] - mx); ssum += z[c]; }
+    const float inv = 1.0f / ssum;
+#pragma unroll
+    for (int c = 0; c < XH_MAXC; ++c) {
+      if (c < C) {
+        const float pr = z[c] * inv;
+        if (lane == c) {
+          if (probs != nullptr) probs[(size_t)b * C + c] = pr;
+          if (onehot != nullptr) {
+            const float yv = onehot[(size_t)b * C + c];
+            sd[b * C + c] = (pr - yv) * invB;
+            // Keras clips probabilities to [1e-7, 1-1e-7] inside the log
+            lsum += -yv * __logf(fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f)) * invB;
+          }
+        }
+      }
+    }
   }
-  float gb[O], lsum = 0.f;
+  if (onehot == nullptr) return;
+  lsum = warp_sum(lsum);
+  if (lane == 0) sloss[warp] = lsum;
+  __syncthreads();
+  if (warp == 0) {
+    float v = sloss[lane];
+    v = warp_sum(v);
+    if (lane == 0) loss[0] = v;
+  }
+  // ---- phase 2 ----
+  const int grp = tid >> 8, f = tid & 255;       // 4 groups x 256 feature slots
+  float wr[XH_MAXC], gw[XH_MAXC], gprev = 0.f;
 #pragma unroll
-  for (int o = 0; o < O; ++o) gb[o] = 0.f;
-  const float inv = 1.0f / ((float)B * (float)O);
-  for (int b = warp_g; b < B; b += nwarps) {
-    float hv[MAXJ], acc[O];
+  for (int c = 0; c < XH_MAXC; ++c) { wr[c] = (f < F && c < C) ? sw[f * C + c] : 0.f; gw[c] = 0.f; }
+  if (f < ldz || f < F) {
+    for (int b = grp; b < B; b += 4) {
+      float av = 0.f, g = 0.f;
+      if (f < F) {
+        av = a[(size_t)b * F + f];
 #pragma unroll
-    for (int o = 0; o < O; ++o) acc[o] = 0.f;
-#pragma unroll
-    for (int u = 0; u < MAXJ; ++u) {
-      const int j = lane + 32 * u;
-      hv[u] = (j < H) ? h[(size_t)b * H + j] : 0.f;
-#pragma unroll
-      for (int o = 0; o < O; ++o) acc[o] = fmaf(hv[u], w[u][o], acc[o]);
-    }
-    float d[O];
-#pragma unroll
-    for (int o = 0; o < O; ++o) {
-      const float pr = warp_sum(acc[o]) + bd[o];
-      if (lane == 0) pred[(size_t)b * O + o] = pr;
-      if (y != nullptr) {
-        const float e = pr - y[(size_t)b * O + o];
-        d[o] = 2.f * e * inv;
-        if (lane == 0) { lsum += e * e * inv; gb[o] += d[o]; }
-      } else {
-        d[o] = 0.f;
+        for (int c = 0; c < XH_MAXC; ++c)
+          if (c < C) { const float d = sd[b * C + c]; g = fmaf(d, wr[c], g); gw[c] = fmaf(av, d, gw[c]); }
+        if (relu_input && !(av > 0.f)) g = 0.f;
+        gprev += g;
+        if (da_f32 != nullptr) da_f32[(size_t)b * F + f] = g;
       }
-    }
-    if (y != nullptr) {
-#pragma unroll
-      for (int u = 0; u < MAXJ; ++u) {
-        const int j = lane + 32 * u;
-        float dhv = 0.f;
-#pragma unroll
-        for (int o = 0; o < O; ++o) { dhv = fmaf(d[o], w[u][o], dhv); gw[u][o] = fmaf(hv[u], d[o], gw[u][o]); }
-        if (j < H) dh[(size_t)b * H + j] = dhv;
-      }
+      if (da_bf16 != nullptr && f < ldz) da_bf16[(size_t)b * ldz + f] = __float2bfloat16(g);
     }
   }
-  if (y != nullptr) {
+  if (f < F) {
+    float* dst = sacc + ((size_t)grp * F + f) * (C + 1);
 #pragma unroll
-    for (int u = 0; u < MAXJ; ++u) {
-      const int j = lane + 32 * u;
-      if (j < H) {
-#pragma unroll
-        for (int o = 0; o < O; ++o) atomicAdd(dwd + j * O + o, gw[u][o]);
-      }
-    }
-    if (lane == 0) {
-#pragma unroll
-      for (int o = 0; o < O; ++o) atomicAdd(dbd + o, gb[o]);
-      atomicAdd(loss, lsum);
-    }
+    for (int c = 0; c < XH_MAXC; ++c)
+      if (c < C) dst[c] = gw[c];
+    dst[C] = gprev;
+  }
+  __syncthreads();
+  for (int i = tid; i < F * (C + 1); i += XH_THREADS) {
+    const float v = sacc[i] + sacc[F * (C + 1) + i] + sacc[2 * F * (C + 1) + i] + sacc[3 * F * (C + 1) + i];
+    const int ff = i / (C + 1), c = i - ff * (C + 1);
+    if (c < C) dw[ff * C + c] = v;
+    else if (dprev_bias != nullptr) dprev_bias[ff] = v;
+  }
+  if (tid < C) {
+    float v = 0.f;
+    for (int b = 0; b < B; ++b) v += sd[b * C + tid];
+    db[tid] = v;
   }
 }
 
-// Dense(F -> C) + softmax + categorical cross-entropy, forward and backward in one launch.
-// a [B,F] fp32, w [F,C], bias [C], onehot [B,C] (null => probabilities only).
-// zeroed by caller: loss[1], dw [F,C], db [C].  C <= 32; lane c owns class c; F walked in chunks.
-__global__ void __launch_bounds__(HD_THREADS) dense_softmax_xent_kernel(
-    const float* __restrict__ a, const float* __restrict__ w, const float* __restrict__ bias,
-    const float* __restrict__ onehot, float* __restrict__ probs, float* __restrict__ loss, float* __restrict__ da,
-    float* __restrict__ dw, float* __restrict__ db, int B, int F, int C) {
+// Dense(H -> O, linear) + MSE, forward AND backward, ONE CTA; every output is overwritten (no zeroing).
+//   h [B,H], wd [H,O], bd [O], y [B,O] (null => pred only); outputs pred [B,O], loss[1], dh [B,H], dwd [H,O], dbd [O]
+constexpr int MH_THREADS = 512;
+template <int O>
+__global__ void __launch_bounds__(MH_THREADS, 1) head_mse_kernel(const float* __restrict__ h, const float* __restrict__ wd,
+                                                                 const float* __restrict__ bd, const float* __restrict__ y,
+                                                                 float* __restrict__ pred, float* __restrict__ loss,
+                                                                 float* __restrict__ dh, float* __restrict__ dwd,
+                                                                 float* __restrict__ dbd, int B, int H) {
   extern __shared__ float sm[];
-  float* sw = sm;                         // [F][C] weights
-  float* sdw = sm + (size_t)F * C;        // [F][C] block-local weight-gradient accumulator
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  for (int i = threadIdx.x; i < F * C; i += blockDim.x) { sw[i] = w[i]; sdw[i] = 0.f; }
-  __syncthreads();
-  const float bc = (lane < C) ? bias[lane] : 0.f;
-  float gb = 0.f, lsum = 0.f;
-  const float invB = 1.0f / (float)B;
-  for (int b = blockIdx.x * nw + warp; b < B; b += gridDim.x * nw) {
-    const float* arow = a + (size_t)b * F;
-    // logits: lane c accumulates over f (weights from smem: bank = (f*C + c) % 32, conflict-free for odd strides)
-    float z = bc;
-    if (lane < C) {
-      for (int f = 0; f < F; ++f) z = fmaf(arow[f], sw[f * C + lane], z);
-    } else {
-      z = -INFINITY;
-    }
-    float mx = z;
+  float* sd = sm;                    // [B][O]  dL/dpred
+  __shared__ float sloss[MH_THREADS / 32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const float inv = 1.0f / ((float)B * (float)O);
+  float lsum = 0.f;
+  for (int b = warp; b < B; b += MH_THREADS / 32) {
+    float acc[O];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    const float e = (lane < C) ? __expf(z - mx) : 0.f;
-    const float s = warp_sum(e);
-    const float pr = e / s;
-    if (lane < C) probs[(size_t)b * C + lane] = pr;
-    if (onehot != nullptr) {
-      const float yv = (lane < C) ? onehot[(size_t)b * C + lane] : 0.f;
-      // Keras clips probabilities to [1e-7, 1-1e-7] inside the log
-      const float pl = fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f);
-      lsum += (lane < C) ? -yv * __logf(pl) * invB : 0.f;
-      const float d = (lane < C) ? (pr - yv) * invB : 0.f;     // dL/dz for softmax + xent
-      gb += d;
-      // da[f] = sum_c d_c * w[f][c]  (lanes stride over f; d broadcast by shuffle)
-      for (int f0 = 0; f0 < F; f0 += 32) {
-        const int f = f0 + lane;
-        float acc = 0.f;
-        for (int c = 0; c < C; ++c) {
-          const float dc = __shfl_sync(0xffffffffu, d, c);
-          if (f < F) acc = fmaf(dc, sw[f * C + c], acc);
+    for (int o = 0; o < O; ++o) acc[o] = 0.f;
+    for (int j = lane; j < H; j += 32) {
+      const float hv = h[(size_t)b * H + j];
+#pragma unroll
+      for (int o = 0; o < O; ++o) acc[o] = fmaf(hv, wd[j * O + o], acc[o]);
+    }
+#pragma unroll
+    for (int o = 0; o < O; ++o) {
+      const float pr = warp_sum(acc[o]) + bd[o];
+      if (lane == 0) {
+        pred[(size_t)b * O + o] = pr;
+        if (y != nullptr) {
+          const float e = pr - y[(size_t)b * O + o];
+          sd[b * O + o] = 2.f * e * inv;
+          lsum += e * e * inv;
         }
-        if (f < F) da[(size_t)b * F + f] = acc;
-      }
-      // dw[f][c] += a[f] * d_c : lane c walks f
-      if (lane < C) {
-        for (int f = 0; f < F; ++f) atomicAdd(&sdw[f * C + lane], arow[f] * d);
       }
     }
   }
-  if (onehot != nullptr) {
-    __syncthreads();
-    for (int i = threadIdx.x; i < F * C; i += blockDim.x) atomicAdd(dw + i, sdw[i]);
-    if (lane < C) atomicAdd(db + lane, gb);
-    lsum = warp_sum(lsum);
-    if (lane == 0) atomicAdd(loss, lsum);
+  if (y == nullptr) return;
+  if (lane == 0) sloss[warp] = lsum;
+  __syncthreads();
+  if (warp == 0) {
+    float v = (lane < MH_THREADS / 32) ? sloss[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) loss[0] = v;
+  }
+  // dh[b][j] = sum_o d[b][o] wd[j][o]
+  for (int i = tid; i < B * H; i += MH_THREADS) {
+    const int b = i / H, j = i - b * H;
+    float g = 0.f;
+#pragma unroll
+    for (int o = 0; o < O; ++o) g = fmaf(sd[b * O + o], wd[j * O + o], g);
+    dh[i] = g;
+  }
+  // dwd[j][o] = sum_b h[b][j] d[b][o]
+  for (int i = tid; i < H * O; i += MH_THREADS) {
+    const int j = i / O, o = i - j * O;
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g = fmaf(h[(size_t)b * H + j], sd[b * O + o], g);
+    dwd[i] = g;
+  }
+  if (tid < O) {
+    float g = 0.f;
+    for (int b = 0; b < B; ++b) g += sd[b * O + tid];
+    dbd[tid] = g;
   }
 }
 
@@ -164,34 +203,42 @@ using namespace ddls;
 extern "C" int ddls_dense_mse(const float* h, const float* wd, const float* bd, const float* y, float* pred,
                               float* loss, float* dh, float* dwd, float* dbd, int B, int H, int O, void* stream) {
   if (B <= 0) return 0;
-  if (H > 256 || O > HD_MAX_O || O < 1) { set_last_error("ddls_dense_mse: supports H <= 256 and 1 <= O <= 4 (got H=%d O=%d)", H, O); return 1; }
-  const int warps_per_block = HD_THREADS / 32;
-  int blocks = (B + warps_per_block - 1) / warps_per_block;
-  if (blocks > 148 * 2) blocks = 148 * 2;
+  if (O > HD_MAX_O || O < 1) { set_last_error("ddls_dense_mse: supports 1 <= O <= 4 (got O=%d)", O); return 1; }
+  const size_t smem = (size_t)B * O * sizeof(float);
+  if (smem > 160 * 1024) { set_last_error("ddls_dense_mse: batch %d too large for the single-CTA head", B); return 1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  switch (O) {
-    case 1: dense_mse_kernel<1><<<blocks, HD_THREADS, 0, st>>>(h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H); break;
-    case 2: dense_mse_kernel<2><<<blocks, HD_THREADS, 0, st>>>(h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H); break;
-    case 3: dense_mse_kernel<3><<<blocks, HD_THREADS, 0, st>>>(h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H); break;
-    default: dense_mse_kernel<4><<<blocks, HD_THREADS, 0, st>>>(h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H); break;
+#define DDLS_LAUNCH_MSE(OO)                                                                                         \
+  {                                                                                                                 \
+    if (smem > 48 * 1024)                                                                                           \
+      DDLS_CUDA_OK(cudaFuncSetAttribute(head_mse_kernel<OO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    head_mse_kernel<OO><<<1, MH_THREADS, smem, st>>>(h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H);                 \
   }
+  switch (O) {
+    case 1: DDLS_LAUNCH_MSE(1) break;
+    case 2: DDLS_LAUNCH_MSE(2) break;
+    case 3: DDLS_LAUNCH_MSE(3) break;
+    default: DDLS_LAUNCH_MSE(4) break;
+  }
+#undef DDLS_LAUNCH_MSE
   count_launch(1);
-  return check_cuda(cudaGetLastError(), "dense_mse_kernel launch");
+  return check_cuda(cudaGetLastError(), "head_mse_kernel launch");
 }
 
 extern "C" int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, const float* onehot,
-                                       float* probs, float* loss, float* da, float* dw, float* db, int B, int F, int C,
-                                       void* stream) {
+                                       float* probs, float* loss, float* da_f32, void* da_bf16, int ldz, float* dw,
+                                       float* db, float* dprev_bias, int B, int F, int C, int relu_input, void* stream) {
   if (B <= 0) return 0;
-  if (C > 32 || C < 1) { set_last_error("ddls_dense_softmax_xent: supports 1 <= C <= 32 (got %d)", C); return 1; }
-  const size_t smem = (size_t)F * C * 2 * sizeof(float);
-  if (smem > 200 * 1024) { set_last_error("ddls_dense_softmax_xent: F*C too large for shared memory"); return 1; }
-  DDLS_CUDA_OK(cudaFuncSetAttribute(dense_softmax_xent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int nw = HD_THREADS / 32;
-  int blocks = (B + nw - 1) / nw;
-  if (blocks > 148) blocks = 148;
-  dense_softmax_xent_kernel<<<blocks, HD_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
-      a, w, bias, onehot, probs, loss, da, dw, db, B, F, C);
+  if (C > XH_MAXC || C < 1 || F > 256) {
+    set_last_error("ddls_dense_softmax_xent: supports C <= 16 and F <= 256 (got C=%d F=%d)", C, F);
+    return 1;
+  }
+  if (da_bf16 != nullptr && ldz > 256) { set_last_error("ddls_dense_softmax_xent: ldz must be <= 256"); return 1; }
+  const size_t smem = ((size_t)F * C + (size_t)B * C + 4 * (size_t)F * (C + 1)) * sizeof(float);
+  if (smem > 200 * 1024) { set_last_error("ddls_dense_softmax_xent: batch %d too large for the single-CTA head", B); return 1; }
+  DDLS_CUDA_OK(cudaFuncSetAttribute(head_softmax_xent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  head_softmax_xent_kernel<<<1, XH_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
+      a, w, bias, onehot, probs, loss, da_f32, static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, B, F, C,
+      relu_input);
   count_launch(1);
-  return check_cuda(cudaGetLastError(), "dense_softmax_xent_kernel launch");
+  return check_cuda(cudaGetLastError(), "head_softmax_xent_kernel launch");
 }

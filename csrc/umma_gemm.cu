@@ -238,6 +238,172 @@ __global__ void __launch_bounds__(256) splitk_finish_kernel(const float* __restr
   }
 }
 
+// =================================================================================================
+// v2 mainloop: bf16 operands with 16-byte aligned rows are streamed with cp.async (LDGSTS) through a
+// 4-stage ring straight into the canonical layouts — three k-blocks of loads are always in flight, so the
+// loop is throughput- rather than latency-bound — and the epilogue transposes through shared memory so
+// global stores are coalesced along the output row.
+// =================================================================================================
+constexpr int V2_THREADS = 256;
+constexpr int V2_STAGES = 4;
+
+template <int ROWS>
+DDLS_DEVINL void cpasync_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int row0, int nrows, int k0, int kend) {
+  constexpr int KCH = GEMM_KC / 8;
+  for (int idx = threadIdx.x; idx < ROWS * KCH; idx += V2_THREADS) {
+    const int blk = idx >> 5, lane = idx & 31;
+    const int rblk = blk % (ROWS / 8), kblk = blk / (ROWS / 8);
+    const int r = rblk * 8 + (lane & 7), kc = kblk * 4 + (lane >> 3);
+    const int gr = row0 + r, gk = k0 + kc * 8;
+    const bool ok = gr < nrows && gk < kend;
+    const int valid = ok ? min(8, kend - gk) : 0;
+    cp_async16(smem + kc * (ROWS * 16) + r * 16, ok ? (const void*)(g + (size_t)gr * ld + gk) : (const void*)g, valid * 2);
+  }
+}
+template <int COLS>
+DDLS_DEVINL void cpasync_mnmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int col0, int ncols, int k0, int kend) {
+  constexpr int MNG = COLS / 8;
+  for (int idx = threadIdx.x; idx < GEMM_KC * MNG; idx += V2_THREADS) {
+    const int blk = idx >> 5, lane = idx & 31;
+    const int gblk = blk % (MNG / 4), kblk = blk / (MNG / 4);
+    const int mng = gblk * 4 + (lane >> 3), k = kblk * 8 + (lane & 7);
+    const int gk = k0 + k, gc = col0 + mng * 8;
+    const bool ok = gk < kend && gc < ncols;
+    const int valid = ok ? min(8, ncols - gc) : 0;
+    cp_async16(smem + (k >> 3) * (COLS * 16) + mng * 128 + (k & 7) * 16, ok ? (const void*)(g + (size_t)gk * ld + gc) : (const void*)g,
+               valid * 2);
+  }
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(V2_THREADS, 1) umma_gemm_v2_kernel(GemmParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int A_BYTES = GEMM_BM * GEMM_KC * 2, B_BYTES = BN * GEMM_KC * 2, STAGE = A_BYTES + B_BYTES;
+  __shared__ uint64_t mma_done[V2_STAGES];
+  __shared__ uint32_t tmem_base_s;
+  constexpr uint32_t TM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * GEMM_BM, n0 = blockIdx.y * BN;
+  const int kbeg = blockIdx.z * p.k_per_split, kend = min(p.K, kbeg + p.k_per_split);
+  const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(p.A);
+  const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(p.B);
+
+  if (warp == 0) tmem_alloc(&tmem_base_s, TM_COLS);
+  if (threadIdx.x == 32) {
+    for (int s = 0; s < V2_STAGES; ++s) mbar_init(&mma_done[s], 1);
+    mbar_fence_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_d = tmem_base_s;
+  constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
+  const int nkb = (kend - kbeg + GEMM_KC - 1) / GEMM_KC;
+
+  auto issue_loads = [&](int kb) {
+    uint8_t* sa = smem + (kb % V2_STAGES) * STAGE;
+    uint8_t* sb = sa + A_BYTES;
+    const int k0 = kbeg + kb * GEMM_KC;
+    if (A_MN) cpasync_mnmajor<GEMM_BM>(sa, A, p.lda, m0, p.M, k0, kend);
+    else      cpasync_kmajor<GEMM_BM>(sa, A, p.lda, m0, p.M, k0, kend);
+    if (B_MN) cpasync_mnmajor<BN>(sb, B, p.ldb, n0, p.N, k0, kend);
+    else      cpasync_kmajor<BN>(sb, B, p.ldb, n0, p.N, k0, kend);
+  };
+  // prologue: fill STAGES-1 slots (always commit so group accounting stays uniform)
+  for (int kb = 0; kb < V2_STAGES - 1; ++kb) {
+    if (kb < nkb) issue_loads(kb);
+    cp_async_commit();
+  }
+  uint32_t waits[V2_STAGES] = {};
+  for (int kb = 0; kb < nkb; ++kb) {
+    const int s = kb % V2_STAGES;
+    // refill the slot that k-block kb-1 used, once its MMAs have drained
+    const int nxt = kb + V2_STAGES - 1;
+    if (nxt < nkb) {
+      const int ns = nxt % V2_STAGES;
+      if (kb >= 1) { mbar_wait(&mma_done[ns], waits[ns] & 1); ++waits[ns]; }
+      issue_loads(nxt);
+    }
+    cp_async_commit();
+    cp_async_wait<V2_STAGES - 1>();       // k-block kb has landed (for this thread)
+    fence_proxy_async_smem();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      tc_fence_after();
+      const uint32_t a_base = smem_u32(smem + s * STAGE), b_base = a_base + A_BYTES;
+#pragma unroll
+      for (int ks = 0; ks < GEMM_KC / 16; ++ks)
+        umma_bf16(tmem_d, umma_desc(a_base + ks * 2 * (GEMM_BM * 16u), GEMM_BM * 16u, 128u),
+                  umma_desc(b_base + ks * 2 * (BN * 16u), BN * 16u, 128u), idesc, (kb | ks) != 0);
+      umma_commit(&mma_done[s]);
+    }
+  }
+  cp_async_wait<0>();
+  for (int s = 0; s < V2_STAGES; ++s) {
+    const uint32_t commits = nkb > s ? (nkb - s + V2_STAGES - 1) / V2_STAGES : 0;
+    while (waits[s] < commits) { mbar_wait(&mma_done[s], waits[s] & 1); ++waits[s]; }
+  }
+  tc_fence_after();
+  __syncthreads();    // every pipeline slot is idle: reuse it as the epilogue transpose buffer
+
+  // ---- epilogue: TMEM -> registers -> smem [128 rows][BN+1] fp32 chunks of 32 columns -> coalesced rows
+  const bool relu = p.flags & DDLS_GEMM_RELU, has_bias = (p.flags & DDLS_GEMM_BIAS);
+  const bool out_bf16 = p.flags & DDLS_GEMM_OUT_BF16, accum = p.flags & DDLS_GEMM_ATOMIC_ADD;
+  const bool to_ws = p.flags & DDLS_GEMM_SPLITK_WS;
+  float* sT = reinterpret_cast<float*>(smem);                  // [128][33] per 32-column chunk
+  const int q4 = warp & 3, half = warp >> 2;
+  for (int c0 = 0; c0 < BN; c0 += 32) {
+    if (n0 + c0 >= p.N) break;
+    uint32_t v[16];
+    tmem_ld16(tmem_d + (static_cast<uint32_t>(q4 * 32) << 16) + c0 + half * 16, v);
+    tmem_ld_wait();
+    const int r = q4 * 32 + lane;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) sT[r * 33 + half * 16 + j] = __uint_as_float(v[j]);
+    __syncthreads();
+    // 8 warps x 16 rows each; lane = column
+    for (int rr = warp * 16; rr < warp * 16 + 16; ++rr) {
+      const int row = m0 + rr, col = n0 + c0 + lane;
+      if (row < p.M && col < p.N) {
+        float x = sT[rr * 33 + lane];
+        if (to_ws) {
+          p.workspace[((size_t)blockIdx.z * p.M + row) * p.N + col] = x;
+        } else {
+          if (has_bias) x += p.bias[col];
+          if (relu) x = fmaxf(x, 0.f);
+          const size_t o = (size_t)row * p.ldc + col;
+          if (out_bf16) reinterpret_cast<__nv_bfloat16*>(p.C)[o] = __float2bfloat16(x);
+          else if (accum) reinterpret_cast<float*>(p.C)[o] += x;
+          else reinterpret_cast<float*>(p.C)[o] = x;
+        }
+      }
+    }
+    __syncthreads();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_d, TM_COLS);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm_v2(const GemmParams& p, int splits, cudaStream_t st) {
+  auto kern = umma_gemm_v2_kernel<BN, A_MN, B_MN>;
+  const int smem = V2_STAGES * (GEMM_BM * GEMM_KC * 2 + BN * GEMM_KC * 2);
+  DDLS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  dim3 grid((p.M + GEMM_BM - 1) / GEMM_BM, (p.N + BN - 1) / BN, splits);
+  kern<<<grid, V2_THREADS, smem, st>>>(p);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "umma_gemm_v2 launch");
+}
+
+template <bool A_MN, bool B_MN>
+static int dispatch_bn_v2(const GemmParams& p, int splits, cudaStream_t st) {
+  if (p.N <= 32) return launch_gemm_v2<32, A_MN, B_MN>(p, splits, st);
+  if (p.N <= 64) return launch_gemm_v2<64, A_MN, B_MN>(p, splits, st);
+  if (p.N <= 128 || p.N >= 1024) return launch_gemm_v2<128, A_MN, B_MN>(p, splits, st);   // wide N: more CTAs
+  return launch_gemm_v2<256, A_MN, B_MN>(p, splits, st);
+}
+
 template <int BN, bool A_MN, bool B_MN>
 static int launch_gemm(const GemmParams& p, int splits, cudaStream_t st) {
   auto kern = umma_gemm_kernel<BN, A_MN, B_MN>;
@@ -285,9 +451,18 @@ extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float
   } else if (flags & DDLS_GEMM_ACCUMULATE) {
     p.flags |= DDLS_GEMM_ATOMIC_ADD;   // single split accumulating into C
   }
+  // v2 (cp.async pipeline) needs bf16 operands whose rows are 16-byte aligned
+  const bool v2 = !(flags & (DDLS_GEMM_A_F32 | DDLS_GEMM_B_F32)) && lda % 8 == 0 && ldb % 8 == 0 &&
+                  (reinterpret_cast<uintptr_t>(A) & 15) == 0 && (reinterpret_cast<uintptr_t>(B) & 15) == 0 &&
+                  !(flags & DDLS_GEMM_FORCE_V1);
   int rc;
-  if (a_mn_major) rc = b_mn_major ? dispatch_bn<true, true>(p, splits, st) : dispatch_bn<true, false>(p, splits, st);
-  else rc = b_mn_major ? dispatch_bn<false, true>(p, splits, st) : dispatch_bn<false, false>(p, splits, st);
+  if (v2) {
+    if (a_mn_major) rc = b_mn_major ? dispatch_bn_v2<true, true>(p, splits, st) : dispatch_bn_v2<true, false>(p, splits, st);
+    else rc = b_mn_major ? dispatch_bn_v2<false, true>(p, splits, st) : dispatch_bn_v2<false, false>(p, splits, st);
+  } else {
+    if (a_mn_major) rc = b_mn_major ? dispatch_bn<true, true>(p, splits, st) : dispatch_bn<true, false>(p, splits, st);
+    else rc = b_mn_major ? dispatch_bn<false, true>(p, splits, st) : dispatch_bn<false, false>(p, splits, st);
+  }
   if (rc || splits == 1) return rc;
   const size_t total = (size_t)M * N;
   int blocks = (int)((total + 255) / 256);

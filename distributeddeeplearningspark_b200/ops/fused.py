@@ -69,3 +69,161 @@ def try_loss(model, x: torch.Tensor, y: torch.Tensor, loss_name: str) -> Optiona
         loss, _ = heads.dense_softmax_xent(a, plan['dense2'].kernel, plan['dense2'].bias, y)
         return loss
     return None
+
+
+# ----------------------------------------------------------------------------------------------------------
+# Autograd-free training step
+# ----------------------------------------------------------------------------------------------------------
+class DirectStep:
+    """Forward + backward of a recognised architecture as a fixed kernel sequence, with every gradient written
+    straight into its slice of the flat gradient buffer (which is the allreduce buffer): no autograd graph,
+    no gradient-accumulation kernels, no per-step allocations.  Requires a flat optimizer that clears the
+    gradient buffer after consuming it (a few small gradients are accumulated with atomics)."""
+
+    def __init__(self, model, optimizer, loss_name: str):
+        from ..optim.keras_optimizers import _FlatOptimizer
+        self.model = model
+        self.inner = getattr(optimizer, 'inner', optimizer)
+        if not isinstance(self.inner, _FlatOptimizer):
+            raise TypeError('DirectStep needs a flat fused optimizer')
+        self.plan = _plan(model)
+        self.kind = self.plan['kind']
+        self.loss_name = loss_name
+        self.flat = self.inner.flat
+        self.inner.zero_grads_in_step = True
+        self.flat.zero_grads()
+        if not self.flat.grads_attached():
+            self.flat.attach_grads()
+        self._bufs = {}
+        self.dev = self.flat.device
+        if self.kind == 'cnn':
+            d1 = self.plan['dense1']
+            self.ld1 = (d1.kernel.shape[1] + 7) // 8 * 8
+            self.w1s = self.inner.add_shadow(d1.kernel, self.ld1)
+
+    @staticmethod
+    def supported(model, optimizer, loss_name: str, x: torch.Tensor) -> bool:
+        from ..optim.keras_optimizers import _FlatOptimizer
+        inner = getattr(optimizer, 'inner', optimizer)
+        if not (x.is_cuda and isinstance(inner, _FlatOptimizer)):
+            return False
+        plan = _plan(model)
+        if plan['kind'] == 'rnn_regressor' and loss_name in ('mean_squared_error', 'mse'):
+            from . import recurrent
+            return recurrent.native_available(x, plan['rnn'].units)
+        if plan['kind'] == 'cnn' and loss_name == 'categorical_crossentropy':
+            from . import cnn
+            return cnn.native_available(plan, x) and plan['dense1'].kernel.shape[1] <= 256 and x.shape[0] <= 1024
+        return False
+
+    def _buf(self, name, shape, dtype):
+        key = (name, tuple(shape), dtype)
+        t = self._bufs.get(key)
+        if t is None:
+            t = torch.empty(shape, dtype=dtype, device=self.dev)
+            self._bufs[key] = t
+        return t
+
+    def run(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        return self._run_cnn(x, y) if self.kind == 'cnn' else self._run_rnn(x, y)
+
+    # ------------------------------------------------------------------ CNN
+    def _run_cnn(self, x, y):
+        from .. import _native as N
+        from . import cnn as C, heads
+        from .gemm import gemm_bf16, workspace
+        p = self.plan
+        c1, c2, d1, d2 = p['conv1'], p['conv2'], p['dense1'], p['dense2']
+        B = x.shape[0]
+        F = d1.kernel.shape[1]
+        ld = self.ld1
+        st = N.stream_ptr(self.dev)
+        bf, f32 = torch.bfloat16, torch.float32
+        a1 = self._buf('a1', (B, 26, 26, 32), bf)
+        pooled = self._buf('pooled', (B, 12, 12, 32), bf)
+        pidx = self._buf('pidx', (B, 12, 12, 32), torch.uint8)
+        a3 = self._buf('a3', (B, F), f32)
+        loss = self._buf('loss', (1,), f32)
+        dz3 = self._buf('dz3', (B, ld), bf)
+        dflat = self._buf('dflat', (B, 4608), bf)
+        dz2 = self._buf('dz2', (B, 24, 24, 32), bf)
+        dz1 = self._buf('dz1', (B, 26, 26, 32), bf)
+        x = x.contiguous()
+        N.call('ddls_cnn_conv1_fwd', x.data_ptr(), c1.kernel.data_ptr(), c1.bias.data_ptr(), a1.data_ptr(), B, st)
+        N.call('ddls_cnn_conv2_pool_fwd', a1.data_ptr(), c2.kernel.data_ptr(), c2.bias.data_ptr(), pooled.data_ptr(),
+               pidx.data_ptr(), B, st)
+        flat = pooled.view(B, 4608)
+        w1s = self.w1s[:, :F]
+        gemm_bf16(flat, w1s, bias=d1.bias, relu=True, b_mn_major=True, split_k=C.FWD_SPLIT_K, out=a3)
+        heads.softmax_xent_raw(a3, d2.kernel, d2.bias, y.contiguous(), None, loss, None, dz3, ld, d2.kernel.grad,
+                               d2.bias.grad, d1.bias.grad, True)
+        gemm_bf16(flat, dz3[:, :F], a_mn_major=True, b_mn_major=True, out=d1.kernel.grad)
+        gemm_bf16(dz3[:, :F], w1s, out=dflat)
+        N.call('ddls_cnn_unpool_bwd', dflat.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), dz2.data_ptr(),
+               c2.bias.grad.data_ptr(), B, st)
+        ws = workspace(self.dev, max(N.lib().ddls_cnn_conv2_wgrad_scratch_bytes(B), B * 320 * 4))
+        N.call('ddls_cnn_conv2_wgrad', a1.data_ptr(), dz2.data_ptr(), c2.kernel.grad.data_ptr(), ws.data_ptr(),
+               ws.numel(), B, st)
+        N.call('ddls_cnn_conv2_dgrad', dz2.data_ptr(), c2.kernel.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
+        g1k, g1b = c1.kernel.grad, c1.bias.grad
+        if g1b.data_ptr() == g1k.data_ptr() + 288 * 4:
+            N.call('ddls_cnn_conv1_wgrad', x.data_ptr(), dz1.data_ptr(), g1k.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
+        else:
+            g1 = self._buf('g1', (320,), f32)
+            N.call('ddls_cnn_conv1_wgrad', x.data_ptr(), dz1.data_ptr(), g1.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
+            g1k.view(-1).copy_(g1[:288]); g1b.copy_(g1[288:])
+        return loss
+
+    # ------------------------------------------------------------------ LSTM / GRU regressor
+    def _run_rnn(self, x, y):
+        from .. import _native as N
+        from . import heads
+        from . import recurrent as R
+        from .gemm import gemm_bf16
+        p = self.plan
+        rnn, dense = p['rnn'], p['dense']
+        is_lstm = rnn.keras_class == 'LSTM'
+        G = 4 if is_lstm else 3
+        H = R.H
+        B, T, _ = x.shape
+        st = N.stream_ptr(self.dev)
+        bf, f32 = torch.bfloat16, torch.float32
+        x2 = x.reshape(B, T).contiguous()
+        O = dense.kernel.shape[1]
+        h = self._buf('h', (B, H), f32)
+        hs = self._buf('hs', (T, B, H), bf)
+        pred = self._buf('pred', (B, O), f32)
+        loss = self._buf('loss', (1,), f32)
+        dh = self._buf('dh', (B, H), f32)
+        dz = self._buf('dz', (T, B, G * H), bf)
+        k, r, b = rnn.kernel, rnn.recurrent_kernel, rnn.bias
+        if is_lstm:
+            gates = self._buf('gates', (T, B, H, 4), bf)
+            cs = self._buf('cs', (T, B, H), f32)
+            N.call('ddls_lstm128_forward', x2.data_ptr(), k.data_ptr(), r.data_ptr(), b.data_ptr(), h.data_ptr(),
+                   hs.data_ptr(), gates.data_ptr(), cs.data_ptr(), B, T, 0, 1, 0, st)
+        else:
+            rh = self._buf('rh', (T, B, H), bf)
+            gates = self._buf('gates', (T, B, H, 4), f32)
+            N.call('ddls_gru128_forward', x2.data_ptr(), k.data_ptr(), r.data_ptr(), b.data_ptr(), h.data_ptr(),
+                   hs.data_ptr(), rh.data_ptr(), gates.data_ptr(), B, T, 0, 1, 0, st)
+        heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh, dense.kernel.grad,
+                            dense.bias.grad)
+        if is_lstm:
+            N.call('ddls_lstm128_backward', dh.data_ptr(), x2.data_ptr(), r.data_ptr(), gates.data_ptr(), cs.data_ptr(),
+                   dz.data_ptr(), k.grad.data_ptr(), b.grad.data_ptr(), B, T, 0, 0, st)
+        else:
+            N.call('ddls_gru128_backward', dh.data_ptr(), x2.data_ptr(), r.data_ptr(), gates.data_ptr(), dz.data_ptr(),
+                   k.grad.data_ptr(), b.grad.data_ptr(), B, T, 0, 0, st)
+        if T > 1:
+            kk = (T - 1) * B
+            sk = R._wgrad_split(kk)
+            dz2 = dz[1:].reshape(kk, G * H)
+            if is_lstm:
+                gemm_bf16(hs[:T - 1].reshape(kk, H), dz2, a_mn_major=True, b_mn_major=True, split_k=sk, out=r.grad)
+            else:
+                gemm_bf16(hs[:T - 1].reshape(kk, H), dz2[:, :2 * H], a_mn_major=True, b_mn_major=True, split_k=sk,
+                          out=r.grad[:, :2 * H])
+                gemm_bf16(rh[1:].reshape(kk, H), dz2[:, 2 * H:], a_mn_major=True, b_mn_major=True, split_k=sk,
+                          out=r.grad[:, 2 * H:])
+        return loss

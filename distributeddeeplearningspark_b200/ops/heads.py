@@ -1,5 +1,5 @@
 """Fused terminal heads: Dense + MSE and Dense + softmax + categorical cross-entropy, forward and
-backward in ONE launch each (``csrc/head.cu``)."""
+backward in ONE launch each (``csrc/head.cu``).  Every output is overwritten by the kernel."""
 from __future__ import annotations
 
 import torch
@@ -8,35 +8,7 @@ from .. import _native as N
 
 P, I = N.c_void_p, N.c_int
 N.register('ddls_dense_mse', [P, P, P, P, P, P, P, P, P, I, I, I, P])
-N.register('ddls_dense_softmax_xent', [P, P, P, P, P, P, P, P, P, I, I, I, P])
-
-
-class _DenseMSE(torch.autograd.Function):
-    """loss = mean_b mean_o (h·W + b - y)^2 ; gradients are produced by the same kernel."""
-
-    @staticmethod
-    def forward(ctx, h, w, b, y):
-        B, Hd = h.shape
-        O = w.shape[1]
-        dev = h.device
-        h = h.contiguous(); y2 = y.reshape(B, O).contiguous()
-        acc = torch.zeros(1 + Hd * O + O, dtype=torch.float32, device=dev)
-        loss, dw, db = acc[0:1], acc[1:1 + Hd * O], acc[1 + Hd * O:]
-        pred = torch.empty((B, O), dtype=torch.float32, device=dev)
-        dh = torch.empty_like(h)
-        N.call('ddls_dense_mse', h.data_ptr(), w.data_ptr(), b.data_ptr(), y2.data_ptr(), pred.data_ptr(),
-               loss.data_ptr(), dh.data_ptr(), dw.data_ptr(), db.data_ptr(), B, Hd, O, N.stream_ptr(dev))
-        ctx.save_for_backward(dh, dw.view(Hd, O), db)
-        ctx.mark_non_differentiable(pred)
-        return loss.reshape(()), pred
-
-    @staticmethod
-    def backward(ctx, gloss, _gpred):
-        dh, dw, db = ctx.saved_tensors
-        if _UNIT_SEED[0]:          # the step engine seeds loss.backward() with exactly 1
-            return dh, dw, db, None
-        return dh * gloss, dw * gloss, db * gloss, None
-
+N.register('ddls_dense_softmax_xent', [P, P, P, P, P, P, P, P, I, P, P, P, I, I, I, I, P])
 
 _UNIT_SEED = [False]
 
@@ -53,6 +25,46 @@ class unit_seed:
         _UNIT_SEED[0] = self._prev
 
 
+def dense_mse_raw(h, w, b, y, pred, loss, dh, dw, db):
+    """Direct launch: all tensors preallocated (``y``/gradients may be None for inference)."""
+    B, Hd = h.shape
+    N.call('ddls_dense_mse', h.data_ptr(), w.data_ptr(), b.data_ptr(), N.ptr(y), pred.data_ptr(), N.ptr(loss),
+           N.ptr(dh), N.ptr(dw), N.ptr(db), B, Hd, w.shape[1], N.stream_ptr(h.device))
+
+
+def softmax_xent_raw(a, w, b, onehot, probs, loss, da_f32, da_bf16, ldz, dw, db, dprev_bias, relu_input):
+    B, F = a.shape
+    N.call('ddls_dense_softmax_xent', a.data_ptr(), w.data_ptr(), b.data_ptr(), N.ptr(onehot), N.ptr(probs),
+           N.ptr(loss), N.ptr(da_f32), N.ptr(da_bf16), int(ldz), N.ptr(dw), N.ptr(db), N.ptr(dprev_bias), B, F,
+           w.shape[1], int(relu_input), N.stream_ptr(a.device))
+
+
+class _DenseMSE(torch.autograd.Function):
+    """loss = mean_b mean_o (h·W + b - y)^2 ; gradients are produced by the same kernel."""
+
+    @staticmethod
+    def forward(ctx, h, w, b, y):
+        B, Hd = h.shape
+        O = w.shape[1]
+        dev = h.device
+        h = h.contiguous(); y2 = y.reshape(B, O).contiguous()
+        buf = torch.empty(1 + Hd * O + O, dtype=torch.float32, device=dev)
+        loss, dw, db = buf[0:1], buf[1:1 + Hd * O].view(Hd, O), buf[1 + Hd * O:]
+        pred = torch.empty((B, O), dtype=torch.float32, device=dev)
+        dh = torch.empty_like(h)
+        dense_mse_raw(h, w, b, y2, pred, loss, dh, dw, db)
+        ctx.save_for_backward(dh, dw, db)
+        ctx.mark_non_differentiable(pred)
+        return loss.reshape(()), pred
+
+    @staticmethod
+    def backward(ctx, gloss, _gpred):
+        dh, dw, db = ctx.saved_tensors
+        if _UNIT_SEED[0]:          # the step engine seeds loss.backward() with exactly 1
+            return dh, dw, db, None
+        return dh * gloss, dw * gloss, db * gloss, None
+
+
 def dense_mse(h, w, b, y):
     """Returns (loss, pred)."""
     return _DenseMSE.apply(h, w, b, y)
@@ -60,11 +72,8 @@ def dense_mse(h, w, b, y):
 
 def dense_linear(h, w, b):
     """Inference-only Dense(H->O) through the same kernel (no targets)."""
-    B, Hd = h.shape
-    O = w.shape[1]
-    pred = torch.empty((B, O), dtype=torch.float32, device=h.device)
-    N.call('ddls_dense_mse', h.contiguous().data_ptr(), w.data_ptr(), b.data_ptr(), 0, pred.data_ptr(), 0, 0, 0, 0,
-           B, Hd, O, N.stream_ptr(h.device))
+    pred = torch.empty((h.shape[0], w.shape[1]), dtype=torch.float32, device=h.device)
+    dense_mse_raw(h.contiguous(), w, b, None, pred, None, None, None, None)
     return pred
 
 
@@ -75,14 +84,12 @@ class _DenseSoftmaxXent(torch.autograd.Function):
         C = w.shape[1]
         dev = a.device
         a = a.contiguous(); onehot = onehot.contiguous()
-        acc = torch.zeros(1 + F * C + C, dtype=torch.float32, device=dev)
-        loss, dw, db = acc[0:1], acc[1:1 + F * C], acc[1 + F * C:]
+        buf = torch.empty(1 + F * C + C, dtype=torch.float32, device=dev)
+        loss, dw, db = buf[0:1], buf[1:1 + F * C].view(F, C), buf[1 + F * C:]
         probs = torch.empty((B, C), dtype=torch.float32, device=dev)
         da = torch.empty_like(a)
-        N.call('ddls_dense_softmax_xent', a.data_ptr(), w.data_ptr(), b.data_ptr(), onehot.data_ptr(),
-               probs.data_ptr(), loss.data_ptr(), da.data_ptr(), dw.data_ptr(), db.data_ptr(), B, F, C,
-               N.stream_ptr(dev))
-        ctx.save_for_backward(da, dw.view(F, C), db)
+        softmax_xent_raw(a, w, b, onehot, probs, loss, da, None, 0, dw, db, None, False)
+        ctx.save_for_backward(da, dw, db)
         ctx.mark_non_differentiable(probs)
         return loss.reshape(()), probs
 
@@ -100,9 +107,6 @@ def dense_softmax_xent(a, w, b, onehot):
 
 
 def dense_softmax(a, w, b):
-    B, F = a.shape
-    C = w.shape[1]
-    probs = torch.empty((B, C), dtype=torch.float32, device=a.device)
-    N.call('ddls_dense_softmax_xent', a.contiguous().data_ptr(), w.data_ptr(), b.data_ptr(), 0, probs.data_ptr(), 0, 0,
-           0, 0, B, F, C, N.stream_ptr(a.device))
+    probs = torch.empty((a.shape[0], w.shape[1]), dtype=torch.float32, device=a.device)
+    softmax_xent_raw(a.contiguous(), w, b, None, probs, None, None, None, 0, None, None, None, False)
     return probs

@@ -14,7 +14,7 @@ CUDA graph replays correctly.  On CPU the same math runs as flat torch ops.
 from __future__ import annotations
 
 import math
-from typing import Dict, Iterable, Optional
+from typing import Dict, Iterable, List, Optional
 
 import torch
 
@@ -35,6 +35,40 @@ class _FlatOptimizer:
         if self.device.type == 'cuda':
             from ..ops import optimizer as native
             self._native = native
+        self._shadows = []          # [(begin, rows, cols, ld, bf16 tensor)]
+        self._shadow_by_param = {}
+        self._specs, self._nspecs = None, 0
+        self._seen_param_version = self.flat.flat_params._version
+
+    # bf16 shadow copies of weight matrices, refreshed inside the fused update kernel -------------------
+    def add_shadow(self, param: torch.nn.Parameter, ld: Optional[int] = None) -> torch.Tensor:
+        """Keep a bf16 copy of 2-D-viewed ``param`` ([rows, cols], rows padded to ``ld`` columns, ld % 8 == 0)
+        up to date: the optimizer kernel rewrites it in the pass that updates the fp32 master."""
+        key = id(param)
+        if key in self._shadow_by_param:
+            return self._shadow_by_param[key]
+        if self._native is None:
+            raise RuntimeError('shadow weights are a CUDA feature')
+        idx = next(i for i, q in enumerate(self.flat.params) if q is param)
+        cols = param.shape[-1]
+        rows = param.numel() // cols
+        ld = ld or (cols + 7) // 8 * 8
+        t = torch.zeros((rows, ld), dtype=torch.bfloat16, device=self.device)
+        self._shadows.append((self.flat.offsets[idx], rows, cols, ld, t))
+        self._shadow_by_param[key] = t
+        self._specs, self._nspecs = self._native.make_specs(self._shadows)
+        self.refresh_shadows()
+        return t
+
+    def refresh_shadows(self) -> None:
+        if self._nspecs:
+            self._native.refresh_shadows(self.flat.flat_params, self._specs, self._nspecs)
+        self._seen_param_version = self.flat.flat_params._version
+
+    def refresh_shadows_if_stale(self) -> None:
+        """Parameters changed through torch ops since the last refresh (broadcast, set_weights, ADAG pull)?"""
+        if self._nspecs and self.flat.flat_params._version != self._seen_param_version:
+            self.refresh_shadows()
 
     # torch.optim-like surface ----------------------------------------------
     @property
@@ -91,7 +125,7 @@ class KerasAdam(_FlatOptimizer):
         if self._native is not None:
             self._native.adam_step(f.flat_params, f.flat_grads, self.m, self.v, self.step_count,
                                    self.lr, self.beta_1, self.beta_2, self.epsilon, self.grad_scale,
-                                   self.zero_grads_in_step)
+                                   self.zero_grads_in_step, self._specs, self._nspecs)
             return
         self.step_count += 1
         t = int(self.step_count.item())
@@ -120,7 +154,8 @@ class KerasAdagrad(_FlatOptimizer):
         f = self.flat
         if self._native is not None:
             self._native.adagrad_step(f.flat_params, f.flat_grads, self.acc, self.step_count,
-                                      self.lr, self.epsilon, self.grad_scale, self.zero_grads_in_step)
+                                      self.lr, self.epsilon, self.grad_scale, self.zero_grads_in_step,
+                                      self._specs, self._nspecs)
             return
         self.step_count += 1
         g = f.flat_grads * self.grad_scale if self.grad_scale != 1.0 else f.flat_grads
@@ -142,7 +177,7 @@ class KerasSGD(_FlatOptimizer):
         f = self.flat
         if self._native is not None:
             self._native.sgd_step(f.flat_params, f.flat_grads, self.step_count, self.lr, self.grad_scale,
-                                  self.zero_grads_in_step)
+                                  self.zero_grads_in_step, self._specs, self._nspecs)
             return
         self.step_count += 1
         f.flat_params.add_(f.flat_grads, alpha=-self.lr * self.grad_scale)

@@ -273,6 +273,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
             stage = self._ensure_stage(n, self.size) if a != AR_NVLS else 0
             N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, n, scale, int(wire_bf16), 0,
                    self._stream())
+            torch.autograd.graph.increment_version(t)     # raw-pointer kernels bypass torch's version counter
             return t
         # not heap-resident: bounce through the scratch region (chunked)
         flat = t.reshape(-1)
@@ -300,6 +301,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
         off = self.offset_of(t) if t.is_contiguous() else None
         if off is not None and off % 16 == 0 and nbytes % 16 == 0:
             N.call('ddls_comm_broadcast', ctypes.byref(self.desc), off, nbytes, root, 1, 0, self._stream())
+            torch.autograd.graph.increment_version(t)
             return t
         flat = t.contiguous().view(-1).view(torch.uint8) if t.is_contiguous() else t.contiguous().view(torch.uint8).view(-1)
         scratch = self._heap_u8[self._scratch_off:self._scratch_off + self._scratch_bytes]

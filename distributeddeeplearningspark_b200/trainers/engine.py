@@ -76,6 +76,10 @@ class StepEngine:
         self._warm = 0
         self.steps = 0
         inner = getattr(self.optimizer, 'inner', self.optimizer)
+        self._inner = inner
+        self._direct = None          # autograd-free fused step (ops.fused.DirectStep), built lazily
+        self._direct_checked = False
+        self.use_direct = self.cuda and env_flag('DDLS_DIRECT_STEP', True)
         # the fused optimizer kernels can clear the gradient buffer after consuming it
         self._skip_zero = self.cuda and bool(getattr(inner, 'zero_grads_in_step', False))
 
@@ -88,7 +92,22 @@ class StepEngine:
                 return loss
         return self.loss_fn(self.model(x), y)
 
+    def _maybe_direct(self, x: torch.Tensor):
+        if self._direct_checked or not self.use_direct:
+            return self._direct
+        self._direct_checked = True
+        from ..ops.fused import DirectStep
+        if DirectStep.supported(self.model, self.optimizer, self.loss_name, x):
+            self._direct = DirectStep(self.model, self.optimizer, self.loss_name)
+            self._skip_zero = True
+        return self._direct
+
     def _eager_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        direct = self._maybe_direct(x)
+        if direct is not None:
+            loss = direct.run(x, y)
+            self.optimizer.step()
+            return loss.reshape(())
         if not self._skip_zero:
             self.optimizer.zero_grad()
         loss = self._loss(x, y)
@@ -110,8 +129,15 @@ class StepEngine:
             self._static_loss = self._eager_step(self._static_x, self._static_y)
         self._graph = g
 
+    def notify_params_changed(self) -> None:
+        """Call after changing parameters outside the optimizer (e.g. an ADAG pull): refreshes bf16 shadows."""
+        if hasattr(self._inner, 'refresh_shadows'):
+            self._inner.refresh_shadows()
+
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         self.steps += 1
+        if self.cuda and hasattr(self._inner, 'refresh_shadows_if_stale'):
+            self._inner.refresh_shadows_if_stale()
         if not self.use_cuda_graph:
             return self._eager_step(x, y)
         if self._graph is None:

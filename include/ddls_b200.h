@@ -29,6 +29,7 @@ unsigned long long ddls_launch_count(void);
 #define DDLS_GEMM_B_F32 32u       /* B is fp32 in memory */
 #define DDLS_GEMM_SPLITK_WS 64u   /* internal */
 #define DDLS_GEMM_ACCUMULATE 128u /* C += result (fp32 C) */
+#define DDLS_GEMM_FORCE_V1 256u   /* use the register-staged mainloop even when the cp.async one applies */
 /* C[M,N] = op(A)·op(B)ᵀ (+bias, ReLU, cast).  a_mn_major=0: A is [M,K] row-major; 1: A is [K,M]
  * row-major.  Same for B over N.  Operands are bf16, or fp32 with the *_F32 flags.  split_k>1 writes
  * fp32 partial tiles to `workspace` (split_k*M*N*4 bytes of scratch) and a second kernel sums them
@@ -42,12 +43,23 @@ int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int
  * 'adagrad' ddl_nyiso_aztk.py:207).  `step` is a device int32 counter the kernel increments, so a
  * captured CUDA graph replays correctly.  grad_scale multiplies the gradient first (1/N, 1/passes).
  * If zero_grads != 0 the gradient buffer is cleared after use (saves a memset launch). */
+#define DDLS_MAX_SHADOWS 4
+/* A bf16 copy of the parameter matrix at flat element offset `begin` ([rows, cols] row-major) kept at dst with
+ * row stride ld (>= cols, multiple of 8; padding columns stay zero).  The optimizer kernels refresh it in the
+ * same pass that updates the fp32 master ("fused cast"). */
+typedef struct {
+  unsigned long long begin;
+  unsigned rows, cols, ld, kind;
+  void* dst;
+} DdlsShadowSpec;
 int ddls_adam_step(float* params, float* grads, float* m, float* v, int* step, size_t n, float lr, float beta1,
-                   float beta2, float eps, float grad_scale, int zero_grads, void* stream);
+                   float beta2, float eps, float grad_scale, int zero_grads, const DdlsShadowSpec* shadows,
+                   int n_shadows, void* stream);
 int ddls_adagrad_step(float* params, float* grads, float* acc, int* step, size_t n, float lr, float eps,
-                      float grad_scale, int zero_grads, void* stream);
+                      float grad_scale, int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream);
 int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, float grad_scale, int zero_grads,
-                  void* stream);
+                  const DdlsShadowSpec* shadows, int n_shadows, void* stream);
+int ddls_refresh_shadows(const float* params, size_t n, const DdlsShadowSpec* shadows, int n_shadows, void* stream);
 
 /* ---- on-device preprocessing (MinMax + reshape + one-hot, ddl_mnist_aztk.py:126-144) ---------- */
 /* pixels uint8 [n,784] -> x fp32 [n,28,28,1] = (p - o_min)*scale + n_min ; labels int64 [n] -> onehot fp32 [n,classes] */
@@ -79,13 +91,15 @@ int ddls_gru128_backward(const float* dout, const float* x, const float* w_hh, c
 
 /* ---- fused output heads (forward + backward in one launch) -------------------------------------- */
 /* Dense(H->O, linear) + Keras mean_squared_error (ddl_nyiso_aztk.py:203,207).  y == NULL: pred only.
- * Caller zeroes loss[1], dwd [H,O], dbd [O]; the kernel accumulates into them. */
+ * One CTA; every output (pred, loss[1], dh [B,H], dwd [H,O], dbd [O]) is overwritten. */
 int ddls_dense_mse(const float* h, const float* wd, const float* bd, const float* y, float* pred, float* loss,
                    float* dh, float* dwd, float* dbd, int B, int H, int O, void* stream);
 /* Dense(F->C) + softmax + categorical_crossentropy (ddl_mnist_aztk.py:191-196).  onehot == NULL:
- * probabilities only.  Caller zeroes loss[1], dw [F,C], db [C]. */
+ * probabilities only.  One CTA; outputs overwritten.  da: fp32 [B,F] and/or bf16 [B,ldz] (zero padded).
+ * relu_input != 0 folds the previous layer's ReLU in (da *= a > 0) and emits its bias gradient dprev_bias [F]. */
 int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, const float* onehot, float* probs,
-                            float* loss, float* da, float* dw, float* db, int B, int F, int C, void* stream);
+                            float* loss, float* da_f32, void* da_bf16, int ldz, float* dw, float* db,
+                            float* dprev_bias, int B, int F, int C, int relu_input, void* stream);
 
 /* ---- MNIST CNN trunk (/root/reference/ddl_mnist_aztk.py:180-190), NHWC, Keras kernel layouts --------
  * conv1+ReLU: x [B,28,28,1] fp32 -> a1 [B,26,26,32] bf16. */

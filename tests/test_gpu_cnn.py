@@ -124,3 +124,33 @@ def test_step_engine_trains_mnist_cnn_with_cuda_graph():
     with torch.no_grad():
         acc = float((m(x[:512]).argmax(-1) == torch.from_numpy(lab[:512]).to(dev)).float().mean())
     assert acc > 0.8
+
+
+@pytest.mark.parametrize('name', ['mnist_cnn', 'nyiso_lstm', 'nyiso_gru'])
+def test_direct_step_matches_autograd_path(name, monkeypatch):
+    """The autograd-free fused step and the autograd Functions are the same math: same losses and weights."""
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    dev = torch.device('cuda', 0)
+    torch.manual_seed(0)
+    if name == 'mnist_cnn':
+        xs = torch.rand(6, 64, 28, 28, 1, device=dev)
+        ys = torch.eye(10, device=dev)[torch.randint(0, 10, (6, 64), device=dev)]
+    else:
+        xs = torch.rand(6, 32, 25, 1, device=dev); ys = torch.rand(6, 32, 1, device=dev)
+    out = {}
+    for direct in ('1', '0'):
+        monkeypatch.setenv('DDLS_DIRECT_STEP', direct)
+        m = getattr(ddls.models, name)(seed=3).to(dev)
+        eng = StepEngine(m, optimizer=m.optimizer_name, loss=m.loss_name, device=dev, use_cuda_graph=False)
+        losses = [float(eng.step(xs[i], ys[i])) for i in range(6)]
+        assert (eng._direct is not None) == (direct == '1')
+        out[direct] = (losses, torch.cat([p.detach().reshape(-1) for p in m.parameters()]))
+        if direct == '1' and name == 'mnist_cnn':      # bf16 shadow of the Dense kernel tracks the fp32 master
+            d1 = m.layers[6]
+            sh = eng._inner._shadow_by_param[id(d1.kernel)]
+            assert torch.equal(sh[:, :225], d1.kernel.detach().bfloat16()) and float(sh[:, 225:].float().abs().max()) == 0
+    la, lb = out['1'][0], out['0'][0]
+    assert all(abs(a - b) <= 2e-2 * max(abs(b), 1e-3) for a, b in zip(la, lb)), (la, lb)
+    wa, wb = out['1'][1], out['0'][1]
+    assert float((wa - wb).norm() / wb.norm()) < 2e-3
