@@ -74,7 +74,7 @@ DDLS_DEVINL void stage_w2_mnmajor(uint8_t* sB, const float* __restrict__ w2) {
 // conv2 + bias + ReLU + 2x2 max-pool : a1 [B,26,26,32] bf16 -> pooled [B,12,12,32] bf16, idx u8 (0..3)
 // M tile = 128 rows = 32 pooled pixels x 4 window positions (row m = p*4 + q), N = 32, K = 288.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(CT, 1) conv2_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ a1,
+__global__ void __launch_bounds__(CT, 2) conv2_relu_pool_fwd_kernel(const __nv_bfloat16* __restrict__ a1,
                                                                     const float* __restrict__ w2,
                                                                     const float* __restrict__ bias,
                                                                     __nv_bfloat16* __restrict__ pooled,
@@ -96,14 +96,18 @@ __global__ void __launch_bounds__(CT, 1) conv2_relu_pool_fwd_kernel(const __nv_b
     const int m = idx & 127, kc = idx >> 7;
     const int tap = kc >> 2, cg = kc & 3, kh = tap / 3, kw = tap - kh * 3;
     const int P = p0 + (m >> 2), q = m & 3;
-    uint4 v = make_uint4(0, 0, 0, 0);
+    const __nv_bfloat16* src = a1;
+    uint32_t nbytes = 0;
     if (P < total_pooled) {
       const int b = P / (PL * PL), r = P - b * PL * PL, ph = r / PL, pw = r - ph * PL;
       const int ih = 2 * ph + (q >> 1) + kh, iw = 2 * pw + (q & 1) + kw;
-      v = *reinterpret_cast<const uint4*>(a1 + (((size_t)b * C1 + ih) * C1 + iw) * CH + cg * 8);
+      src = a1 + (((size_t)b * C1 + ih) * C1 + iw) * CH + cg * 8;
+      nbytes = 16;
     }
-    *reinterpret_cast<uint4*>(sA + kc * 2048 + m * 16) = v;
+    cp_async16(sA + kc * 2048 + m * 16, src, nbytes);       // LDGSTS: no register staging, 18 copies in flight
   }
+  cp_async_commit();
+  cp_async_wait<0>();
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -234,14 +238,14 @@ __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const __nv_bfloat1
 constexpr int WG_KB = 64;                 // pixels per pipeline stage
 constexpr int WG_A_STAGE = 8 * 48 * 128;  // [8 k-groups][48 m-groups][8 k][8 m] bf16 = 49,152 B
 constexpr int WG_B_STAGE = 8 * 4 * 128;   // [8 k-groups][4 n-groups][8 k][8 n]       =  4,096 B
+constexpr int WG_STAGE = WG_A_STAGE + WG_B_STAGE;
+constexpr int WG_STAGES = 3;
 
 __global__ void __launch_bounds__(CT, 1) conv2_wgrad_kernel(const __nv_bfloat16* __restrict__ a1,
                                                             const __nv_bfloat16* __restrict__ dz2,
                                                             float* __restrict__ partial, int B, int pix_per_cta) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  uint8_t* sA[2] = {smem, smem + WG_A_STAGE};
-  uint8_t* sB[2] = {smem + 2 * WG_A_STAGE, smem + 2 * WG_A_STAGE + WG_B_STAGE};
-  __shared__ uint64_t bars[2];
+  __shared__ uint64_t bars[WG_STAGES];
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int total_pix = B * C2 * C2;
@@ -249,50 +253,66 @@ __global__ void __launch_bounds__(CT, 1) conv2_wgrad_kernel(const __nv_bfloat16*
   const int k_end = min(total_pix, k_begin + pix_per_cta);
 
   if (warp == 0) tmem_alloc(&tmem_s, 128);
-  if (tid == 32) { mbar_init(&bars[0], 1); mbar_init(&bars[1], 1); mbar_fence_init(); }
-  // zero the padding m-groups (taps 9..11) of both stages once
-  for (int idx = tid; idx < 2 * 8 * 12 * 8; idx += CT) {
+  if (tid == 32) { for (int s = 0; s < WG_STAGES; ++s) mbar_init(&bars[s], 1); mbar_fence_init(); }
+  // zero the padding m-groups (taps 9..11) of every stage once
+  for (int idx = tid; idx < WG_STAGES * 8 * 12 * 8; idx += CT) {
     const int s = idx / (8 * 12 * 8), r = idx - s * (8 * 12 * 8);
     const int kg = r / (12 * 8), r2 = r - kg * (12 * 8);
-    *reinterpret_cast<uint4*>(sA[s] + kg * (48 * 128) + (36 + r2 / 8) * 128 + (r2 & 7) * 16) = make_uint4(0, 0, 0, 0);
+    *reinterpret_cast<uint4*>(smem + s * WG_STAGE + kg * (48 * 128) + (36 + r2 / 8) * 128 + (r2 & 7) * 16) =
+        make_uint4(0, 0, 0, 0);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_s;
   constexpr uint32_t idesc = umma_idesc_bf16(128, 32, true, true);
-
   const int nkb = (k_end - k_begin + WG_KB - 1) / WG_KB;
-  uint32_t waits[2] = {0, 0};
-  for (int kb = 0; kb < nkb; ++kb) {
-    const int s = kb & 1;
-    if (kb >= 2) { mbar_wait(&bars[s], waits[s] & 1); ++waits[s]; }
+
+  auto issue = [&](int kb) {
+    uint8_t* sA = smem + (kb % WG_STAGES) * WG_STAGE;
+    uint8_t* sB = sA + WG_A_STAGE;
     const int kk0 = k_begin + kb * WG_KB;
     // A gather: item = (m-group mg = tap*4 + cg, pixel k); 8 consecutive lanes -> 8 consecutive pixels (128 B)
     for (int idx = tid; idx < 36 * WG_KB; idx += CT) {
       const int k = idx & (WG_KB - 1), mg = idx >> 6;
       const int tap = mg >> 2, cg = mg & 3, kh = tap / 3, kw = tap - kh * 3;
       const int pix = kk0 + k;
-      uint4 v = make_uint4(0, 0, 0, 0);
+      const __nv_bfloat16* src = a1;
+      uint32_t nb = 0;
       if (pix < k_end) {
         const int b = pix / (C2 * C2), r = pix - b * C2 * C2, oh = r / C2, ow = r - oh * C2;
-        v = *reinterpret_cast<const uint4*>(a1 + (((size_t)b * C1 + oh + kh) * C1 + ow + kw) * CH + cg * 8);
+        src = a1 + (((size_t)b * C1 + oh + kh) * C1 + ow + kw) * CH + cg * 8;
+        nb = 16;
       }
-      *reinterpret_cast<uint4*>(sA[s] + (k >> 3) * (48 * 128) + mg * 128 + (k & 7) * 16) = v;
+      cp_async16(sA + (k >> 3) * (48 * 128) + mg * 128 + (k & 7) * 16, src, nb);
     }
-    // B: dz2 rows are 64 contiguous bytes per pixel
-    for (int idx = tid; idx < 4 * WG_KB; idx += CT) {
+    for (int idx = tid; idx < 4 * WG_KB; idx += CT) {   // dz2 rows are 64 contiguous bytes per pixel
       const int k = idx & (WG_KB - 1), ng = idx >> 6;
       const int pix = kk0 + k;
-      uint4 v = make_uint4(0, 0, 0, 0);
-      if (pix < k_end) v = *reinterpret_cast<const uint4*>(dz2 + (size_t)pix * CH + ng * 8);
-      *reinterpret_cast<uint4*>(sB[s] + (k >> 3) * 512 + ng * 128 + (k & 7) * 16) = v;
+      const bool ok = pix < k_end;
+      cp_async16(sB + (k >> 3) * 512 + ng * 128 + (k & 7) * 16, ok ? dz2 + (size_t)pix * CH + ng * 8 : dz2, ok ? 16 : 0);
     }
+  };
+  for (int kb = 0; kb < WG_STAGES - 1; ++kb) {
+    if (kb < nkb) issue(kb);
+    cp_async_commit();
+  }
+  uint32_t waits[WG_STAGES] = {};
+  for (int kb = 0; kb < nkb; ++kb) {
+    const int s = kb % WG_STAGES;
+    const int nxt = kb + WG_STAGES - 1;
+    if (nxt < nkb) {
+      const int ns = nxt % WG_STAGES;
+      if (kb >= 1) { mbar_wait(&bars[ns], waits[ns] & 1); ++waits[ns]; }
+      issue(nxt);
+    }
+    cp_async_commit();
+    cp_async_wait<WG_STAGES - 1>();
     fence_proxy_async_smem();
     __syncthreads();
     if (tid == 0) {
       tc_fence_after();
-      const uint32_t a_base = smem_u32(sA[s]), b_base = smem_u32(sB[s]);
+      const uint32_t a_base = smem_u32(smem + s * WG_STAGE), b_base = a_base + WG_A_STAGE;
 #pragma unroll
       for (int mt = 0; mt < 3; ++mt)
 #pragma unroll
@@ -302,8 +322,9 @@ __global__ void __launch_bounds__(CT, 1) conv2_wgrad_kernel(const __nv_bfloat16*
       umma_commit(&bars[s]);
     }
   }
-  for (int s = 0; s < 2; ++s) {
-    const uint32_t commits = (nkb + 1 - s) / 2;
+  cp_async_wait<0>();
+  for (int s = 0; s < WG_STAGES; ++s) {
+    const uint32_t commits = nkb > s ? (nkb - s + WG_STAGES - 1) / WG_STAGES : 0;
     while (waits[s] < commits) { mbar_wait(&bars[s], waits[s] & 1); ++waits[s]; }
   }
   tc_fence_after();
@@ -316,16 +337,13 @@ __global__ void __launch_bounds__(CT, 1) conv2_wgrad_kernel(const __nv_bfloat16*
       tmem_ld32(tmem + (static_cast<uint32_t>(warp * 32) << 16) + mt * 32, v);
       tmem_ld_wait();
       const int m = mt * 128 + mrow;
-      if (m < K2 && nkb > 0) {
+      if (m < K2) {
         float4* o = reinterpret_cast<float4*>(dst + (size_t)m * CH);
 #pragma unroll
         for (int c = 0; c < 8; ++c)
-          o[c] = make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]), __uint_as_float(v[4 * c + 2]),
-                             __uint_as_float(v[4 * c + 3]));
-      } else if (m < K2) {
-        float4* o = reinterpret_cast<float4*>(dst + (size_t)m * CH);
-#pragma unroll
-        for (int c = 0; c < 8; ++c) o[c] = make_float4(0.f, 0.f, 0.f, 0.f);
+          o[c] = nkb > 0 ? make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]),
+                                       __uint_as_float(v[4 * c + 2]), __uint_as_float(v[4 * c + 3]))
+                         : make_float4(0.f, 0.f, 0.f, 0.f);
       }
     }
   }
@@ -353,7 +371,7 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restri
 //   dz1[b,ih,iw,ci] = (a1 > 0) * sum_{kh,kw,co} dz2[b,ih-kh,iw-kw,co] * W2[kh,kw,ci,co]
 // implicit GEMM: M tile = 128 input pixels, N = 32 (ci), K = 288 (tap, co)
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(CT, 1) conv2_dgrad_relu_kernel(const __nv_bfloat16* __restrict__ dz2,
+__global__ void __launch_bounds__(CT, 2) conv2_dgrad_relu_kernel(const __nv_bfloat16* __restrict__ dz2,
                                                                  const float* __restrict__ w2,
                                                                  const __nv_bfloat16* __restrict__ a1,
                                                                  __nv_bfloat16* __restrict__ dz1, int B) {
@@ -381,15 +399,20 @@ __global__ void __launch_bounds__(CT, 1) conv2_dgrad_relu_kernel(const __nv_bflo
     const int m = idx & 127, kc = idx >> 7;
     const int tap = kc >> 2, cog = kc & 3, kh = tap / 3, kw = tap - kh * 3;
     const int pix = m0 + m;
-    uint4 v = make_uint4(0, 0, 0, 0);
+    const __nv_bfloat16* src = dz2;
+    uint32_t nbytes = 0;
     if (pix < total_pix) {
       const int b = pix / (C1 * C1), r = pix - b * C1 * C1, ih = r / C1, iw = r - ih * C1;
       const int oh = ih - kh, ow = iw - kw;
-      if (oh >= 0 && oh < C2 && ow >= 0 && ow < C2)
-        v = *reinterpret_cast<const uint4*>(dz2 + (((size_t)b * C2 + oh) * C2 + ow) * CH + cog * 8);
+      if (oh >= 0 && oh < C2 && ow >= 0 && ow < C2) {
+        src = dz2 + (((size_t)b * C2 + oh) * C2 + ow) * CH + cog * 8;
+        nbytes = 16;
+      }
     }
-    *reinterpret_cast<uint4*>(sA + kc * 2048 + m * 16) = v;
+    cp_async16(sA + kc * 2048 + m * 16, src, nbytes);
   }
+  cp_async_commit();
+  cp_async_wait<0>();
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -528,7 +551,7 @@ extern "C" int ddls_cnn_conv2_wgrad(const void* a1, const void* dz2, float* dw2,
     set_last_error("ddls_cnn_conv2_wgrad: needs %zu bytes of scratch (got %zu)", need, scratch_bytes);
     return 1;
   }
-  const int smem = 2 * WG_A_STAGE + 2 * WG_B_STAGE;
+  const int smem = WG_STAGES * WG_STAGE;
   DDLS_CUDA_OK(cudaFuncSetAttribute(conv2_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   conv2_wgrad_kernel<<<splits, CT, smem, ST(stream)>>>(static_cast<const __nv_bfloat16*>(a1),
                                                         static_cast<const __nv_bfloat16*>(dz2),

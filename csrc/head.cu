@@ -29,6 +29,7 @@ DDLS_DEVINL float warp_sum(float v) {
 //          and accumulating dw[f][:] and dprev_bias[f]; the four groups are combined through shared memory.
 constexpr int XH_THREADS = 1024;
 constexpr int XH_MAXC = 16;
+constexpr int XH_ROWS = 128;      // rows of `a` staged in shared memory per pass
 __global__ void __launch_bounds__(XH_THREADS, 1) head_softmax_xent_kernel(
     const float* __restrict__ a, const float* __restrict__ w, const float* __restrict__ bias,
     const float* __restrict__ onehot, float* __restrict__ probs, float* __restrict__ loss, float* __restrict__ da_f32,
@@ -36,78 +37,92 @@ __global__ void __launch_bounds__(XH_THREADS, 1) head_softmax_xent_kernel(
     float* __restrict__ dprev_bias, int B, int F, int C, int relu_input) {
   extern __shared__ float sm[];
   float* sw = sm;                               // [F][C]
-  float* sd = sw + F * C;                       // [B][C]   dL/dlogits
-  float* sacc = sd + B * C;                     // [4][F][C+1] group partials (dw | dprev_bias)
+  float* sd = sw + F * C;                       // [XH_ROWS][C]   dL/dlogits of the staged rows
+  float* sa = sd + XH_ROWS * C;                 // [XH_ROWS][F]   staged activations
+  float* sacc = sa;                             // [4][F][C+1] group partials, aliases sa after the last pass
   __shared__ float sloss[32];
+  __shared__ float sdb[XH_MAXC];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < F * C; i += XH_THREADS) sw[i] = w[i];
-  __syncthreads();
+  if (tid < XH_MAXC) sdb[tid] = 0.f;
   const float invB = 1.0f / (float)B;
   float lsum = 0.f;
-  for (int b = warp; b < B; b += XH_THREADS / 32) {
-    float z[XH_MAXC];
+  const int grp = tid >> 8, f = tid & 255;       // phase 2: 4 row groups x 256 feature slots
+  float wr[XH_MAXC], gw[XH_MAXC], gprev = 0.f;
+  __syncthreads();
 #pragma unroll
-    for (int c = 0; c < XH_MAXC; ++c) z[c] = 0.f;
-    for (int f = lane; f < F; f += 32) {
-      const float av = a[(size_t)b * F + f];
+  for (int c = 0; c < XH_MAXC; ++c) { wr[c] = (f < F && c < C) ? sw[f * C + c] : 0.f; gw[c] = 0.f; }
+
+  for (int r0 = 0; r0 < B; r0 += XH_ROWS) {
+    const int rows = min(XH_ROWS, B - r0);
+    // stage rows [r0, r0+rows) of a: coalesced, many independent loads in flight per thread
+    const float* src = a + (size_t)r0 * F;
+#pragma unroll 8
+    for (int i = tid; i < rows * F; i += XH_THREADS) sa[i] = src[i];
+    __syncthreads();
+    // ---- phase 1: one warp per row -> logits, softmax, d = (p - y)/B ----
+    for (int rb = warp; rb < rows; rb += XH_THREADS / 32) {
+      const int b = r0 + rb;
+      float z[XH_MAXC];
+#pragma unroll
+      for (int c = 0; c < XH_MAXC; ++c) z[c] = 0.f;
+      for (int ff = lane; ff < F; ff += 32) {
+        const float av = sa[rb * F + ff];
+#pragma unroll
+        for (int c = 0; c < XH_MAXC; ++c)
+          if (c < C) z[c] = fmaf(av, sw[ff * C + c], z[c]);
+      }
+      float mx = -INFINITY;
 #pragma unroll
       for (int c = 0; c < XH_MAXC; ++c)
-        if (c < C) z[c] = fmaf(av, sw[f * C + c], z[c]);
-    }
-    float mx = -INFINITY;
+        if (c < C) { z[c] = warp_sum(z[c]) + bias[c]; mx = fmaxf(mx, z[c]); }
+      float ssum = 0.f;
 #pragma unroll
-    for (int c = 0; c < XH_MAXC; ++c)
-      if (c < C) { z[c] = warp_sum(z[c]) + bias[c]; mx = fmaxf(mx, z[c]); }
-    float ssum = 0.f;
+      for (int c = 0; c < XH_MAXC; ++c)
+        if (c < C) { z[c] = __expf(z[c] - mx); ssum += z[c]; }
+      const float inv = 1.0f / ssum;
 #pragma unroll
-    for (int c = 0; c < XH_MAXC; ++c)
-      if (c < C) { z[c] = __expf(z[c] - mx); ssum += z[c]; }
-    const float inv = 1.0f / ssum;
-#pragma unroll
-    for (int c = 0; c < XH_MAXC; ++c) {
-      if (c < C) {
-        const float pr = z[c] * inv;
-        if (lane == c) {
+      for (int c = 0; c < XH_MAXC; ++c) {
+        if (c < C && lane == c) {
+          const float pr = z[c] * inv;
           if (probs != nullptr) probs[(size_t)b * C + c] = pr;
           if (onehot != nullptr) {
             const float yv = onehot[(size_t)b * C + c];
-            sd[b * C + c] = (pr - yv) * invB;
+            sd[rb * C + c] = (pr - yv) * invB;
             // Keras clips probabilities to [1e-7, 1-1e-7] inside the log
             lsum += -yv * __logf(fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f)) * invB;
           }
         }
       }
     }
+    if (onehot == nullptr) { __syncthreads(); continue; }
+    __syncthreads();
+    // ---- phase 2: thread (group, feature) walks its rows; w[f][:] lives in registers ----
+    if (f < ldz || f < F) {
+      for (int rb = grp; rb < rows; rb += 4) {
+        float g = 0.f;
+        if (f < F) {
+          const float av = sa[rb * F + f];
+#pragma unroll
+          for (int c = 0; c < XH_MAXC; ++c)
+            if (c < C) { const float d = sd[rb * C + c]; g = fmaf(d, wr[c], g); gw[c] = fmaf(av, d, gw[c]); }
+          if (relu_input && !(av > 0.f)) g = 0.f;
+          gprev += g;
+          if (da_f32 != nullptr) da_f32[(size_t)(r0 + rb) * F + f] = g;
+        }
+        if (da_bf16 != nullptr && f < ldz) da_bf16[(size_t)(r0 + rb) * ldz + f] = __float2bfloat16(g);
+      }
+    }
+    if (tid < C) {
+      float v = 0.f;
+      for (int rb = 0; rb < rows; ++rb) v += sd[rb * C + tid];
+      sdb[tid] += v;
+    }
+    __syncthreads();
   }
   if (onehot == nullptr) return;
   lsum = warp_sum(lsum);
   if (lane == 0) sloss[warp] = lsum;
-  __syncthreads();
-  if (warp == 0) {
-    float v = sloss[lane];
-    v = warp_sum(v);
-    if (lane == 0) loss[0] = v;
-  }
-  // ---- phase 2 ----
-  const int grp = tid >> 8, f = tid & 255;       // 4 groups x 256 feature slots
-  float wr[XH_MAXC], gw[XH_MAXC], gprev = 0.f;
-#pragma unroll
-  for (int c = 0; c < XH_MAXC; ++c) { wr[c] = (f < F && c < C) ? sw[f * C + c] : 0.f; gw[c] = 0.f; }
-  if (f < ldz || f < F) {
-    for (int b = grp; b < B; b += 4) {
-      float av = 0.f, g = 0.f;
-      if (f < F) {
-        av = a[(size_t)b * F + f];
-#pragma unroll
-        for (int c = 0; c < XH_MAXC; ++c)
-          if (c < C) { const float d = sd[b * C + c]; g = fmaf(d, wr[c], g); gw[c] = fmaf(av, d, gw[c]); }
-        if (relu_input && !(av > 0.f)) g = 0.f;
-        gprev += g;
-        if (da_f32 != nullptr) da_f32[(size_t)b * F + f] = g;
-      }
-      if (da_bf16 != nullptr && f < ldz) da_bf16[(size_t)b * ldz + f] = __float2bfloat16(g);
-    }
-  }
   if (f < F) {
     float* dst = sacc + ((size_t)grp * F + f) * (C + 1);
 #pragma unroll
@@ -116,17 +131,18 @@ __global__ void __launch_bounds__(XH_THREADS, 1) head_softmax_xent_kernel(
     dst[C] = gprev;
   }
   __syncthreads();
+  if (warp == 0) {
+    float v = sloss[lane];
+    v = warp_sum(v);
+    if (lane == 0) loss[0] = v;
+  }
   for (int i = tid; i < F * (C + 1); i += XH_THREADS) {
     const float v = sacc[i] + sacc[F * (C + 1) + i] + sacc[2 * F * (C + 1) + i] + sacc[3 * F * (C + 1) + i];
     const int ff = i / (C + 1), c = i - ff * (C + 1);
     if (c < C) dw[ff * C + c] = v;
     else if (dprev_bias != nullptr) dprev_bias[ff] = v;
   }
-  if (tid < C) {
-    float v = 0.f;
-    for (int b = 0; b < B; ++b) v += sd[b * C + tid];
-    db[tid] = v;
-  }
+  if (tid < C) db[tid] = sdb[tid];
 }
 
 // Dense(H -> O, linear) + MSE, forward AND backward, ONE CTA; every output is overwritten (no zeroing).
@@ -233,8 +249,10 @@ extern "C" int ddls_dense_softmax_xent(const float* a, const float* w, const flo
     return 1;
   }
   if (da_bf16 != nullptr && ldz > 256) { set_last_error("ddls_dense_softmax_xent: ldz must be <= 256"); return 1; }
-  const size_t smem = ((size_t)F * C + (size_t)B * C + 4 * (size_t)F * (C + 1)) * sizeof(float);
-  if (smem > 200 * 1024) { set_last_error("ddls_dense_softmax_xent: batch %d too large for the single-CTA head", B); return 1; }
+  size_t tail = (size_t)XH_ROWS * F;                       // staged rows; reused for the group partials
+  if (tail < 4 * (size_t)F * (C + 1)) tail = 4 * (size_t)F * (C + 1);
+  const size_t smem = ((size_t)F * C + (size_t)XH_ROWS * C + tail) * sizeof(float);
+  if (smem > 220 * 1024) { set_last_error("ddls_dense_softmax_xent: F*C too large for shared memory"); return 1; }
   DDLS_CUDA_OK(cudaFuncSetAttribute(head_softmax_xent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   head_softmax_xent_kernel<<<1, XH_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
       a, w, bias, onehot, probs, loss, da_f32, static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, B, F, C,
