@@ -60,13 +60,28 @@ __global__ void __launch_bounds__(256) conv1_relu_fwd_kernel(const float* __rest
 // stage the conv2 kernel (fp32 [tap][ci][co]) as an MN-major B image: k = tap*32+ci, n = co
 //   [K/8=36][N/8=4][8 k][8 n] bf16, LBO (k-group stride) = 512, SBO = 128
 DDLS_DEVINL void stage_w2_mnmajor(uint8_t* sB, const float* __restrict__ w2) {
-  for (int idx = threadIdx.x; idx < K2 * 4; idx += blockDim.x) {
-    const int blk = idx >> 5, ln = idx & 31;
-    const int k = blk * 8 + (ln & 7), ng = ln >> 3;
-    const float4* src = reinterpret_cast<const float4*>(w2 + (size_t)k * CH + ng * 8);
-    const float4 a = src[0], b = src[1];
-    *reinterpret_cast<uint4*>(sB + (k >> 3) * 512 + ng * 128 + (k & 7) * 16) =
-        make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  constexpr int ITER = (K2 * 4 + CT - 1) / CT;   // CT threads; loads batched ahead of the converts
+  float4 va[ITER], vb[ITER];
+#pragma unroll
+  for (int it = 0; it < ITER; ++it) {
+    const int idx = threadIdx.x + it * CT;
+    if (idx < K2 * 4) {
+      const int blk = idx >> 5, ln = idx & 31;
+      const int k = blk * 8 + (ln & 7), ng = ln >> 3;
+      const float4* src = reinterpret_cast<const float4*>(w2 + (size_t)k * CH + ng * 8);
+      va[it] = src[0]; vb[it] = src[1];
+    }
+  }
+#pragma unroll
+  for (int it = 0; it < ITER; ++it) {
+    const int idx = threadIdx.x + it * CT;
+    if (idx < K2 * 4) {
+      const int blk = idx >> 5, ln = idx & 31;
+      const int k = blk * 8 + (ln & 7), ng = ln >> 3;
+      *reinterpret_cast<uint4*>(sB + (k >> 3) * 512 + ng * 128 + (k & 7) * 16) =
+          make_uint4(pack_bf16x2(va[it].x, va[it].y), pack_bf16x2(va[it].z, va[it].w), pack_bf16x2(vb[it].x, vb[it].y),
+                     pack_bf16x2(vb[it].z, vb[it].w));
+    }
   }
 }
 
@@ -92,7 +107,11 @@ __global__ void __launch_bounds__(CT, 2) conv2_relu_pool_fwd_kernel(const __nv_b
   if (tid == 32) { mbar_init(&bar, 1); mbar_fence_init(); }
   stage_w2_mnmajor(sB, w2);
   // im2col gather: item = (k-chunk kc = tap*4 + cg, row m); 32 consecutive lanes write 512 contiguous bytes
-  for (int idx = tid; idx < 36 * 128; idx += CT) {
+  // (constant trip count + full unroll: every LDGSTS gets its own address registers, so the copies are
+  //  issued back to back instead of each waiting for the previous one to release its operands)
+#pragma unroll
+  for (int it = 0; it < 36 * 128 / CT; ++it) {
+    const int idx = tid + it * CT;
     const int m = idx & 127, kc = idx >> 7;
     const int tap = kc >> 2, cg = kc & 3, kh = tap / 3, kw = tap - kh * 3;
     const int P = p0 + (m >> 2), q = m & 3;
@@ -273,7 +292,9 @@ __global__ void __launch_bounds__(CT, 1) conv2_wgrad_kernel(const __nv_bfloat16*
     uint8_t* sB = sA + WG_A_STAGE;
     const int kk0 = k_begin + kb * WG_KB;
     // A gather: item = (m-group mg = tap*4 + cg, pixel k); 8 consecutive lanes -> 8 consecutive pixels (128 B)
-    for (int idx = tid; idx < 36 * WG_KB; idx += CT) {
+#pragma unroll
+    for (int it = 0; it < 36 * WG_KB / CT; ++it) {
+      const int idx = tid + it * CT;
       const int k = idx & (WG_KB - 1), mg = idx >> 6;
       const int tap = mg >> 2, cg = mg & 3, kh = tap / 3, kw = tap - kh * 3;
       const int pix = kk0 + k;
@@ -286,7 +307,8 @@ __global__ void __launch_bounds__(CT, 1) conv2_wgrad_kernel(const __nv_bfloat16*
       }
       cp_async16(sA + (k >> 3) * (48 * 128) + mg * 128 + (k & 7) * 16, src, nb);
     }
-    for (int idx = tid; idx < 4 * WG_KB; idx += CT) {   // dz2 rows are 64 contiguous bytes per pixel
+    {                                                  // dz2 rows are 64 contiguous bytes per pixel
+      const int idx = tid;
       const int k = idx & (WG_KB - 1), ng = idx >> 6;
       const int pix = kk0 + k;
       const bool ok = pix < k_end;
@@ -387,15 +409,33 @@ __global__ void __launch_bounds__(CT, 2) conv2_dgrad_relu_kernel(const __nv_bflo
   if (warp == 0) tmem_alloc(&tmem_s, 32);
   if (tid == 32) { mbar_init(&bar, 1); mbar_fence_init(); }
   // B image: element (n = ci, k = tap*32 + co) = W2[tap][ci][co]; vector = 8 consecutive co
-  for (int idx = tid; idx < 36 * CH; idx += CT) {
-    const int n = idx & 31, kc = idx >> 5;          // kc = tap*4 + cog
-    const int tap = kc >> 2, cog = kc & 3;
-    const float4* src = reinterpret_cast<const float4*>(w2 + ((size_t)tap * CH + n) * CH + cog * 8);
-    const float4 a = src[0], b = src[1];
-    *reinterpret_cast<uint4*>(sB + kc * 512 + n * 16) =
-        make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  {
+    constexpr int ITER = (36 * CH + CT - 1) / CT;
+    float4 va[ITER], vb[ITER];
+#pragma unroll
+    for (int it = 0; it < ITER; ++it) {
+      const int idx = tid + it * CT;
+      if (idx < 36 * CH) {
+        const int n = idx & 31, kc = idx >> 5;          // kc = tap*4 + cog
+        const int tap = kc >> 2, cog = kc & 3;
+        const float4* src = reinterpret_cast<const float4*>(w2 + ((size_t)tap * CH + n) * CH + cog * 8);
+        va[it] = src[0]; vb[it] = src[1];
+      }
+    }
+#pragma unroll
+    for (int it = 0; it < ITER; ++it) {
+      const int idx = tid + it * CT;
+      if (idx < 36 * CH) {
+        const int n = idx & 31, kc = idx >> 5;
+        *reinterpret_cast<uint4*>(sB + kc * 512 + n * 16) =
+            make_uint4(pack_bf16x2(va[it].x, va[it].y), pack_bf16x2(va[it].z, va[it].w), pack_bf16x2(vb[it].x, vb[it].y),
+                       pack_bf16x2(vb[it].z, vb[it].w));
+      }
+    }
   }
-  for (int idx = tid; idx < 36 * 128; idx += CT) {
+#pragma unroll
+  for (int it = 0; it < 36 * 128 / CT; ++it) {
+    const int idx = tid + it * CT;
     const int m = idx & 127, kc = idx >> 7;
     const int tap = kc >> 2, cog = kc & 3, kh = tap / 3, kw = tap - kh * 3;
     const int pix = m0 + m;

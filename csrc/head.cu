@@ -18,131 +18,134 @@ DDLS_DEVINL float warp_sum(float v) {
   return v;
 }
 
-// Dense(F -> C) + softmax + categorical cross-entropy, forward AND backward, one CTA of 1024 threads.
+// Dense(F -> C) + softmax + categorical cross-entropy, forward AND backward in one launch.
 //   a [B,F] fp32 (the previous layer's output), w [F,C], bias [C], onehot [B,C] (null => probabilities only)
-// outputs (all overwritten, nothing needs zeroing):
-//   probs [B,C] (optional), loss[1], dw [F,C], db [C],
-//   da: gradient w.r.t. `a` — fp32 [B,F] (da_f32) or bf16 [B,ldz] zero-padded (da_bf16);
-//   with relu_input the ReLU of the previous layer is folded in: da *= (a > 0), and dprev_bias[f] = sum_b da.
-// Phase 1: one warp per row computes logits / softmax / d = (p - y)/B into shared memory.
-// Phase 2: thread (group g, feature f) walks rows b = g, g+4, ... with w[f][:] in registers, producing da,
-//          and accumulating dw[f][:] and dprev_bias[f]; the four groups are combined through shared memory.
-constexpr int XH_THREADS = 1024;
+// Each CTA owns XH_ROWS batch rows: phase 1 (one warp per row) computes logits / softmax / d = (p - y)/B;
+// phase 2 (one thread per input feature, w[f][:] in registers) produces the gradient w.r.t. `a` and the
+// CTA's partial weight gradients, which are added to dw / db / dprev_bias with one atomic per element per
+// CTA (B/8 CTAs, so 16 adds per address at B = 128).  dw, db, dprev_bias must be zero on entry (they are
+// slices of the flat gradient buffer the optimizer kernel clears).  The loss is reduced without a
+// pre-zeroed output: CTAs write partial sums to `scratch` and the last CTA to arrive (self-resetting ticket
+// in scratch[0]) adds them up.  With relu_input the previous layer's ReLU is folded in (da *= a > 0).
+constexpr int XH_THREADS = 256;
 constexpr int XH_MAXC = 16;
-constexpr int XH_ROWS = 128;      // rows of `a` staged in shared memory per pass
-__global__ void __launch_bounds__(XH_THREADS, 1) head_softmax_xent_kernel(
+constexpr int XH_ROWS = 8;
+constexpr int XH_MAXF = 256;
+template <int CC>
+__global__ void __launch_bounds__(XH_THREADS) head_softmax_xent_kernel(
     const float* __restrict__ a, const float* __restrict__ w, const float* __restrict__ bias,
     const float* __restrict__ onehot, float* __restrict__ probs, float* __restrict__ loss, float* __restrict__ da_f32,
     __nv_bfloat16* __restrict__ da_bf16, int ldz, float* __restrict__ dw, float* __restrict__ db,
-    float* __restrict__ dprev_bias, int B, int F, int C, int relu_input) {
+    float* __restrict__ dprev_bias, float* __restrict__ scratch, int B, int F, int C, int relu_input) {
   extern __shared__ float sm[];
   float* sw = sm;                               // [F][C]
-  float* sd = sw + F * C;                       // [XH_ROWS][C]   dL/dlogits of the staged rows
-  float* sa = sd + XH_ROWS * C;                 // [XH_ROWS][F]   staged activations
-  float* sacc = sa;                             // [4][F][C+1] group partials, aliases sa after the last pass
-  __shared__ float sloss[32];
-  __shared__ float sdb[XH_MAXC];
+  float* sa = sw + F * C;                       // [XH_ROWS][F]
+  float* sd = sa + XH_ROWS * F;                 // [XH_ROWS][CC]
+  __shared__ float sloss[XH_THREADS / 32];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < F * C; i += XH_THREADS) sw[i] = w[i];
-  if (tid < XH_MAXC) sdb[tid] = 0.f;
+  const int r0 = blockIdx.x * XH_ROWS;
+  const int rows = min(XH_ROWS, B - r0);
+  {  // stage weights and this CTA's rows: loads batched ahead of the stores
+    const int nW = F * C, nA = rows * F;
+    const float* asrc = a + (size_t)r0 * F;
+    constexpr int IT = (XH_MAXF * XH_MAXC + XH_ROWS * XH_MAXF + XH_THREADS - 1) / XH_THREADS;
+    float v[IT];
+#pragma unroll
+    for (int it = 0; it < IT; ++it) {
+      const int i = tid + it * XH_THREADS;
+      v[it] = i < nW ? w[i] : (i - nW < nA ? asrc[i - nW] : 0.f);
+    }
+#pragma unroll
+    for (int it = 0; it < IT; ++it) {
+      const int i = tid + it * XH_THREADS;
+      if (i < nW + nA) sm[i < nW ? i : (F * C + (i - nW))] = v[it];
+    }
+  }
+  __syncthreads();
   const float invB = 1.0f / (float)B;
   float lsum = 0.f;
-  const int grp = tid >> 8, f = tid & 255;       // phase 2: 4 row groups x 256 feature slots
-  float wr[XH_MAXC], gw[XH_MAXC], gprev = 0.f;
-  __syncthreads();
+  if (warp < rows) {
+    const int b = r0 + warp;
+    float z[CC];
 #pragma unroll
-  for (int c = 0; c < XH_MAXC; ++c) { wr[c] = (f < F && c < C) ? sw[f * C + c] : 0.f; gw[c] = 0.f; }
-
-  for (int r0 = 0; r0 < B; r0 += XH_ROWS) {
-    const int rows = min(XH_ROWS, B - r0);
-    // stage rows [r0, r0+rows) of a: coalesced, many independent loads in flight per thread
-    const float* src = a + (size_t)r0 * F;
-#pragma unroll 8
-    for (int i = tid; i < rows * F; i += XH_THREADS) sa[i] = src[i];
-    __syncthreads();
-    // ---- phase 1: one warp per row -> logits, softmax, d = (p - y)/B ----
-    for (int rb = warp; rb < rows; rb += XH_THREADS / 32) {
-      const int b = r0 + rb;
-      float z[XH_MAXC];
+    for (int c = 0; c < CC; ++c) z[c] = 0.f;
+    for (int ff = lane; ff < F; ff += 32) {
+      const float av = sa[warp * F + ff];
 #pragma unroll
-      for (int c = 0; c < XH_MAXC; ++c) z[c] = 0.f;
-      for (int ff = lane; ff < F; ff += 32) {
-        const float av = sa[rb * F + ff];
+      for (int c = 0; c < CC; ++c)
+        if (CC == 10 || c < C) z[c] = fmaf(av, sw[ff * C + c], z[c]);
+    }
+    float mx = -INFINITY;
 #pragma unroll
-        for (int c = 0; c < XH_MAXC; ++c)
-          if (c < C) z[c] = fmaf(av, sw[ff * C + c], z[c]);
-      }
-      float mx = -INFINITY;
+    for (int c = 0; c < CC; ++c)
+      if (CC == 10 || c < C) { z[c] = warp_sum(z[c]) + bias[c]; mx = fmaxf(mx, z[c]); }
+    float ssum = 0.f;
 #pragma unroll
-      for (int c = 0; c < XH_MAXC; ++c)
-        if (c < C) { z[c] = warp_sum(z[c]) + bias[c]; mx = fmaxf(mx, z[c]); }
-      float ssum = 0.f;
+    for (int c = 0; c < CC; ++c)
+      if (CC == 10 || c < C) { z[c] = __expf(z[c] - mx); ssum += z[c]; }
+    const float inv = 1.0f / ssum;
 #pragma unroll
-      for (int c = 0; c < XH_MAXC; ++c)
-        if (c < C) { z[c] = __expf(z[c] - mx); ssum += z[c]; }
-      const float inv = 1.0f / ssum;
-#pragma unroll
-      for (int c = 0; c < XH_MAXC; ++c) {
-        if (c < C && lane == c) {
-          const float pr = z[c] * inv;
-          if (probs != nullptr) probs[(size_t)b * C + c] = pr;
-          if (onehot != nullptr) {
-            const float yv = onehot[(size_t)b * C + c];
-            sd[rb * C + c] = (pr - yv) * invB;
-            // Keras clips probabilities to [1e-7, 1-1e-7] inside the log
-            lsum += -yv * __logf(fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f)) * invB;
-          }
+    for (int c = 0; c < CC; ++c) {
+      if ((CC == 10 || c < C) && lane == c) {
+        const float pr = z[c] * inv;
+        if (probs != nullptr) probs[(size_t)b * C + c] = pr;
+        if (onehot != nullptr) {
+          const float yv = onehot[(size_t)b * C + c];
+          sd[warp * CC + c] = (pr - yv) * invB;
+          // Keras clips probabilities to [1e-7, 1-1e-7] inside the log
+          lsum = -yv * __logf(fminf(fmaxf(pr, 1e-7f), 1.f - 1e-7f)) * invB;
         }
       }
     }
-    if (onehot == nullptr) { __syncthreads(); continue; }
-    __syncthreads();
-    // ---- phase 2: thread (group, feature) walks its rows; w[f][:] lives in registers ----
-    if (f < ldz || f < F) {
-      for (int rb = grp; rb < rows; rb += 4) {
-        float g = 0.f;
-        if (f < F) {
-          const float av = sa[rb * F + f];
-#pragma unroll
-          for (int c = 0; c < XH_MAXC; ++c)
-            if (c < C) { const float d = sd[rb * C + c]; g = fmaf(d, wr[c], g); gw[c] = fmaf(av, d, gw[c]); }
-          if (relu_input && !(av > 0.f)) g = 0.f;
-          gprev += g;
-          if (da_f32 != nullptr) da_f32[(size_t)(r0 + rb) * F + f] = g;
-        }
-        if (da_bf16 != nullptr && f < ldz) da_bf16[(size_t)(r0 + rb) * ldz + f] = __float2bfloat16(g);
-      }
-    }
-    if (tid < C) {
-      float v = 0.f;
-      for (int rb = 0; rb < rows; ++rb) v += sd[rb * C + tid];
-      sdb[tid] += v;
-    }
-    __syncthreads();
   }
   if (onehot == nullptr) return;
   lsum = warp_sum(lsum);
   if (lane == 0) sloss[warp] = lsum;
-  if (f < F) {
-    float* dst = sacc + ((size_t)grp * F + f) * (C + 1);
-#pragma unroll
-    for (int c = 0; c < XH_MAXC; ++c)
-      if (c < C) dst[c] = gw[c];
-    dst[C] = gprev;
-  }
   __syncthreads();
-  if (warp == 0) {
-    float v = sloss[lane];
-    v = warp_sum(v);
-    if (lane == 0) loss[0] = v;
+  // ---- phase 2: thread = input feature ----
+  const int f = tid;
+  if (f < F) {
+    float wr[CC], gw[CC], gprev = 0.f;
+#pragma unroll
+    for (int c = 0; c < CC; ++c) { wr[c] = (CC == 10 || c < C) ? sw[f * C + c] : 0.f; gw[c] = 0.f; }
+    for (int rb = 0; rb < rows; ++rb) {
+      const float av = sa[rb * F + f];
+      float g = 0.f;
+#pragma unroll
+      for (int c = 0; c < CC; ++c)
+        if (CC == 10 || c < C) { const float d = sd[rb * CC + c]; g = fmaf(d, wr[c], g); gw[c] = fmaf(av, d, gw[c]); }
+      if (relu_input && !(av > 0.f)) g = 0.f;
+      gprev += g;
+      if (da_f32 != nullptr) da_f32[(size_t)(r0 + rb) * F + f] = g;
+      if (da_bf16 != nullptr) da_bf16[(size_t)(r0 + rb) * ldz + f] = __float2bfloat16(g);
+    }
+#pragma unroll
+    for (int c = 0; c < CC; ++c)
+      if (CC == 10 || c < C) atomicAdd(dw + f * C + c, gw[c]);
+    if (dprev_bias != nullptr) atomicAdd(dprev_bias + f, gprev);
+  } else if (da_bf16 != nullptr && f < ldz) {
+    for (int rb = 0; rb < rows; ++rb) da_bf16[(size_t)(r0 + rb) * ldz + f] = __float2bfloat16(0.f);   // padding columns
   }
-  for (int i = tid; i < F * (C + 1); i += XH_THREADS) {
-    const float v = sacc[i] + sacc[F * (C + 1) + i] + sacc[2 * F * (C + 1) + i] + sacc[3 * F * (C + 1) + i];
-    const int ff = i / (C + 1), c = i - ff * (C + 1);
-    if (c < C) dw[ff * C + c] = v;
-    else if (dprev_bias != nullptr) dprev_bias[ff] = v;
+  if (tid < C) {
+    float v = 0.f;
+    for (int rb = 0; rb < rows; ++rb) v += sd[rb * CC + tid];
+    atomicAdd(db + tid, v);
   }
-  if (tid < C) db[tid] = sdb[tid];
+  // loss: per-CTA partial -> scratch[1 + block]; last CTA (ticket in scratch[0]) sums in block order
+  if (tid == 0) {
+    float v = 0.f;
+    for (int i = 0; i < XH_THREADS / 32; ++i) v += sloss[i];
+    scratch[1 + blockIdx.x] = v;
+    __threadfence();
+    const unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(scratch), 1u);
+    if (ticket == gridDim.x - 1) {
+      __threadfence();
+      float t = 0.f;
+      for (unsigned i = 0; i < gridDim.x; ++i) t += reinterpret_cast<volatile float*>(scratch)[1 + i];
+      loss[0] = t;
+      *reinterpret_cast<unsigned*>(scratch) = 0u;
+    }
+  }
 }
 
 // Dense(H -> O, linear) + MSE, forward AND backward, ONE CTA; every output is overwritten (no zeroing).
@@ -242,21 +245,28 @@ extern "C" int ddls_dense_mse(const float* h, const float* wd, const float* bd, 
 
 extern "C" int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, const float* onehot,
                                        float* probs, float* loss, float* da_f32, void* da_bf16, int ldz, float* dw,
-                                       float* db, float* dprev_bias, int B, int F, int C, int relu_input, void* stream) {
+                                       float* db, float* dprev_bias, float* scratch, int B, int F, int C,
+                                       int relu_input, void* stream) {
   if (B <= 0) return 0;
-  if (C > XH_MAXC || C < 1 || F > 256) {
+  if (C > XH_MAXC || C < 1 || F > XH_MAXF) {
     set_last_error("ddls_dense_softmax_xent: supports C <= 16 and F <= 256 (got C=%d F=%d)", C, F);
     return 1;
   }
-  if (da_bf16 != nullptr && ldz > 256) { set_last_error("ddls_dense_softmax_xent: ldz must be <= 256"); return 1; }
-  size_t tail = (size_t)XH_ROWS * F;                       // staged rows; reused for the group partials
-  if (tail < 4 * (size_t)F * (C + 1)) tail = 4 * (size_t)F * (C + 1);
-  const size_t smem = ((size_t)F * C + (size_t)XH_ROWS * C + tail) * sizeof(float);
-  if (smem > 220 * 1024) { set_last_error("ddls_dense_softmax_xent: F*C too large for shared memory"); return 1; }
-  DDLS_CUDA_OK(cudaFuncSetAttribute(head_softmax_xent_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  head_softmax_xent_kernel<<<1, XH_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
-      a, w, bias, onehot, probs, loss, da_f32, static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, B, F, C,
-      relu_input);
+  if (da_bf16 != nullptr && ldz > XH_MAXF) { set_last_error("ddls_dense_softmax_xent: ldz must be <= 256"); return 1; }
+  const int blocks = (B + XH_ROWS - 1) / XH_ROWS;
+  if (onehot != nullptr && scratch == nullptr) {
+    set_last_error("ddls_dense_softmax_xent: training needs %d floats of zero-initialised scratch", blocks + 1);
+    return 1;
+  }
+  const int CCsel = (C == 10) ? 10 : XH_MAXC;
+  const size_t smem = ((size_t)F * C + (size_t)XH_ROWS * F + (size_t)XH_ROWS * CCsel) * sizeof(float);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (C == 10)
+    head_softmax_xent_kernel<10><<<blocks, XH_THREADS, smem, st>>>(a, w, bias, onehot, probs, loss, da_f32,
+        static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, scratch, B, F, C, relu_input);
+  else
+    head_softmax_xent_kernel<XH_MAXC><<<blocks, XH_THREADS, smem, st>>>(a, w, bias, onehot, probs, loss, da_f32,
+        static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, scratch, B, F, C, relu_input);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "head_softmax_xent_kernel launch");
 }

@@ -250,7 +250,10 @@ constexpr int V2_STAGES = 4;
 template <int ROWS>
 DDLS_DEVINL void cpasync_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int row0, int nrows, int k0, int kend) {
   constexpr int KCH = GEMM_KC / 8;
-  for (int idx = threadIdx.x; idx < ROWS * KCH; idx += V2_THREADS) {
+  static_assert((ROWS * KCH) % V2_THREADS == 0, "tile must divide evenly over the CTA");
+#pragma unroll
+  for (int it = 0; it < ROWS * KCH / V2_THREADS; ++it) {
+    const int idx = threadIdx.x + it * V2_THREADS;
     const int blk = idx >> 5, lane = idx & 31;
     const int rblk = blk % (ROWS / 8), kblk = blk / (ROWS / 8);
     const int r = rblk * 8 + (lane & 7), kc = kblk * 4 + (lane >> 3);
@@ -263,7 +266,10 @@ DDLS_DEVINL void cpasync_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, i
 template <int COLS>
 DDLS_DEVINL void cpasync_mnmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int col0, int ncols, int k0, int kend) {
   constexpr int MNG = COLS / 8;
-  for (int idx = threadIdx.x; idx < GEMM_KC * MNG; idx += V2_THREADS) {
+  static_assert((GEMM_KC * MNG) % V2_THREADS == 0, "tile must divide evenly over the CTA");
+#pragma unroll
+  for (int it = 0; it < GEMM_KC * MNG / V2_THREADS; ++it) {
+    const int idx = threadIdx.x + it * V2_THREADS;
     const int blk = idx >> 5, lane = idx & 31;
     const int gblk = blk % (MNG / 4), kblk = blk / (MNG / 4);
     const int mng = gblk * 4 + (lane >> 3), k = kblk * 8 + (lane & 7);

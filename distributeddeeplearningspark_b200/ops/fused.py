@@ -155,8 +155,11 @@ class DirectStep:
         flat = pooled.view(B, 4608)
         w1s = self.w1s[:, :F]
         gemm_bf16(flat, w1s, bias=d1.bias, relu=True, b_mn_major=True, split_k=C.FWD_SPLIT_K, out=a3)
+        scr = self._bufs.get(('head_scratch', B))
+        if scr is None:
+            scr = self._bufs[('head_scratch', B)] = heads.softmax_xent_scratch(B, self.dev)
         heads.softmax_xent_raw(a3, d2.kernel, d2.bias, y.contiguous(), None, loss, None, dz3, ld, d2.kernel.grad,
-                               d2.bias.grad, d1.bias.grad, True)
+                               d2.bias.grad, d1.bias.grad, True, scr)
         gemm_bf16(flat, dz3[:, :F], a_mn_major=True, b_mn_major=True, out=d1.kernel.grad)
         gemm_bf16(dz3[:, :F], w1s, out=dflat)
         N.call('ddls_cnn_unpool_bwd', dflat.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), dz2.data_ptr(),

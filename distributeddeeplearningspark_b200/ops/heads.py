@@ -8,7 +8,7 @@ from .. import _native as N
 
 P, I = N.c_void_p, N.c_int
 N.register('ddls_dense_mse', [P, P, P, P, P, P, P, P, P, I, I, I, P])
-N.register('ddls_dense_softmax_xent', [P, P, P, P, P, P, P, P, I, P, P, P, I, I, I, I, P])
+N.register('ddls_dense_softmax_xent', [P, P, P, P, P, P, P, P, I, P, P, P, P, I, I, I, I, P])
 
 _UNIT_SEED = [False]
 
@@ -32,11 +32,17 @@ def dense_mse_raw(h, w, b, y, pred, loss, dh, dw, db):
            N.ptr(dh), N.ptr(dw), N.ptr(db), B, Hd, w.shape[1], N.stream_ptr(h.device))
 
 
-def softmax_xent_raw(a, w, b, onehot, probs, loss, da_f32, da_bf16, ldz, dw, db, dprev_bias, relu_input):
+def softmax_xent_scratch(B: int, device) -> torch.Tensor:
+    """Zero-initialised scratch for the head kernel (arrival ticket + per-CTA loss partials); reusable across calls."""
+    return torch.zeros((B + 7) // 8 + 2, dtype=torch.float32, device=device)
+
+
+def softmax_xent_raw(a, w, b, onehot, probs, loss, da_f32, da_bf16, ldz, dw, db, dprev_bias, relu_input, scratch=None):
+    """dw / db / dprev_bias are accumulated into (must be zero on entry); everything else is overwritten."""
     B, F = a.shape
     N.call('ddls_dense_softmax_xent', a.data_ptr(), w.data_ptr(), b.data_ptr(), N.ptr(onehot), N.ptr(probs),
-           N.ptr(loss), N.ptr(da_f32), N.ptr(da_bf16), int(ldz), N.ptr(dw), N.ptr(db), N.ptr(dprev_bias), B, F,
-           w.shape[1], int(relu_input), N.stream_ptr(a.device))
+           N.ptr(loss), N.ptr(da_f32), N.ptr(da_bf16), int(ldz), N.ptr(dw), N.ptr(db), N.ptr(dprev_bias),
+           N.ptr(scratch), B, F, w.shape[1], int(relu_input), N.stream_ptr(a.device))
 
 
 class _DenseMSE(torch.autograd.Function):
@@ -84,11 +90,12 @@ class _DenseSoftmaxXent(torch.autograd.Function):
         C = w.shape[1]
         dev = a.device
         a = a.contiguous(); onehot = onehot.contiguous()
-        buf = torch.empty(1 + F * C + C, dtype=torch.float32, device=dev)
-        loss, dw, db = buf[0:1], buf[1:1 + F * C].view(F, C), buf[1 + F * C:]
+        nscr = (B + 7) // 8 + 2
+        buf = torch.zeros(1 + F * C + C + nscr, dtype=torch.float32, device=dev)
+        loss, dw, db = buf[0:1], buf[1:1 + F * C].view(F, C), buf[1 + F * C:1 + F * C + C]
         probs = torch.empty((B, C), dtype=torch.float32, device=dev)
         da = torch.empty_like(a)
-        softmax_xent_raw(a, w, b, onehot, probs, loss, da, None, 0, dw, db, None, False)
+        softmax_xent_raw(a, w, b, onehot, probs, loss, da, None, 0, dw, db, None, False, buf[1 + F * C + C:])
         ctx.save_for_backward(da, dw, db)
         ctx.mark_non_differentiable(probs)
         return loss.reshape(()), probs

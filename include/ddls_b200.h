@@ -95,11 +95,14 @@ int ddls_gru128_backward(const float* dout, const float* x, const float* w_hh, c
 int ddls_dense_mse(const float* h, const float* wd, const float* bd, const float* y, float* pred, float* loss,
                    float* dh, float* dwd, float* dbd, int B, int H, int O, void* stream);
 /* Dense(F->C) + softmax + categorical_crossentropy (ddl_mnist_aztk.py:191-196).  onehot == NULL:
- * probabilities only.  One CTA; outputs overwritten.  da: fp32 [B,F] and/or bf16 [B,ldz] (zero padded).
- * relu_input != 0 folds the previous layer's ReLU in (da *= a > 0) and emits its bias gradient dprev_bias [F]. */
+ * probabilities only.  B/8 CTAs; dw [F,C], db [C], dprev_bias [F] are ACCUMULATED (caller zeroes; they are
+ * slices of the flat gradient buffer).  loss[1], probs, da are overwritten.  da: fp32 [B,F] and/or bf16
+ * [B,ldz] (zero padded).  relu_input folds the previous layer's ReLU in and emits its bias gradient.
+ * scratch: (B/8 + 2) floats, zero-initialised ONCE by the caller (holds a self-resetting arrival ticket
+ * and the per-CTA loss partials). */
 int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, const float* onehot, float* probs,
                             float* loss, float* da_f32, void* da_bf16, int ldz, float* dw, float* db,
-                            float* dprev_bias, int B, int F, int C, int relu_input, void* stream);
+                            float* dprev_bias, float* scratch, int B, int F, int C, int relu_input, void* stream);
 
 /* ---- MNIST CNN trunk (/root/reference/ddl_mnist_aztk.py:180-190), NHWC, Keras kernel layouts --------
  * conv1+ReLU: x [B,28,28,1] fp32 -> a1 [B,26,26,32] bf16. */
