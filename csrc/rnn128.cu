@@ -1,0 +1,544 @@
+// Persistent recurrent kernels, second generation (LSTM(128) / GRU(128), input dim 1).
+//
+// Same "weights on M, batch on N" tcgen05 design as csrc/lstm.cu / csrc/gru.cu (which remain as the
+// first-generation reference implementation), re-engineered after profiling showed the step loop was
+// bound by instruction count and exposed global latency, not by the tensor pipe:
+//   * the recurrent weights, the input kernel and the bias are packed ONCE per optimizer step into a bf16
+//     UMMA image (ddls_rnn128_pack) that every CTA pulls into shared memory with one bulk TMA copy
+//     (cp.async.bulk -> UBLKCP) — the same bytes serve the forward (MN-major A) and the BPTT (K-major A);
+//   * the rank-1 input projection and the bias ride in the MMA as one extra K = 16 step: A rows
+//     [w_hi, w_lo, b_hi, b_lo, w_hi], B rows [x_hi, x_hi, 1, 1, x_lo] (hi/lo bf16 splits keep ~fp32 accuracy),
+//     so the epilogue is only the gate non-linearities (hard_sigmoid = one FFMA.SAT);
+//   * 512 threads per CTA (4 TMEM lane quarters x 4 column groups) for latency hiding;
+//   * everything saved for BPTT is laid out per thread as 8 consecutive batch rows (16/32-byte vector
+//     stores, coalesced across the hidden-unit lanes); h_t and dz_t are stored directly as K-major UMMA
+//     images, so the recurrent weight-gradient GEMM (ddls_rnn128_wgrad) streams them with bulk TMA copies
+//     through a 4-stage mbarrier pipeline with a dedicated producer thread — no staging pass at all.
+// Keras semantics as in the first generation: LSTM gates i,f,c,o, GRU gates z,r,h with reset applied
+// before the recurrent matmul (/root/reference/ddl_nyiso_aztk.py:201-203,249-251).
+#include "common.cuh"
+#include "../include/ddls_b200.h"
+
+namespace ddls {
+
+constexpr int RH = 128;             // hidden units
+constexpr int RT = 512;             // threads per CTA
+constexpr int R_KG = 18;            // k-groups in the weight image: 16 (hidden) + 1 (input/bias rows) + 1 (zeros)
+
+// image element (k, m): ((k>>3) * (GH/8) + (m>>3)) * 64 + (k&7)*8 + (m&7)   [bf16 elements]
+__global__ void __launch_bounds__(256) rnn128_pack_kernel(const float* __restrict__ rec, const float* __restrict__ wih,
+                                                          const float* __restrict__ bias, __nv_bfloat16* __restrict__ img,
+                                                          int GH) {
+  const int MG = GH / 8;
+  const int total = R_KG * MG * 8;                  // one item = (k, m-group): 8 consecutive m
+  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+    const int kr = idx & 7, mg = (idx >> 3) % MG, kg = idx / (8 * MG);
+    const int k = kg * 8 + kr;
+    float v[8];
+    if (k < RH) {
+      const float4* s = reinterpret_cast<const float4*>(rec + (size_t)k * GH + mg * 8);
+      const float4 a = s[0], b = s[1];
+      v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+    } else {
+      const int row = k - RH;                       // 0: w_hi 1: w_lo 2: b_hi 3: b_lo 4: w_hi, else 0
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float w = wih[mg * 8 + e], bb = bias[mg * 8 + e];
+        const float whi = __bfloat162float(__float2bfloat16(w)), bhi = __bfloat162float(__float2bfloat16(bb));
+        v[e] = (row == 0 || row == 4) ? whi : row == 1 ? (w - whi) : row == 2 ? bhi : row == 3 ? (bb - bhi) : 0.f;
+      }
+    }
+    *reinterpret_cast<uint4*>(img + ((size_t)(kg * MG + mg) * 64 + kr * 8)) =
+        make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+}
+
+// x image for the extra K step: per time step one k-group [NB/8][8 k][8 n]: rows x_hi, x_hi, 1, 1, x_lo, 0, 0, 0
+template <int NB>
+DDLS_DEVINL void build_x_image(uint8_t* sX, uint8_t* sZero, const float* __restrict__ x, int b0, int B, int T) {
+  for (int idx = threadIdx.x; idx < T * NB; idx += RT) {
+    const int t = idx / NB, b = idx - t * NB;
+    const float xv = (b0 + b < B) ? x[(size_t)(b0 + b) * T + t] : 0.f;
+    const __nv_bfloat16 hi = __float2bfloat16(xv);
+    const __nv_bfloat16 lo = __float2bfloat16(xv - __bfloat162float(hi));
+    const __nv_bfloat16 one = __float2bfloat16(1.f), zero = __float2bfloat16(0.f);
+    __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(sX + (size_t)t * (NB * 16) + (b >> 3) * 128) + (b & 7);
+    g[0 * 8] = hi; g[1 * 8] = hi; g[2 * 8] = one; g[3 * 8] = one; g[4 * 8] = lo; g[5 * 8] = zero; g[6 * 8] = zero; g[7 * 8] = zero;
+  }
+  for (int idx = threadIdx.x; idx < NB * 16 / 16; idx += RT) reinterpret_cast<uint4*>(sZero)[idx] = make_uint4(0, 0, 0, 0);
+}
+
+struct LstmV2Fwd {
+  const float* x;                 // [B, T]
+  const __nv_bfloat16* img;       // packed weights [18][64][8][8]
+  float* out;                     // [B, H] or [B, T, H]
+  uint4* hs;                      // [T][B8][128] x 16 B   (8 batch rows of h_t, bf16)  == K-major UMMA image
+  uint4* gates;                   // [T][B8][4][128] x 16 B (post-activation i,f,g,o, bf16)
+  float4* cs;                     // [T][B8][128] x 32 B   (c_t, fp32)
+  int B, T, B8;
+  int return_sequences, save;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(RT, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int GH = 4 * RH, MG = GH / 8;
+  constexpr uint32_t W_LBO = MG * 128;                       // 8192: k-group stride of the image
+  constexpr int W_BYTES = R_KG * MG * 128;                   // 147,456
+  constexpr int CH8 = NB / 32;                               // 8-column chunks per thread
+  uint8_t* sW = smem;
+  uint8_t* sH = sW + W_BYTES;                                // [16][NB/8][8][8] bf16
+  uint8_t* sX = sH + RH * NB * 2;                            // [T][NB*16 B]
+  uint8_t* sZero = sX + (size_t)p.T * NB * 16;               // one zero k-group
+  __shared__ uint64_t bar_w, bar_mma;
+  __shared__ uint32_t tmem_s;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q = warp & 3, cgp = warp >> 2;                   // TMEM lane quarter, column group (0..3)
+  const int j = q * 32 + lane;
+  const int b0 = blockIdx.x * NB;
+  const int T = p.T, B = p.B;
+
+  if (warp == 0) tmem_alloc(&tmem_s, 4 * NB);
+  if (tid == 32) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
+  __syncthreads();
+  if (tid == 0) {                                            // one bulk TMA copy brings the whole weight image
+    mbar_expect_tx(&bar_w, W_BYTES);
+#pragma unroll
+    for (int c = 0; c < R_KG; ++c)
+      tma_bulk_g2s(sW + c * (MG * 128), reinterpret_cast<const uint8_t*>(p.img) + (size_t)c * (MG * 128), MG * 128, &bar_w);
+  }
+  build_x_image<NB>(sX, sZero, p.x, b0, B, T);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_s;
+  const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+  constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
+  const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), x_base = smem_u32(sX), z_base = smem_u32(sZero);
+  if (tid == 0) mbar_wait(&bar_w, 0);
+
+  float c[CH8 * 8];
+#pragma unroll
+  for (int i = 0; i < CH8 * 8; ++i) c[i] = 0.f;
+  uint32_t phase = 0;
+  for (int t = 0; t < T; ++t) {
+    if (tid == 0) {
+      tc_fence_after();
+      const uint32_t xt = x_base + t * (NB * 16);
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        if (t > 0) {
+#pragma unroll
+          for (int ks = 0; ks < RH / 16; ++ks)
+            umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
+                      umma_desc(h_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+        }
+        // input projection + bias: k-groups 16 (payload) and 17 (zeros) of the image x [x rows | zero group]
+        umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + 16 * W_LBO, W_LBO, 128),
+                  umma_desc(xt, z_base - xt, 128), idesc, t > 0);
+      }
+      umma_commit(&bar_mma);
+    }
+    mbar_wait(&bar_mma, phase);
+    phase ^= 1;
+    tc_fence_after();
+    const bool last = (t == T - 1);
+#pragma unroll
+    for (int ch = 0; ch < CH8; ++ch) {
+      const int col0 = (cgp * CH8 + ch) * 8;
+      uint32_t vi[8], vf[8], vg[8], vo[8];
+      tmem_ld8(t_lane + 0 * NB + col0, vi);
+      tmem_ld8(t_lane + 1 * NB + col0, vf);
+      tmem_ld8(t_lane + 2 * NB + col0, vg);
+      tmem_ld8(t_lane + 3 * NB + col0, vo);
+      tmem_ld_wait();
+      float gi[8], gf[8], gg[8], go[8], hv[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        gi[e] = __saturatef(fmaf(0.2f, __uint_as_float(vi[e]), 0.5f));
+        gf[e] = __saturatef(fmaf(0.2f, __uint_as_float(vf[e]), 0.5f));
+        gg[e] = fast_tanh(__uint_as_float(vg[e]));
+        go[e] = __saturatef(fmaf(0.2f, __uint_as_float(vo[e]), 0.5f));
+        const float cn = fmaf(gf[e], c[ch * 8 + e], gi[e] * gg[e]);
+        c[ch * 8 + e] = cn;
+        hv[e] = go[e] * fast_tanh(cn);
+      }
+      const uint4 h16 = make_uint4(pack_bf16x2(hv[0], hv[1]), pack_bf16x2(hv[2], hv[3]), pack_bf16x2(hv[4], hv[5]),
+                                   pack_bf16x2(hv[6], hv[7]));
+      if (!last) *reinterpret_cast<uint4*>(sH + (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16) = h16;
+      const int bc = (b0 + col0) >> 3;                      // global 8-row chunk index
+      if (bc < p.B8) {
+        if (p.save) {
+          const size_t base = (size_t)t * p.B8 + bc;
+          p.hs[base * RH + j] = h16;
+          uint4* gd = p.gates + base * 4 * RH + j;
+          gd[0 * RH] = make_uint4(pack_bf16x2(gi[0], gi[1]), pack_bf16x2(gi[2], gi[3]), pack_bf16x2(gi[4], gi[5]), pack_bf16x2(gi[6], gi[7]));
+          gd[1 * RH] = make_uint4(pack_bf16x2(gf[0], gf[1]), pack_bf16x2(gf[2], gf[3]), pack_bf16x2(gf[4], gf[5]), pack_bf16x2(gf[6], gf[7]));
+          gd[2 * RH] = make_uint4(pack_bf16x2(gg[0], gg[1]), pack_bf16x2(gg[2], gg[3]), pack_bf16x2(gg[4], gg[5]), pack_bf16x2(gg[6], gg[7]));
+          gd[3 * RH] = make_uint4(pack_bf16x2(go[0], go[1]), pack_bf16x2(go[2], go[3]), pack_bf16x2(go[4], go[5]), pack_bf16x2(go[6], go[7]));
+          float4* cd = p.cs + (base * RH + j) * 2;
+          cd[0] = make_float4(c[ch * 8 + 0], c[ch * 8 + 1], c[ch * 8 + 2], c[ch * 8 + 3]);
+          cd[1] = make_float4(c[ch * 8 + 4], c[ch * 8 + 5], c[ch * 8 + 6], c[ch * 8 + 7]);
+        }
+        if (p.return_sequences || last) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int bg = b0 + col0 + e;
+            if (bg < B) {
+              if (p.return_sequences) p.out[((size_t)bg * T + t) * RH + j] = hv[e];
+              else p.out[(size_t)bg * RH + j] = hv[e];
+            }
+          }
+        }
+      }
+    }
+    if (!last) {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncthreads();
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 4 * NB);
+}
+
+struct LstmV2Bwd {
+  const float* dout;              // [B, H] or [B, T, H]
+  const float* x;                 // [B, T]
+  const __nv_bfloat16* img;
+  const uint4* gates;             // [T][B8][4][128]
+  const float4* cs;               // [T][B8][128] x 2
+  uint4* dz;                      // [T][B8][512] x 16 B  == K-major UMMA image (N = gate column)
+  float* d_wih;                   // [4H] atomic accumulate
+  float* d_bias;                  // [4H]
+  int B, T, B8;
+  int return_sequences;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(RT, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int GH = 4 * RH, MG = GH / 8;
+  constexpr int W_BYTES = 16 * MG * 128;                     // hidden k-groups only: 131,072
+  constexpr int CH8 = NB / 32;
+  uint8_t* sW = smem;                                        // image: as K-major A, LBO = 128, SBO = MG*128
+  uint8_t* sZ = sW + W_BYTES;                                // dz MN-major B: [64 k-groups][NB/8][8][8]
+  float* sX = reinterpret_cast<float*>(sZ + GH * NB * 2);    // [NB][T]
+  __shared__ uint64_t bar_w, bar_mma;
+  __shared__ uint32_t tmem_s;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int q = warp & 3, cgp = warp >> 2;
+  const int j = q * 32 + lane;
+  const int b0 = blockIdx.x * NB;
+  const int T = p.T, B = p.B;
+  constexpr uint32_t TM_COLS = NB < 32 ? 32 : NB;
+
+  if (warp == 0) tmem_alloc(&tmem_s, TM_COLS);
+  if (tid == 32) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
+  __syncthreads();
+  if (tid == 0) {
+    mbar_expect_tx(&bar_w, W_BYTES);
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      tma_bulk_g2s(sW + c * (MG * 128), reinterpret_cast<const uint8_t*>(p.img) + (size_t)c * (MG * 128), MG * 128, &bar_w);
+  }
+  for (int idx = tid; idx < NB * T; idx += RT) {
+    const int b = idx / T, t = idx - b * T;
+    sX[idx] = (b0 + b < B) ? p.x[(size_t)(b0 + b) * T + t] : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_s;
+  const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+  constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
+  const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
+  if (tid == 0) mbar_wait(&bar_w, 0);
+
+  float dc[CH8 * 8];
+#pragma unroll
+  for (int i = 0; i < CH8 * 8; ++i) dc[i] = 0.f;
+  float acc_w[4] = {0.f, 0.f, 0.f, 0.f}, acc_b[4] = {0.f, 0.f, 0.f, 0.f};
+  uint32_t phase = 0;
+  for (int t = T - 1; t >= 0; --t) {
+    const bool have_dh = (t < T - 1);
+    // ---- issue this step's loads before waiting on the tensor pipe (they do not depend on it) ----
+    uint4 g4[CH8][4];
+    float4 ct[CH8][2], cp[CH8][2];
+    float dext[CH8][8];
+    bool live[CH8];
+#pragma unroll
+    for (int ch = 0; ch < CH8; ++ch) {
+      const int col0 = (cgp * CH8 + ch) * 8;
+      const int bc = (b0 + col0) >> 3;
+      live[ch] = bc < p.B8;
+      if (live[ch]) {
+        const size_t base = (size_t)t * p.B8 + bc;
+        const uint4* gs = p.gates + base * 4 * RH + j;
+        g4[ch][0] = gs[0]; g4[ch][1] = gs[RH]; g4[ch][2] = gs[2 * RH]; g4[ch][3] = gs[3 * RH];
+        const float4* cc = p.cs + (base * RH + j) * 2;
+        ct[ch][0] = cc[0]; ct[ch][1] = cc[1];
+        if (t > 0) {
+          const float4* pc = p.cs + (((size_t)(t - 1) * p.B8 + bc) * RH + j) * 2;
+          cp[ch][0] = pc[0]; cp[ch][1] = pc[1];
+        } else {
+          cp[ch][0] = cp[ch][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int bg = b0 + col0 + e;
+        float d = 0.f;
+        if (bg < B) {
+          if (p.return_sequences) d = p.dout[((size_t)bg * T + t) * RH + j];
+          else if (t == T - 1) d = p.dout[(size_t)bg * RH + j];
+        }
+        dext[ch][e] = d;
+      }
+    }
+    if (have_dh) {
+      mbar_wait(&bar_mma, phase);
+      phase ^= 1;
+      tc_fence_after();
+    }
+#pragma unroll
+    for (int ch = 0; ch < CH8; ++ch) {
+      const int col0 = (cgp * CH8 + ch) * 8;
+      uint32_t vd[8];
+      if (have_dh) { tmem_ld8(t_lane + col0, vd); tmem_ld_wait(); }
+      float zi[8], zf[8], zg[8], zo[8];
+      if (live[ch]) {
+        const __nv_bfloat16* bi = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][0]);
+        const __nv_bfloat16* bf = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][1]);
+        const __nv_bfloat16* bg_ = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][2]);
+        const __nv_bfloat16* bo = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][3]);
+        const float* ctv = reinterpret_cast<const float*>(&ct[ch][0]);
+        const float* cpv = reinterpret_cast<const float*>(&cp[ch][0]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float gi = __bfloat162float(bi[e]), gf = __bfloat162float(bf[e]);
+          const float gg = __bfloat162float(bg_[e]), go = __bfloat162float(bo[e]);
+          const float dh = dext[ch][e] + (have_dh ? __uint_as_float(vd[e]) : 0.f);
+          const float tc = fast_tanh(ctv[e]);
+          const float dcv = fmaf(dh * go, 1.f - tc * tc, dc[ch * 8 + e]);
+          zo[e] = dh * tc * ((go > 0.f && go < 1.f) ? 0.2f : 0.f);
+          zi[e] = dcv * gg * ((gi > 0.f && gi < 1.f) ? 0.2f : 0.f);
+          zf[e] = dcv * cpv[e] * ((gf > 0.f && gf < 1.f) ? 0.2f : 0.f);
+          zg[e] = dcv * gi * (1.f - gg * gg);
+          dc[ch * 8 + e] = dcv * gf;
+          const float xv = sX[(col0 + e) * T + t];
+          acc_w[0] = fmaf(xv, zi[e], acc_w[0]); acc_w[1] = fmaf(xv, zf[e], acc_w[1]);
+          acc_w[2] = fmaf(xv, zg[e], acc_w[2]); acc_w[3] = fmaf(xv, zo[e], acc_w[3]);
+          acc_b[0] += zi[e]; acc_b[1] += zf[e]; acc_b[2] += zg[e]; acc_b[3] += zo[e];
+        }
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) zi[e] = zf[e] = zg[e] = zo[e] = 0.f;
+      }
+      const uint4 pi = make_uint4(pack_bf16x2(zi[0], zi[1]), pack_bf16x2(zi[2], zi[3]), pack_bf16x2(zi[4], zi[5]), pack_bf16x2(zi[6], zi[7]));
+      const uint4 pf = make_uint4(pack_bf16x2(zf[0], zf[1]), pack_bf16x2(zf[2], zf[3]), pack_bf16x2(zf[4], zf[5]), pack_bf16x2(zf[6], zf[7]));
+      const uint4 pg = make_uint4(pack_bf16x2(zg[0], zg[1]), pack_bf16x2(zg[2], zg[3]), pack_bf16x2(zg[4], zg[5]), pack_bf16x2(zg[6], zg[7]));
+      const uint4 po = make_uint4(pack_bf16x2(zo[0], zo[1]), pack_bf16x2(zo[2], zo[3]), pack_bf16x2(zo[4], zo[5]), pack_bf16x2(zo[6], zo[7]));
+      if (t > 0) {
+        const uint32_t off = (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16;
+        constexpr uint32_t gstride = 16 * (NB * 16);
+        *reinterpret_cast<uint4*>(sZ + 0 * gstride + off) = pi;
+        *reinterpret_cast<uint4*>(sZ + 1 * gstride + off) = pf;
+        *reinterpret_cast<uint4*>(sZ + 2 * gstride + off) = pg;
+        *reinterpret_cast<uint4*>(sZ + 3 * gstride + off) = po;
+      }
+      if (live[ch]) {
+        uint4* dzp = p.dz + ((size_t)t * p.B8 + ((b0 + col0) >> 3)) * GH + j;
+        dzp[0 * RH] = pi; dzp[1 * RH] = pf; dzp[2 * RH] = pg; dzp[3 * RH] = po;
+      }
+    }
+    if (t > 0) {
+      fence_proxy_async_smem();
+      tc_fence_before();
+      __syncthreads();
+      if (tid == 0) {
+        tc_fence_after();
+#pragma unroll 8
+        for (int ks = 0; ks < GH / 16; ++ks)
+          umma_bf16(tmem, umma_desc(w_base + ks * 2 * 128, 128, MG * 128),
+                    umma_desc(z_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+        umma_commit(&bar_mma);
+      }
+    }
+  }
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    atomicAdd(p.d_wih + g * RH + j, acc_w[g]);
+    atomicAdd(p.d_bias + g * RH + j, acc_b[g]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, TM_COLS);
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Recurrent weight-gradient GEMM on pre-tiled operands:
+//   C[128, n0:n0+BN] = sum over k-groups g of  A_img[g]ᵀ(8 x 128) · B_img[g](8 x N)
+// A_img: [KG][128] x 16 B, B_img: [KG][b_ntotal] x 16 B — both already K-major UMMA images in global memory,
+// so a producer thread streams them with bulk TMA copies through a 4-stage full/empty mbarrier ring, one
+// thread issues the MMAs, four warps drain TMEM.  KG must be a multiple of 8 (callers zero-pad).
+// ------------------------------------------------------------------------------------------------------
+constexpr int WG2_STAGES = 4;
+constexpr int WG2_THREADS = 192;   // warp 0: TMA producer, warp 1: MMA issuer, warps 2-5: epilogue
+
+template <int BN>
+__global__ void __launch_bounds__(WG2_THREADS, 1) rnn128_wgrad_kernel(const uint8_t* __restrict__ a_img,
+                                                                      const uint8_t* __restrict__ b_img, float* __restrict__ C,
+                                                                      int kgroups, int b_ntotal, int b_noff, int ldc) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int A_ST = 8 * RH * 16, B_ST = 8 * BN * 16, ST = A_ST + B_ST;
+  __shared__ uint64_t full[WG2_STAGES], empty[WG2_STAGES], done;
+  __shared__ uint32_t tmem_s;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n0 = blockIdx.x * BN;
+  constexpr uint32_t TM_COLS = BN < 32 ? 32 : BN;
+  if (warp == 0) tmem_alloc(&tmem_s, TM_COLS);
+  if (tid == 32) {
+    for (int s = 0; s < WG2_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(&done, 1);
+    mbar_fence_init();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_s;
+  const int nkb = kgroups / 8;
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % WG2_STAGES;
+        if (kb >= WG2_STAGES) mbar_wait(&empty[s], ((kb / WG2_STAGES) - 1) & 1);
+        uint8_t* sa = smem + s * ST;
+        uint8_t* sb = sa + A_ST;
+        mbar_expect_tx(&full[s], ST);
+        tma_bulk_g2s(sa, a_img + (size_t)kb * A_ST, A_ST, &full[s]);       // 8 k-groups of A are contiguous
+#pragma unroll
+        for (int g = 0; g < 8; ++g)
+          tma_bulk_g2s(sb + g * (BN * 16), b_img + ((size_t)(kb * 8 + g) * b_ntotal + b_noff + n0) * 16, BN * 16, &full[s]);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, BN, false, false);
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % WG2_STAGES;
+        mbar_wait(&full[s], (kb / WG2_STAGES) & 1);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * ST), b_base = a_base + A_ST;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+          umma_bf16(tmem, umma_desc(a_base + ks * 2 * (RH * 16), RH * 16, 128),
+                    umma_desc(b_base + ks * 2 * (BN * 16), BN * 16, 128), idesc, (kb | ks) != 0);
+        umma_commit(&empty[s]);
+      }
+      umma_commit(&done);
+    }
+  } else {
+    mbar_wait(&done, 0);
+    tc_fence_after();
+    const int q = warp & 3;                                   // warps 2..5 -> lane quarters 2,3,0,1
+    const int row = q * 32 + lane;
+    float* dst = C + (size_t)row * ldc + n0;
+#pragma unroll 1
+    for (int c0 = 0; c0 < BN; c0 += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem + (static_cast<uint32_t>(q * 32) << 16) + c0, v);
+      tmem_ld_wait();
+      if (nkb > 0) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          reinterpret_cast<float4*>(dst + c0)[i] = make_float4(__uint_as_float(v[4 * i]), __uint_as_float(v[4 * i + 1]),
+                                                               __uint_as_float(v[4 * i + 2]), __uint_as_float(v[4 * i + 3]));
+      } else {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) reinterpret_cast<float4*>(dst + c0)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, TM_COLS);
+}
+
+}  // namespace ddls
+
+using namespace ddls;
+
+extern "C" int ddls_rnn128_pack(const float* recurrent, const float* w_ih, const float* bias, void* image, int gates,
+                                void* stream) {
+  if (gates != 3 && gates != 4) { set_last_error("ddls_rnn128_pack: gates must be 3 (GRU) or 4 (LSTM)"); return 1; }
+  const int GH = gates * RH;
+  const int total = R_KG * (GH / 8) * 8;
+  rnn128_pack_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+      recurrent, w_ih, bias, static_cast<__nv_bfloat16*>(image), GH);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "rnn128_pack_kernel launch");
+}
+
+static int pick_tile(int B, int tile) {
+  if (tile > 0) return tile;
+  return (B <= 32 * 148) ? 32 : 64;
+}
+
+extern "C" int ddls_lstm128_forward_v2(const float* x, const void* image, float* out, void* hs, void* gates, void* cs, int B,
+                                       int T, int return_sequences, int save_for_backward, int tile, void* stream) {
+  if (B <= 0 || T <= 0) { set_last_error("ddls_lstm128_forward_v2: empty problem"); return 1; }
+  LstmV2Fwd p{x, static_cast<const __nv_bfloat16*>(image), out, static_cast<uint4*>(hs), static_cast<uint4*>(gates),
+              static_cast<float4*>(cs), B, T, (B + 7) / 8, return_sequences, save_for_backward};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = pick_tile(B, tile);
+  const size_t smem = (size_t)R_KG * 64 * 128 + (size_t)RH * nb * 2 + (size_t)T * nb * 16 + (size_t)nb * 16;
+  if (smem > 227 * 1024) { set_last_error("ddls_lstm128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
+  if (nb == 32) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lstm_fwd_v2_kernel<32><<<(B + 31) / 32, RT, smem, st>>>(p);
+  } else if (nb == 64) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lstm_fwd_v2_kernel<64><<<(B + 63) / 64, RT, smem, st>>>(p);
+  } else { set_last_error("ddls_lstm128_forward_v2: tile must be 32 or 64"); return 1; }
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "lstm_fwd_v2_kernel launch");
+}
+
+extern "C" int ddls_lstm128_backward_v2(const float* dout, const float* x, const void* image, const void* gates,
+                                        const void* cs, void* dz, float* d_wih, float* d_bias, int B, int T,
+                                        int return_sequences, int tile, void* stream) {
+  if (B <= 0 || T <= 0) { set_last_error("ddls_lstm128_backward_v2: empty problem"); return 1; }
+  LstmV2Bwd p{dout, x, static_cast<const __nv_bfloat16*>(image), static_cast<const uint4*>(gates),
+              static_cast<const float4*>(cs), static_cast<uint4*>(dz), d_wih, d_bias, B, T, (B + 7) / 8, return_sequences};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = pick_tile(B, tile);
+  const size_t smem = (size_t)16 * 64 * 128 + (size_t)4 * RH * nb * 2 + (size_t)nb * T * 4;
+  if (smem > 227 * 1024) { set_last_error("ddls_lstm128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
+  if (nb == 32) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lstm_bwd_v2_kernel<32><<<(B + 31) / 32, RT, smem, st>>>(p);
+  } else if (nb == 64) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lstm_bwd_v2_kernel<64><<<(B + 63) / 64, RT, smem, st>>>(p);
+  } else { set_last_error("ddls_lstm128_backward_v2: tile must be 32 or 64"); return 1; }
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "lstm_bwd_v2_kernel launch");
+}
+
+extern "C" int ddls_rnn128_wgrad(const void* a_img, const void* b_img, float* C, int kgroups, int n, int b_ntotal,
+                                 int b_noff, int ldc, void* stream) {
+  if (kgroups % 8 != 0 || n % 64 != 0) {
+    set_last_error("ddls_rnn128_wgrad: kgroups must be a multiple of 8 and n a multiple of 64 (got %d, %d)", kgroups, n);
+    return 1;
+  }
+  constexpr int BN = 64;
+  const int smem = WG2_STAGES * (8 * RH * 16 + 8 * BN * 16);
+  DDLS_CUDA_OK(cudaFuncSetAttribute(rnn128_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  rnn128_wgrad_kernel<BN><<<n / BN, WG2_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
+      static_cast<const uint8_t*>(a_img), static_cast<const uint8_t*>(b_img), C, kgroups, b_ntotal, b_noff, ldc);
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "rnn128_wgrad_kernel launch");
+}

@@ -13,7 +13,59 @@ N.register('ddls_lstm128_backward', [P, P, P, P, P, P, P, P, I, I, I, I, P])
 N.register('ddls_gru128_forward', [P, P, P, P, P, P, P, P, I, I, I, I, I, P])
 N.register('ddls_gru128_backward', [P, P, P, P, P, P, P, I, I, I, I, P])
 
+N.register('ddls_rnn128_pack', [P, P, P, P, I, P])
+N.register('ddls_lstm128_forward_v2', [P, P, P, P, P, P, I, I, I, I, I, P])
+N.register('ddls_lstm128_backward_v2', [P, P, P, P, P, P, P, P, I, I, I, I, P])
+N.register('ddls_rnn128_wgrad', [P, P, P, I, I, I, I, I, P])
+
 H = 128
+
+
+def use_v2() -> bool:
+    import os
+    return os.environ.get('DDLS_RNN_V1', '0') != '1'
+
+
+def pack_image(recurrent, kernel, bias, gates: int, out=None):
+    """fp32 Keras weights -> bf16 UMMA image [18][gates*16][8][8] (see csrc/rnn128.cu)."""
+    if out is None:
+        out = torch.empty(18 * gates * 16 * 64, dtype=torch.bfloat16, device=recurrent.device)
+    N.call('ddls_rnn128_pack', recurrent.data_ptr(), kernel.data_ptr(), bias.data_ptr(), out.data_ptr(), gates,
+           N.stream_ptr(recurrent.device))
+    return out
+
+
+def kgroups_padded(T: int, B8: int) -> int:
+    return ((T - 1) * B8 + 7) // 8 * 8
+
+
+def lstm_v2_buffers(B: int, T: int, dev, zero: bool = True):
+    """Stash buffers of the v2 kernels.  hs / dz carry 8 zeroed padding k-groups for the wgrad GEMM."""
+    B8 = (B + 7) // 8
+    mk = torch.zeros if zero else torch.empty
+    hs = mk(((T * B8 + 8) * H * 8,), dtype=torch.bfloat16, device=dev)
+    gates = torch.empty((T * B8 * 4 * H * 8,), dtype=torch.bfloat16, device=dev)
+    cs = torch.empty((T * B8 * H * 8,), dtype=torch.float32, device=dev)
+    dz = mk(((T * B8 + 8) * 4 * H * 8,), dtype=torch.bfloat16, device=dev)
+    return hs, gates, cs, dz
+
+
+def lstm_v2_forward(x2, img, out, hs, gates, cs, B, T, return_sequences, save):
+    N.call('ddls_lstm128_forward_v2', x2.data_ptr(), img.data_ptr(), out.data_ptr(), N.ptr(hs), N.ptr(gates), N.ptr(cs),
+           B, T, int(return_sequences), int(save), 0, N.stream_ptr(x2.device))
+
+
+def lstm_v2_backward(dout, x2, img, gates, cs, dz, d_wih, d_bias, d_rec, B, T, return_sequences, hs):
+    """BPTT + recurrent weight gradient.  d_wih / d_bias are accumulated into, d_rec [128,512] is overwritten."""
+    N.call('ddls_lstm128_backward_v2', dout.data_ptr(), x2.data_ptr(), img.data_ptr(), gates.data_ptr(), cs.data_ptr(),
+           dz.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(return_sequences), 0, N.stream_ptr(x2.device))
+    B8 = (B + 7) // 8
+    if T > 1:
+        b_img = dz.data_ptr() + B8 * 4 * H * 16          # k-groups of t >= 1
+        N.call('ddls_rnn128_wgrad', hs.data_ptr(), b_img, d_rec.data_ptr(), kgroups_padded(T, B8), 4 * H, 4 * H, 0,
+               d_rec.stride(0), N.stream_ptr(x2.device))
+    else:
+        d_rec.zero_()
 
 
 def native_available(x: torch.Tensor, units: int) -> bool:
@@ -29,6 +81,43 @@ def native_available(x: torch.Tensor, units: int) -> bool:
 
 def _wgrad_split(k: int) -> int:
     return max(1, min(32, k // 64))
+
+
+class _LSTM128v2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, kernel, recurrent, bias, return_sequences):
+        B, T, _ = x.shape
+        dev = x.device
+        x2 = x.reshape(B, T).contiguous()
+        need_bwd = any(ctx.needs_input_grad)
+        out = torch.empty((B, T, H) if return_sequences else (B, H), dtype=torch.float32, device=dev)
+        img = pack_image(recurrent, kernel, bias, 4)
+        if need_bwd:
+            hs, gates, cs, dz = lstm_v2_buffers(B, T, dev)
+        else:
+            hs = gates = cs = dz = None
+        lstm_v2_forward(x2, img, out, hs, gates, cs, B, T, return_sequences, need_bwd)
+        if need_bwd:
+            ctx.save_for_backward(x2, kernel, img, hs, gates, cs, dz)
+            ctx.return_sequences = return_sequences
+            ctx.dims = (B, T)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x2, kernel, img, hs, gates, cs, dz = ctx.saved_tensors
+        B, T = ctx.dims
+        dev = x2.device
+        small = torch.zeros(8 * H, dtype=torch.float32, device=dev)
+        d_wih, d_bias = small[:4 * H], small[4 * H:]
+        d_rec = torch.empty((H, 4 * H), dtype=torch.float32, device=dev)
+        lstm_v2_backward(dout.contiguous(), x2, img, gates, cs, dz, d_wih, d_bias, d_rec, B, T, ctx.return_sequences, hs)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            B8 = (B + 7) // 8
+            dzf = dz[:T * B8 * 4 * H * 8].view(T, B8, 4 * H, 8).permute(0, 1, 3, 2).reshape(T, B8 * 8, 4 * H)[:, :B].float()
+            dx = (dzf @ kernel.t()).permute(1, 0, 2).contiguous()
+        return dx, d_wih.view(1, 4 * H), d_rec, d_bias, None
 
 
 class _LSTM128(torch.autograd.Function):
@@ -78,7 +167,8 @@ class _LSTM128(torch.autograd.Function):
 
 
 def lstm_layer(x, kernel, recurrent, bias, return_sequences=False):
-    return _LSTM128.apply(x, kernel, recurrent, bias, bool(return_sequences))
+    fn = _LSTM128v2 if use_v2() else _LSTM128
+    return fn.apply(x, kernel, recurrent, bias, bool(return_sequences))
 
 
 class _GRU128(torch.autograd.Function):

@@ -79,6 +79,22 @@ int ddls_lstm128_backward(const float* dout, const float* x, const float* w_hh, 
                           void* dz, float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile,
                           void* stream);
 
+/* ---- second-generation recurrent kernels (csrc/rnn128.cu) ---------------------------------------------
+ * ddls_rnn128_pack: recurrent [128, G*128], w_ih [G*128], bias [G*128] (fp32, Keras layout) -> bf16 UMMA
+ * image [18][G*16][8][8] (16 hidden k-groups, 1 k-group of input-kernel/bias hi-lo rows, 1 zero k-group);
+ * pulled into shared memory by the kernels below with bulk TMA copies. */
+int ddls_rnn128_pack(const float* recurrent, const float* w_ih, const float* bias, void* image, int gates, void* stream);
+/* B8 = ceil(B/8).  hs: [T][B8][128] x 16 B (h_t, 8 batch rows per vector = K-major UMMA image);
+ * gates: [T][B8][4][128] x 16 B; cs: [T][B8][128] x 32 B; dz: [T][B8][512] x 16 B (K-major UMMA image). */
+int ddls_lstm128_forward_v2(const float* x, const void* image, float* out, void* hs, void* gates, void* cs, int B, int T,
+                            int return_sequences, int save_for_backward, int tile, void* stream);
+int ddls_lstm128_backward_v2(const float* dout, const float* x, const void* image, const void* gates, const void* cs,
+                             void* dz, float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile,
+                             void* stream);
+/* C[128, n] (ldc) = sum_g A_img[g]^T · B_img[g][b_noff : b_noff+n]; images as above, kgroups % 8 == 0, n % 64 == 0. */
+int ddls_rnn128_wgrad(const void* a_img, const void* b_img, float* C, int kgroups, int n, int b_ntotal, int b_noff,
+                      int ldc, void* stream);
+
 /* ---- persistent GRU(128) recurrence, tcgen05 (Keras GRU reset_after=False, ddl_nyiso_aztk.py:201-203) ----
  * Gate order z,r,h.  When save_for_backward: hs [T,B,H] bf16 (h_t), rh [T,B,H] bf16 (r_t*h_{t-1}),
  * gates [T,B,H] float4 (z, r, hh, h_{t-1}). */
