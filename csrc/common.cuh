@@ -81,6 +81,14 @@ DDLS_DEVINL void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// named barriers: producer warps arrive (non-blocking), the consumer warp syncs
+DDLS_DEVINL void named_bar_sync(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+DDLS_DEVINL void named_bar_arrive(uint32_t id, uint32_t nthreads) {
+  asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 // generic-proxy smem writes -> visible to the async proxy (UMMA / TMA reads)
 DDLS_DEVINL void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 

@@ -22,7 +22,6 @@
 namespace ddls {
 
 constexpr int RH = 128;             // hidden units
-constexpr int RT = 512;             // threads per CTA
 constexpr int R_KG = 18;            // k-groups in the weight image: 16 (hidden) + 1 (input/bias rows) + 1 (zeros)
 
 // image element (k, m): ((k>>3) * (GH/8) + (m>>3)) * 64 + (k&7)*8 + (m&7)   [bf16 elements]
@@ -56,7 +55,7 @@ __global__ void __launch_bounds__(256) rnn128_pack_kernel(const float* __restric
 // x image for the extra K step: per time step one k-group [NB/8][8 k][8 n]: rows x_hi, x_hi, 1, 1, x_lo, 0, 0, 0
 template <int NB>
 DDLS_DEVINL void build_x_image(uint8_t* sX, uint8_t* sZero, const float* __restrict__ x, int b0, int B, int T) {
-  for (int idx = threadIdx.x; idx < T * NB; idx += RT) {
+  for (int idx = threadIdx.x; idx < T * NB; idx += blockDim.x) {
     const int t = idx / NB, b = idx - t * NB;
     const float xv = (b0 + b < B) ? x[(size_t)(b0 + b) * T + t] : 0.f;
     const __nv_bfloat16 hi = __float2bfloat16(xv);
@@ -65,8 +64,26 @@ DDLS_DEVINL void build_x_image(uint8_t* sX, uint8_t* sZero, const float* __restr
     __nv_bfloat16* g = reinterpret_cast<__nv_bfloat16*>(sX + (size_t)t * (NB * 16) + (b >> 3) * 128) + (b & 7);
     g[0 * 8] = hi; g[1 * 8] = hi; g[2 * 8] = one; g[3 * 8] = one; g[4 * 8] = lo; g[5 * 8] = zero; g[6 * 8] = zero; g[7 * 8] = zero;
   }
-  for (int idx = threadIdx.x; idx < NB * 16 / 16; idx += RT) reinterpret_cast<uint4*>(sZero)[idx] = make_uint4(0, 0, 0, 0);
+  for (int idx = threadIdx.x; idx < NB * 16 / 16; idx += blockDim.x) reinterpret_cast<uint4*>(sZero)[idx] = make_uint4(0, 0, 0, 0);
 }
+
+// Thread organisation of the recurrence kernels: warps 0..15 are the epilogue (TMEM lane quarter q = warp & 3,
+// column group warp >> 2), warp 16 only issues MMAs.  Per step the epilogue (a) reads its accumulators, does the
+// gate math and writes the next N-side operand to shared memory, (b) ARRIVES on a named barrier the MMA warp is
+// waiting on, and only then (c) writes the backward stash to global memory — so (c) overlaps the next MMAs.
+constexpr int R_EPI = 512;          // epilogue threads
+constexpr int R_ALL = R_EPI + 32;   // + MMA warp
+constexpr uint32_t BAR_H = 1, BAR_R = 2;
+
+DDLS_DEVINL uint4 pack8(const float (&v)[8]) {
+  return make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+}
+DDLS_DEVINL void unpack8(const uint4& p, float (&v)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&p);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { v[2 * i] = __low2float(h[i]); v[2 * i + 1] = __high2float(h[i]); }
+}
+DDLS_DEVINL float hs_grad(float a) { return (a > 0.f && a < 1.f) ? 0.2f : 0.f; }   // hard_sigmoid' from its output
 
 struct LstmV2Fwd {
   const float* x;                 // [B, T]
@@ -80,12 +97,12 @@ struct LstmV2Fwd {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(RT, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
+__global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int GH = 4 * RH, MG = GH / 8;
   constexpr uint32_t W_LBO = MG * 128;                       // 8192: k-group stride of the image
   constexpr int W_BYTES = R_KG * MG * 128;                   // 147,456
-  constexpr int CH8 = NB / 32;                               // 8-column chunks per thread
+  constexpr int CH8 = NB / 32;                               // 8-column chunks per epilogue thread
   uint8_t* sW = smem;
   uint8_t* sH = sW + W_BYTES;                                // [16][NB/8][8][8] bf16
   uint8_t* sX = sH + RH * NB * 2;                            // [T][NB*16 B]
@@ -93,15 +110,13 @@ __global__ void __launch_bounds__(RT, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   __shared__ uint64_t bar_w, bar_mma;
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int q = warp & 3, cgp = warp >> 2;                   // TMEM lane quarter, column group (0..3)
-  const int j = q * 32 + lane;
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
 
-  if (warp == 0) tmem_alloc(&tmem_s, 4 * NB);
-  if (tid == 32) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
+  if (warp == 16) tmem_alloc(&tmem_s, 4 * NB);
+  if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
-  if (tid == 0) {                                            // one bulk TMA copy brings the whole weight image
+  if (tid == R_EPI) {                                        // bulk TMA copies bring the whole weight image
     mbar_expect_tx(&bar_w, W_BYTES);
 #pragma unroll
     for (int c = 0; c < R_KG; ++c)
@@ -113,95 +128,105 @@ __global__ void __launch_bounds__(RT, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_s;
-  const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
-  constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
-  const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), x_base = smem_u32(sX), z_base = smem_u32(sZero);
-  if (tid == 0) mbar_wait(&bar_w, 0);
 
-  float c[CH8 * 8];
-#pragma unroll
-  for (int i = 0; i < CH8 * 8; ++i) c[i] = 0.f;
-  uint32_t phase = 0;
-  for (int t = 0; t < T; ++t) {
-    if (tid == 0) {
+  if (warp == 16) {
+    // ================= MMA warp: the whole warp runs the (warp-uniform) loop, one elected lane issues =================
+    constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
+    const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), x_base = smem_u32(sX), z_base = smem_u32(sZero);
+    mbar_wait(&bar_w, 0);
+    for (int t = 0; t < T; ++t) {
+      if (t > 0) named_bar_sync(BAR_H, R_ALL);               // h_{t-1} is in shared memory, TMEM has been drained
       tc_fence_after();
-      const uint32_t xt = x_base + t * (NB * 16);
+      if (elect_one()) {
+        const uint32_t xt = x_base + t * (NB * 16);
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        if (t > 0) {
+        for (int g = 0; g < 4; ++g) {
+          if (t > 0) {
 #pragma unroll
-          for (int ks = 0; ks < RH / 16; ++ks)
-            umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
-                      umma_desc(h_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+            for (int ks = 0; ks < RH / 16; ++ks)
+              umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
+                        umma_desc(h_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+          }
+          // input projection + bias: image k-groups 16 (payload) / 17 (zeros) times [x rows of step t | zero group]
+          umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + 16 * W_LBO, W_LBO, 128),
+                    umma_desc(xt, z_base - xt, 128), idesc, t > 0);
         }
-        // input projection + bias: k-groups 16 (payload) and 17 (zeros) of the image x [x rows | zero group]
-        umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + 16 * W_LBO, W_LBO, 128),
-                  umma_desc(xt, z_base - xt, 128), idesc, t > 0);
+        umma_commit(&bar_mma);
       }
-      umma_commit(&bar_mma);
+      __syncwarp();
     }
-    mbar_wait(&bar_mma, phase);
-    phase ^= 1;
-    tc_fence_after();
-    const bool last = (t == T - 1);
+  } else {
+    // ================= epilogue warps =================
+    const int q = warp & 3, cgp = warp >> 2;
+    const int j = q * 32 + lane;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    float c[CH8 * 8];
 #pragma unroll
-    for (int ch = 0; ch < CH8; ++ch) {
-      const int col0 = (cgp * CH8 + ch) * 8;
-      uint32_t vi[8], vf[8], vg[8], vo[8];
-      tmem_ld8(t_lane + 0 * NB + col0, vi);
-      tmem_ld8(t_lane + 1 * NB + col0, vf);
-      tmem_ld8(t_lane + 2 * NB + col0, vg);
-      tmem_ld8(t_lane + 3 * NB + col0, vo);
-      tmem_ld_wait();
-      float gi[8], gf[8], gg[8], go[8], hv[8];
+    for (int i = 0; i < CH8 * 8; ++i) c[i] = 0.f;
+    uint32_t phase = 0;
+    for (int t = 0; t < T; ++t) {
+      const bool last = (t == T - 1);
+      mbar_wait(&bar_mma, phase);
+      phase ^= 1;
+      tc_fence_after();
+      float gi[CH8][8], gf[CH8][8], gg[CH8][8], go[CH8][8], hv[CH8][8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        gi[e] = __saturatef(fmaf(0.2f, __uint_as_float(vi[e]), 0.5f));
-        gf[e] = __saturatef(fmaf(0.2f, __uint_as_float(vf[e]), 0.5f));
-        gg[e] = fast_tanh(__uint_as_float(vg[e]));
-        go[e] = __saturatef(fmaf(0.2f, __uint_as_float(vo[e]), 0.5f));
-        const float cn = fmaf(gf[e], c[ch * 8 + e], gi[e] * gg[e]);
-        c[ch * 8 + e] = cn;
-        hv[e] = go[e] * fast_tanh(cn);
-      }
-      const uint4 h16 = make_uint4(pack_bf16x2(hv[0], hv[1]), pack_bf16x2(hv[2], hv[3]), pack_bf16x2(hv[4], hv[5]),
-                                   pack_bf16x2(hv[6], hv[7]));
-      if (!last) *reinterpret_cast<uint4*>(sH + (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16) = h16;
-      const int bc = (b0 + col0) >> 3;                      // global 8-row chunk index
-      if (bc < p.B8) {
-        if (p.save) {
-          const size_t base = (size_t)t * p.B8 + bc;
-          p.hs[base * RH + j] = h16;
-          uint4* gd = p.gates + base * 4 * RH + j;
-          gd[0 * RH] = make_uint4(pack_bf16x2(gi[0], gi[1]), pack_bf16x2(gi[2], gi[3]), pack_bf16x2(gi[4], gi[5]), pack_bf16x2(gi[6], gi[7]));
-          gd[1 * RH] = make_uint4(pack_bf16x2(gf[0], gf[1]), pack_bf16x2(gf[2], gf[3]), pack_bf16x2(gf[4], gf[5]), pack_bf16x2(gf[6], gf[7]));
-          gd[2 * RH] = make_uint4(pack_bf16x2(gg[0], gg[1]), pack_bf16x2(gg[2], gg[3]), pack_bf16x2(gg[4], gg[5]), pack_bf16x2(gg[6], gg[7]));
-          gd[3 * RH] = make_uint4(pack_bf16x2(go[0], go[1]), pack_bf16x2(go[2], go[3]), pack_bf16x2(go[4], go[5]), pack_bf16x2(go[6], go[7]));
-          float4* cd = p.cs + (base * RH + j) * 2;
-          cd[0] = make_float4(c[ch * 8 + 0], c[ch * 8 + 1], c[ch * 8 + 2], c[ch * 8 + 3]);
-          cd[1] = make_float4(c[ch * 8 + 4], c[ch * 8 + 5], c[ch * 8 + 6], c[ch * 8 + 7]);
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint32_t vi[8], vf[8], vg[8], vo[8];
+        tmem_ld8(t_lane + 0 * NB + col0, vi);
+        tmem_ld8(t_lane + 1 * NB + col0, vf);
+        tmem_ld8(t_lane + 2 * NB + col0, vg);
+        tmem_ld8(t_lane + 3 * NB + col0, vo);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          gi[ch][e] = __saturatef(fmaf(0.2f, __uint_as_float(vi[e]), 0.5f));
+          gf[ch][e] = __saturatef(fmaf(0.2f, __uint_as_float(vf[e]), 0.5f));
+          gg[ch][e] = fast_tanh(__uint_as_float(vg[e]));
+          go[ch][e] = __saturatef(fmaf(0.2f, __uint_as_float(vo[e]), 0.5f));
+          const float cn = fmaf(gf[ch][e], c[ch * 8 + e], gi[ch][e] * gg[ch][e]);
+          c[ch * 8 + e] = cn;
+          hv[ch][e] = go[ch][e] * fast_tanh(cn);
         }
-        if (p.return_sequences || last) {
+        if (!last) *reinterpret_cast<uint4*>(sH + (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16) = pack8(hv[ch]);
+      }
+      if (!last) {                                           // hand h_t to the MMA warp, then do the non-critical stores
+        fence_proxy_async_smem();
+        tc_fence_before();
+        named_bar_arrive(BAR_H, R_ALL);
+      }
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int bg = b0 + col0 + e;
-            if (bg < B) {
-              if (p.return_sequences) p.out[((size_t)bg * T + t) * RH + j] = hv[e];
-              else p.out[(size_t)bg * RH + j] = hv[e];
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        const int bc = (b0 + col0) >> 3;
+        if (bc < p.B8) {
+          if (p.save) {
+            const size_t base = (size_t)t * p.B8 + bc;
+            p.hs[base * RH + j] = pack8(hv[ch]);
+            uint4* gd = p.gates + base * 4 * RH + j;
+            gd[0 * RH] = pack8(gi[ch]); gd[1 * RH] = pack8(gf[ch]); gd[2 * RH] = pack8(gg[ch]); gd[3 * RH] = pack8(go[ch]);
+            float4* cd = p.cs + (base * RH + j) * 2;
+            cd[0] = make_float4(c[ch * 8 + 0], c[ch * 8 + 1], c[ch * 8 + 2], c[ch * 8 + 3]);
+            cd[1] = make_float4(c[ch * 8 + 4], c[ch * 8 + 5], c[ch * 8 + 6], c[ch * 8 + 7]);
+          }
+          if (p.return_sequences || last) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int bg = b0 + col0 + e;
+              if (bg < B) {
+                if (p.return_sequences) p.out[((size_t)bg * T + t) * RH + j] = hv[ch][e];
+                else p.out[(size_t)bg * RH + j] = hv[ch][e];
+              }
             }
           }
         }
       }
     }
-    if (!last) {
-      fence_proxy_async_smem();
-      tc_fence_before();
-      __syncthreads();
-    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, 4 * NB);
+  if (warp == 16) tmem_dealloc(tmem, 4 * NB);
 }
 
 struct LstmV2Bwd {
@@ -218,33 +243,31 @@ struct LstmV2Bwd {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(RT, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
+__global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int GH = 4 * RH, MG = GH / 8;
   constexpr int W_BYTES = 16 * MG * 128;                     // hidden k-groups only: 131,072
   constexpr int CH8 = NB / 32;
-  uint8_t* sW = smem;                                        // image: as K-major A, LBO = 128, SBO = MG*128
+  uint8_t* sW = smem;                                        // image as K-major A: LBO = 128, SBO = MG*128
   uint8_t* sZ = sW + W_BYTES;                                // dz MN-major B: [64 k-groups][NB/8][8][8]
   float* sX = reinterpret_cast<float*>(sZ + GH * NB * 2);    // [NB][T]
   __shared__ uint64_t bar_w, bar_mma;
   __shared__ uint32_t tmem_s;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int q = warp & 3, cgp = warp >> 2;
-  const int j = q * 32 + lane;
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
   constexpr uint32_t TM_COLS = NB < 32 ? 32 : NB;
 
-  if (warp == 0) tmem_alloc(&tmem_s, TM_COLS);
-  if (tid == 32) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
+  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
-  if (tid == 0) {
+  if (tid == R_EPI) {
     mbar_expect_tx(&bar_w, W_BYTES);
 #pragma unroll
     for (int c = 0; c < 16; ++c)
       tma_bulk_g2s(sW + c * (MG * 128), reinterpret_cast<const uint8_t*>(p.img) + (size_t)c * (MG * 128), MG * 128, &bar_w);
   }
-  for (int idx = tid; idx < NB * T; idx += RT) {
+  for (int idx = tid; idx < NB * T; idx += R_ALL) {
     const int b = idx / T, t = idx - b * T;
     sX[idx] = (b0 + b < B) ? p.x[(size_t)(b0 + b) * T + t] : 0.f;
   }
@@ -252,130 +275,558 @@ __global__ void __launch_bounds__(RT, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = tmem_s;
-  const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
-  constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
-  const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
-  if (tid == 0) mbar_wait(&bar_w, 0);
 
-  float dc[CH8 * 8];
-#pragma unroll
-  for (int i = 0; i < CH8 * 8; ++i) dc[i] = 0.f;
-  float acc_w[4] = {0.f, 0.f, 0.f, 0.f}, acc_b[4] = {0.f, 0.f, 0.f, 0.f};
-  uint32_t phase = 0;
-  for (int t = T - 1; t >= 0; --t) {
-    const bool have_dh = (t < T - 1);
-    // ---- issue this step's loads before waiting on the tensor pipe (they do not depend on it) ----
-    uint4 g4[CH8][4];
-    float4 ct[CH8][2], cp[CH8][2];
-    float dext[CH8][8];
-    bool live[CH8];
-#pragma unroll
-    for (int ch = 0; ch < CH8; ++ch) {
-      const int col0 = (cgp * CH8 + ch) * 8;
-      const int bc = (b0 + col0) >> 3;
-      live[ch] = bc < p.B8;
-      if (live[ch]) {
-        const size_t base = (size_t)t * p.B8 + bc;
-        const uint4* gs = p.gates + base * 4 * RH + j;
-        g4[ch][0] = gs[0]; g4[ch][1] = gs[RH]; g4[ch][2] = gs[2 * RH]; g4[ch][3] = gs[3 * RH];
-        const float4* cc = p.cs + (base * RH + j) * 2;
-        ct[ch][0] = cc[0]; ct[ch][1] = cc[1];
-        if (t > 0) {
-          const float4* pc = p.cs + (((size_t)(t - 1) * p.B8 + bc) * RH + j) * 2;
-          cp[ch][0] = pc[0]; cp[ch][1] = pc[1];
-        } else {
-          cp[ch][0] = cp[ch][1] = make_float4(0.f, 0.f, 0.f, 0.f);
-        }
-      }
-#pragma unroll
-      for (int e = 0; e < 8; ++e) {
-        const int bg = b0 + col0 + e;
-        float d = 0.f;
-        if (bg < B) {
-          if (p.return_sequences) d = p.dout[((size_t)bg * T + t) * RH + j];
-          else if (t == T - 1) d = p.dout[(size_t)bg * RH + j];
-        }
-        dext[ch][e] = d;
-      }
-    }
-    if (have_dh) {
-      mbar_wait(&bar_mma, phase);
-      phase ^= 1;
+  if (warp == 16) {
+    constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
+    const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
+    mbar_wait(&bar_w, 0);
+    for (int t = T - 1; t >= 1; --t) {
+      named_bar_sync(BAR_H, R_ALL);                          // dz_t is in shared memory
       tc_fence_after();
-    }
-#pragma unroll
-    for (int ch = 0; ch < CH8; ++ch) {
-      const int col0 = (cgp * CH8 + ch) * 8;
-      uint32_t vd[8];
-      if (have_dh) { tmem_ld8(t_lane + col0, vd); tmem_ld_wait(); }
-      float zi[8], zf[8], zg[8], zo[8];
-      if (live[ch]) {
-        const __nv_bfloat16* bi = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][0]);
-        const __nv_bfloat16* bf = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][1]);
-        const __nv_bfloat16* bg_ = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][2]);
-        const __nv_bfloat16* bo = reinterpret_cast<const __nv_bfloat16*>(&g4[ch][3]);
-        const float* ctv = reinterpret_cast<const float*>(&ct[ch][0]);
-        const float* cpv = reinterpret_cast<const float*>(&cp[ch][0]);
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float gi = __bfloat162float(bi[e]), gf = __bfloat162float(bf[e]);
-          const float gg = __bfloat162float(bg_[e]), go = __bfloat162float(bo[e]);
-          const float dh = dext[ch][e] + (have_dh ? __uint_as_float(vd[e]) : 0.f);
-          const float tc = fast_tanh(ctv[e]);
-          const float dcv = fmaf(dh * go, 1.f - tc * tc, dc[ch * 8 + e]);
-          zo[e] = dh * tc * ((go > 0.f && go < 1.f) ? 0.2f : 0.f);
-          zi[e] = dcv * gg * ((gi > 0.f && gi < 1.f) ? 0.2f : 0.f);
-          zf[e] = dcv * cpv[e] * ((gf > 0.f && gf < 1.f) ? 0.2f : 0.f);
-          zg[e] = dcv * gi * (1.f - gg * gg);
-          dc[ch * 8 + e] = dcv * gf;
-          const float xv = sX[(col0 + e) * T + t];
-          acc_w[0] = fmaf(xv, zi[e], acc_w[0]); acc_w[1] = fmaf(xv, zf[e], acc_w[1]);
-          acc_w[2] = fmaf(xv, zg[e], acc_w[2]); acc_w[3] = fmaf(xv, zo[e], acc_w[3]);
-          acc_b[0] += zi[e]; acc_b[1] += zf[e]; acc_b[2] += zg[e]; acc_b[3] += zo[e];
-        }
-      } else {
-#pragma unroll
-        for (int e = 0; e < 8; ++e) zi[e] = zf[e] = zg[e] = zo[e] = 0.f;
-      }
-      const uint4 pi = make_uint4(pack_bf16x2(zi[0], zi[1]), pack_bf16x2(zi[2], zi[3]), pack_bf16x2(zi[4], zi[5]), pack_bf16x2(zi[6], zi[7]));
-      const uint4 pf = make_uint4(pack_bf16x2(zf[0], zf[1]), pack_bf16x2(zf[2], zf[3]), pack_bf16x2(zf[4], zf[5]), pack_bf16x2(zf[6], zf[7]));
-      const uint4 pg = make_uint4(pack_bf16x2(zg[0], zg[1]), pack_bf16x2(zg[2], zg[3]), pack_bf16x2(zg[4], zg[5]), pack_bf16x2(zg[6], zg[7]));
-      const uint4 po = make_uint4(pack_bf16x2(zo[0], zo[1]), pack_bf16x2(zo[2], zo[3]), pack_bf16x2(zo[4], zo[5]), pack_bf16x2(zo[6], zo[7]));
-      if (t > 0) {
-        const uint32_t off = (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16;
-        constexpr uint32_t gstride = 16 * (NB * 16);
-        *reinterpret_cast<uint4*>(sZ + 0 * gstride + off) = pi;
-        *reinterpret_cast<uint4*>(sZ + 1 * gstride + off) = pf;
-        *reinterpret_cast<uint4*>(sZ + 2 * gstride + off) = pg;
-        *reinterpret_cast<uint4*>(sZ + 3 * gstride + off) = po;
-      }
-      if (live[ch]) {
-        uint4* dzp = p.dz + ((size_t)t * p.B8 + ((b0 + col0) >> 3)) * GH + j;
-        dzp[0 * RH] = pi; dzp[1 * RH] = pf; dzp[2 * RH] = pg; dzp[3 * RH] = po;
-      }
-    }
-    if (t > 0) {
-      fence_proxy_async_smem();
-      tc_fence_before();
-      __syncthreads();
-      if (tid == 0) {
-        tc_fence_after();
+      if (elect_one()) {
 #pragma unroll 8
         for (int ks = 0; ks < GH / 16; ++ks)
           umma_bf16(tmem, umma_desc(w_base + ks * 2 * 128, 128, MG * 128),
                     umma_desc(z_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
         umma_commit(&bar_mma);
       }
+      __syncwarp();
     }
-  }
+  } else {
+    const int q = warp & 3, cgp = warp >> 2;
+    const int j = q * 32 + lane;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    float dc[CH8 * 8];
 #pragma unroll
-  for (int g = 0; g < 4; ++g) {
-    atomicAdd(p.d_wih + g * RH + j, acc_w[g]);
-    atomicAdd(p.d_bias + g * RH + j, acc_b[g]);
+    for (int i = 0; i < CH8 * 8; ++i) dc[i] = 0.f;
+    float acc_w[4] = {0.f, 0.f, 0.f, 0.f}, acc_b[4] = {0.f, 0.f, 0.f, 0.f};
+    uint32_t phase = 0;
+    for (int t = T - 1; t >= 0; --t) {
+      const bool have_dh = (t < T - 1);
+      // ---- this step's loads do not depend on the tensor pipe: issue them before waiting on it ----
+      uint4 g4[CH8][4];
+      float4 ct[CH8][2], cp[CH8][2];
+      float dext[CH8][8];
+      bool live[CH8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        const int bc = (b0 + col0) >> 3;
+        live[ch] = bc < p.B8;
+        if (live[ch]) {
+          const size_t base = (size_t)t * p.B8 + bc;
+          const uint4* gs = p.gates + base * 4 * RH + j;
+          g4[ch][0] = gs[0]; g4[ch][1] = gs[RH]; g4[ch][2] = gs[2 * RH]; g4[ch][3] = gs[3 * RH];
+          const float4* cc = p.cs + (base * RH + j) * 2;
+          ct[ch][0] = cc[0]; ct[ch][1] = cc[1];
+          if (t > 0) {
+            const float4* pc = p.cs + (((size_t)(t - 1) * p.B8 + bc) * RH + j) * 2;
+            cp[ch][0] = pc[0]; cp[ch][1] = pc[1];
+          } else {
+            cp[ch][0] = cp[ch][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+        }
+        if (p.return_sequences || t == T - 1) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int bg = b0 + col0 + e;
+            float d = 0.f;
+            if (bg < B) d = p.return_sequences ? p.dout[((size_t)bg * T + t) * RH + j] : p.dout[(size_t)bg * RH + j];
+            dext[ch][e] = d;
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dext[ch][e] = 0.f;
+        }
+      }
+      if (have_dh) {
+        mbar_wait(&bar_mma, phase);
+        phase ^= 1;
+        tc_fence_after();
+      }
+      float zi[CH8][8], zf[CH8][8], zg[CH8][8], zo[CH8][8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint32_t vd[8];
+        if (have_dh) { tmem_ld8(t_lane + col0, vd); tmem_ld_wait(); }
+        if (live[ch]) {
+          float gi[8], gf[8], gg[8], go[8];
+          unpack8(g4[ch][0], gi); unpack8(g4[ch][1], gf); unpack8(g4[ch][2], gg); unpack8(g4[ch][3], go);
+          const float* ctv = reinterpret_cast<const float*>(&ct[ch][0]);
+          const float* cpv = reinterpret_cast<const float*>(&cp[ch][0]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float dh = dext[ch][e] + (have_dh ? __uint_as_float(vd[e]) : 0.f);
+            const float tc = fast_tanh(ctv[e]);
+            const float dcv = fmaf(dh * go[e], 1.f - tc * tc, dc[ch * 8 + e]);
+            zo[ch][e] = dh * tc * hs_grad(go[e]);
+            zi[ch][e] = dcv * gg[e] * hs_grad(gi[e]);
+            zf[ch][e] = dcv * cpv[e] * hs_grad(gf[e]);
+            zg[ch][e] = dcv * gi[e] * (1.f - gg[e] * gg[e]);
+            dc[ch * 8 + e] = dcv * gf[e];
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) zi[ch][e] = zf[ch][e] = zg[ch][e] = zo[ch][e] = 0.f;
+        }
+        if (t > 0) {
+          const uint32_t off = (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16;
+          constexpr uint32_t gstride = 16 * (NB * 16);
+          *reinterpret_cast<uint4*>(sZ + 0 * gstride + off) = pack8(zi[ch]);
+          *reinterpret_cast<uint4*>(sZ + 1 * gstride + off) = pack8(zf[ch]);
+          *reinterpret_cast<uint4*>(sZ + 2 * gstride + off) = pack8(zg[ch]);
+          *reinterpret_cast<uint4*>(sZ + 3 * gstride + off) = pack8(zo[ch]);
+        }
+      }
+      if (t > 0) {
+        fence_proxy_async_smem();
+        tc_fence_before();
+        named_bar_arrive(BAR_H, R_ALL);
+      }
+      // ---- off the critical path: global dz image, input-kernel / bias gradient partials ----
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        if (!live[ch]) continue;
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint4* dzp = p.dz + ((size_t)t * p.B8 + ((b0 + col0) >> 3)) * GH + j;
+        dzp[0 * RH] = pack8(zi[ch]); dzp[1 * RH] = pack8(zf[ch]); dzp[2 * RH] = pack8(zg[ch]); dzp[3 * RH] = pack8(zo[ch]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float xv = sX[(col0 + e) * T + t];
+          acc_w[0] = fmaf(xv, zi[ch][e], acc_w[0]); acc_w[1] = fmaf(xv, zf[ch][e], acc_w[1]);
+          acc_w[2] = fmaf(xv, zg[ch][e], acc_w[2]); acc_w[3] = fmaf(xv, zo[ch][e], acc_w[3]);
+          acc_b[0] += zi[ch][e]; acc_b[1] += zf[ch][e]; acc_b[2] += zg[ch][e]; acc_b[3] += zo[ch][e];
+        }
+      }
+    }
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      atomicAdd(p.d_wih + g * RH + j, acc_w[g]);
+      atomicAdd(p.d_bias + g * RH + j, acc_b[g]);
+    }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem, TM_COLS);
+  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
+}
+
+// ======================================================================================================
+// GRU(128), reset_after = False.  Per step two dependent tensor-core phases:
+//   batch A: [z | r] = Uzrᵀ·h + x-terms, plus the x-term of the candidate;   batch B: candidate += Uhᵀ·(r ⊙ h)
+// ======================================================================================================
+struct GruV2Fwd {
+  const float* x;
+  const __nv_bfloat16* img;       // [18][48][8][8]
+  float* out;
+  uint4* hs;                      // [T][B8][128] x 16 B   h_t (bf16 image)
+  uint4* rh;                      // [T][B8][128] x 16 B   r_t ⊙ h_{t-1} (bf16 image)
+  uint4* zrh;                     // [T][B8][3][128] x 16 B  z, r, hh (bf16)
+  float4* hprev;                  // [T][B8][128] x 32 B   h_{t-1} (fp32)
+  int B, T, B8;
+  int return_sequences, save;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int GH = 3 * RH, MG = GH / 8;                    // 384, 48
+  constexpr uint32_t W_LBO = MG * 128;                       // 6144
+  constexpr int W_BYTES = R_KG * MG * 128;                   // 110,592
+  constexpr int CH8 = NB / 32;
+  uint8_t* sW = smem;
+  uint8_t* sH = sW + W_BYTES;
+  uint8_t* sR = sH + RH * NB * 2;
+  uint8_t* sX = sR + RH * NB * 2;
+  uint8_t* sZero = sX + (size_t)p.T * NB * 16;
+  __shared__ uint64_t bar_w, bar_a, bar_b;
+  __shared__ uint32_t tmem_s;
+  constexpr uint32_t TM_COLS = NB <= 32 ? 128 : 256;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b0 = blockIdx.x * NB;
+  const int T = p.T, B = p.B;
+
+  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_a, 1); mbar_init(&bar_b, 1); mbar_fence_init(); }
+  __syncthreads();
+  if (tid == R_EPI) {
+    mbar_expect_tx(&bar_w, W_BYTES);
+#pragma unroll
+    for (int c = 0; c < R_KG; ++c)
+      tma_bulk_g2s(sW + c * (MG * 128), reinterpret_cast<const uint8_t*>(p.img) + (size_t)c * (MG * 128), MG * 128, &bar_w);
+  }
+  build_x_image<NB>(sX, sZero, p.x, b0, B, T);
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_s;
+
+  if (warp == 16) {
+    constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
+    const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), r_base = smem_u32(sR), x_base = smem_u32(sX),
+                   z_base = smem_u32(sZero);
+    mbar_wait(&bar_w, 0);
+    for (int t = 0; t < T; ++t) {
+      if (t > 0) named_bar_sync(BAR_H, R_ALL);
+      tc_fence_after();
+      const uint32_t xt = x_base + t * (NB * 16);
+      if (elect_one()) {
+#pragma unroll
+        for (int g = 0; g < 3; ++g) {
+          if (t > 0 && g < 2) {
+#pragma unroll
+            for (int ks = 0; ks < RH / 16; ++ks)
+              umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
+                        umma_desc(h_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+          }
+          umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + 16 * W_LBO, W_LBO, 128),
+                    umma_desc(xt, z_base - xt, 128), idesc, t > 0 && g < 2);
+        }
+        umma_commit(&bar_a);
+      }
+      __syncwarp();
+      if (t > 0) {
+        named_bar_sync(BAR_R, R_ALL);                        // r ⊙ h is in shared memory
+        tc_fence_after();
+        if (elect_one()) {
+#pragma unroll
+          for (int ks = 0; ks < RH / 16; ++ks)
+            umma_bf16(tmem + 2 * NB, umma_desc(w_base + 2 * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
+                      umma_desc(r_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, true);
+          umma_commit(&bar_b);
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    const int q = warp & 3, cgp = warp >> 2;
+    const int j = q * 32 + lane;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    float hreg[CH8 * 8];
+#pragma unroll
+    for (int i = 0; i < CH8 * 8; ++i) hreg[i] = 0.f;
+    uint32_t pha = 0, phb = 0;
+    for (int t = 0; t < T; ++t) {
+      const bool last = (t == T - 1);
+      mbar_wait(&bar_a, pha);
+      pha ^= 1;
+      tc_fence_after();
+      float z[CH8][8], r[CH8][8], rhv[CH8][8], hp[CH8][8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint32_t vz[8], vr[8];
+        tmem_ld8(t_lane + 0 * NB + col0, vz);
+        tmem_ld8(t_lane + 1 * NB + col0, vr);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          z[ch][e] = __saturatef(fmaf(0.2f, __uint_as_float(vz[e]), 0.5f));
+          r[ch][e] = __saturatef(fmaf(0.2f, __uint_as_float(vr[e]), 0.5f));
+          hp[ch][e] = hreg[ch * 8 + e];
+          rhv[ch][e] = r[ch][e] * hp[ch][e];
+        }
+        if (t > 0) *reinterpret_cast<uint4*>(sR + (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16) = pack8(rhv[ch]);
+      }
+      if (t > 0) {
+        fence_proxy_async_smem();
+        tc_fence_before();
+        named_bar_arrive(BAR_R, R_ALL);
+      }
+      if (p.save) {                                          // overlaps the candidate MMAs
+#pragma unroll
+        for (int ch = 0; ch < CH8; ++ch) {
+          const int col0 = (cgp * CH8 + ch) * 8;
+          const int bc = (b0 + col0) >> 3;
+          if (bc < p.B8) {
+            const size_t base = (size_t)t * p.B8 + bc;
+            p.rh[base * RH + j] = pack8(rhv[ch]);
+            uint4* zd = p.zrh + base * 3 * RH + j;
+            zd[0] = pack8(z[ch]); zd[RH] = pack8(r[ch]);
+            float4* hd = p.hprev + (base * RH + j) * 2;
+            hd[0] = make_float4(hp[ch][0], hp[ch][1], hp[ch][2], hp[ch][3]);
+            hd[1] = make_float4(hp[ch][4], hp[ch][5], hp[ch][6], hp[ch][7]);
+          }
+        }
+      }
+      if (t > 0) {
+        mbar_wait(&bar_b, phb);
+        phb ^= 1;
+        tc_fence_after();
+      }
+      float hh[CH8][8], hn[CH8][8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint32_t vh[8];
+        tmem_ld8(t_lane + 2 * NB + col0, vh);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          hh[ch][e] = fast_tanh(__uint_as_float(vh[e]));
+          hn[ch][e] = fmaf(z[ch][e], hp[ch][e] - hh[ch][e], hh[ch][e]);     // z*h + (1-z)*hh
+          hreg[ch * 8 + e] = hn[ch][e];
+        }
+        if (!last) *reinterpret_cast<uint4*>(sH + (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16) = pack8(hn[ch]);
+      }
+      if (!last) {
+        fence_proxy_async_smem();
+        tc_fence_before();
+        named_bar_arrive(BAR_H, R_ALL);
+      }
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        const int bc = (b0 + col0) >> 3;
+        if (bc < p.B8) {
+          if (p.save) {
+            const size_t base = (size_t)t * p.B8 + bc;
+            p.hs[base * RH + j] = pack8(hn[ch]);
+            p.zrh[base * 3 * RH + 2 * RH + j] = pack8(hh[ch]);
+          }
+          if (p.return_sequences || last) {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int bg = b0 + col0 + e;
+              if (bg < B) {
+                if (p.return_sequences) p.out[((size_t)bg * T + t) * RH + j] = hn[ch][e];
+                else p.out[(size_t)bg * RH + j] = hn[ch][e];
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
+}
+
+struct GruV2Bwd {
+  const float* dout;
+  const float* x;
+  const __nv_bfloat16* img;
+  const uint4* zrh;               // [T][B8][3][128]
+  const float4* hprev;            // [T][B8][128] x 2
+  uint4* da;                      // [T][B8][384] x 16 B: d(az), d(ar), d(ah)  == K-major UMMA image
+  float* d_wih;                   // [3H]
+  float* d_bias;                  // [3H]
+  int B, T, B8;
+  int return_sequences;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  constexpr int GH = 3 * RH, MG = GH / 8;
+  constexpr int W_BYTES = 16 * MG * 128;                     // 98,304
+  constexpr int CH8 = NB / 32;
+  uint8_t* sW = smem;                                        // image as K-major A (M = h_{t-1} unit, K = gate column)
+  uint8_t* sB1 = sW + W_BYTES;                               // [d(az) | d(ah)]ᵀ : k-groups 0..15 = az, 16..31 = ah
+  uint8_t* sB2 = sB1 + 2 * RH * NB * 2;                      // d(ar)ᵀ
+  float* sX = reinterpret_cast<float*>(sB2 + RH * NB * 2);
+  __shared__ uint64_t bar_w, bar_1, bar_2;
+  __shared__ uint32_t tmem_s;
+  constexpr uint32_t TM_COLS = 2 * NB < 32 ? 32 : 2 * NB;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int b0 = blockIdx.x * NB;
+  const int T = p.T, B = p.B;
+
+  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_1, 1); mbar_init(&bar_2, 1); mbar_fence_init(); }
+  __syncthreads();
+  if (tid == R_EPI) {
+    mbar_expect_tx(&bar_w, W_BYTES);
+#pragma unroll
+    for (int c = 0; c < 16; ++c)
+      tma_bulk_g2s(sW + c * (MG * 128), reinterpret_cast<const uint8_t*>(p.img) + (size_t)c * (MG * 128), MG * 128, &bar_w);
+  }
+  for (int idx = tid; idx < NB * T; idx += R_ALL) {
+    const int b = idx / T, t = idx - b * T;
+    sX[idx] = (b0 + b < B) ? p.x[(size_t)(b0 + b) * T + t] : 0.f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_s;
+
+  if (warp == 16) {
+    constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
+    const uint32_t w_base = smem_u32(sW), b1_base = smem_u32(sB1), b2_base = smem_u32(sB2);
+    mbar_wait(&bar_w, 0);
+    for (int t = T - 1; t >= 1; --t) {
+      named_bar_sync(BAR_H, R_ALL);                          // d(az), d(ah) staged
+      tc_fence_after();
+      if (elect_one()) {
+        // D1 (cols 0..NB)   = U_h · d(ah)ᵀ            (image columns 256..383 -> K chunks 32..47)
+        // D2 (cols NB..2NB) = U_z · d(az)ᵀ            (image columns 0..127   -> K chunks 0..15)
+#pragma unroll
+        for (int ks = 0; ks < RH / 16; ++ks)
+          umma_bf16(tmem, umma_desc(w_base + (32 + ks * 2) * 128, 128, MG * 128),
+                    umma_desc(b1_base + (16 + ks * 2) * (NB * 16), NB * 16, 128), idesc, ks > 0);
+#pragma unroll
+        for (int ks = 0; ks < RH / 16; ++ks)
+          umma_bf16(tmem + NB, umma_desc(w_base + (ks * 2) * 128, 128, MG * 128),
+                    umma_desc(b1_base + (ks * 2) * (NB * 16), NB * 16, 128), idesc, ks > 0);
+        umma_commit(&bar_1);
+      }
+      __syncwarp();
+      named_bar_sync(BAR_R, R_ALL);                          // d(ar) staged
+      tc_fence_after();
+      if (elect_one()) {
+        // D2 += U_r · d(ar)ᵀ                             (image columns 128..255 -> K chunks 16..31)
+#pragma unroll
+        for (int ks = 0; ks < RH / 16; ++ks)
+          umma_bf16(tmem + NB, umma_desc(w_base + (16 + ks * 2) * 128, 128, MG * 128),
+                    umma_desc(b2_base + (ks * 2) * (NB * 16), NB * 16, 128), idesc, true);
+        umma_commit(&bar_2);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int q = warp & 3, cgp = warp >> 2;
+    const int j = q * 32 + lane;
+    const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    float dh[CH8 * 8];
+#pragma unroll
+    for (int i = 0; i < CH8 * 8; ++i) dh[i] = 0.f;
+    float acc_w[3] = {0.f, 0.f, 0.f}, acc_b[3] = {0.f, 0.f, 0.f};
+    uint32_t ph1 = 0, ph2 = 0;
+    for (int t = T - 1; t >= 0; --t) {
+      uint4 g3[CH8][3];
+      float4 hpv[CH8][2];
+      float dext[CH8][8];
+      bool live[CH8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        const int bc = (b0 + col0) >> 3;
+        live[ch] = bc < p.B8;
+        if (live[ch]) {
+          const size_t base = (size_t)t * p.B8 + bc;
+          const uint4* gs = p.zrh + base * 3 * RH + j;
+          g3[ch][0] = gs[0]; g3[ch][1] = gs[RH]; g3[ch][2] = gs[2 * RH];
+          const float4* hh = p.hprev + (base * RH + j) * 2;
+          hpv[ch][0] = hh[0]; hpv[ch][1] = hh[1];
+        }
+        if (p.return_sequences || t == T - 1) {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int bg = b0 + col0 + e;
+            float d = 0.f;
+            if (bg < B) d = p.return_sequences ? p.dout[((size_t)bg * T + t) * RH + j] : p.dout[(size_t)bg * RH + j];
+            dext[ch][e] = d;
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) dext[ch][e] = 0.f;
+        }
+      }
+      // ---- stage 1: d(ah), d(az) ----
+      float daz[CH8][8], dah[CH8][8], pdh[CH8][8], zv[CH8][8], rv[CH8][8], hp[CH8][8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        if (live[ch]) {
+          float hh[8];
+          unpack8(g3[ch][0], zv[ch]); unpack8(g3[ch][1], rv[ch]); unpack8(g3[ch][2], hh);
+          const float* hpf = reinterpret_cast<const float*>(&hpv[ch][0]);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            hp[ch][e] = hpf[e];
+            const float d = dh[ch * 8 + e] + dext[ch][e];
+            dah[ch][e] = d * (1.f - zv[ch][e]) * (1.f - hh[e] * hh[e]);
+            daz[ch][e] = d * (hp[ch][e] - hh[e]) * hs_grad(zv[ch][e]);
+            pdh[ch][e] = d * zv[ch][e];
+          }
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) { dah[ch][e] = daz[ch][e] = pdh[ch][e] = zv[ch][e] = rv[ch][e] = hp[ch][e] = 0.f; }
+        }
+        if (t > 0) {
+          const uint32_t off = (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16;
+          *reinterpret_cast<uint4*>(sB1 + off) = pack8(daz[ch]);
+          *reinterpret_cast<uint4*>(sB1 + 16 * (NB * 16) + off) = pack8(dah[ch]);
+        }
+      }
+      if (t > 0) {
+        fence_proxy_async_smem();
+        tc_fence_before();
+        named_bar_arrive(BAR_H, R_ALL);
+      }
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {                     // off the critical path
+        if (!live[ch]) continue;
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint4* dap = p.da + ((size_t)t * p.B8 + ((b0 + col0) >> 3)) * GH + j;
+        dap[0] = pack8(daz[ch]); dap[2 * RH] = pack8(dah[ch]);
+        if (t == 0) { const float zero8[8] = {0, 0, 0, 0, 0, 0, 0, 0}; dap[RH] = pack8(zero8); }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float xv = sX[(col0 + e) * T + t];
+          acc_w[0] = fmaf(xv, daz[ch][e], acc_w[0]); acc_b[0] += daz[ch][e];
+          acc_w[2] = fmaf(xv, dah[ch][e], acc_w[2]); acc_b[2] += dah[ch][e];
+        }
+      }
+      if (t == 0) break;
+      // ---- stage 2: drh -> d(ar) ----
+      mbar_wait(&bar_1, ph1);
+      ph1 ^= 1;
+      tc_fence_after();
+      float dar[CH8][8];
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint32_t vd[8];
+        tmem_ld8(t_lane + col0, vd);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float drh = live[ch] ? __uint_as_float(vd[e]) : 0.f;
+          dar[ch][e] = drh * hp[ch][e] * hs_grad(rv[ch][e]);
+          pdh[ch][e] = fmaf(drh, rv[ch][e], pdh[ch][e]);
+        }
+        *reinterpret_cast<uint4*>(sB2 + (j >> 3) * (NB * 16) + (col0 >> 3) * 128 + (j & 7) * 16) = pack8(dar[ch]);
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      named_bar_arrive(BAR_R, R_ALL);
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        if (!live[ch]) continue;
+        const int col0 = (cgp * CH8 + ch) * 8;
+        p.da[((size_t)t * p.B8 + ((b0 + col0) >> 3)) * GH + RH + j] = pack8(dar[ch]);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const float xv = sX[(col0 + e) * T + t];
+          acc_w[1] = fmaf(xv, dar[ch][e], acc_w[1]); acc_b[1] += dar[ch][e];
+        }
+      }
+      mbar_wait(&bar_2, ph2);
+      ph2 ^= 1;
+      tc_fence_after();
+#pragma unroll
+      for (int ch = 0; ch < CH8; ++ch) {
+        const int col0 = (cgp * CH8 + ch) * 8;
+        uint32_t vd[8];
+        tmem_ld8(t_lane + NB + col0, vd);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 8; ++e) dh[ch * 8 + e] = pdh[ch][e] + (live[ch] ? __uint_as_float(vd[e]) : 0.f);
+      }
+      // the next iteration's stage-1 stores and MMAs are ordered behind these TMEM reads by the BAR_H arrive
+    }
+#pragma unroll
+    for (int g = 0; g < 3; ++g) {
+      atomicAdd(p.d_wih + g * RH + j, acc_w[g]);
+      atomicAdd(p.d_bias + g * RH + j, acc_b[g]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -498,10 +949,10 @@ extern "C" int ddls_lstm128_forward_v2(const float* x, const void* image, float*
   if (smem > 227 * 1024) { set_last_error("ddls_lstm128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
   if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<32><<<(B + 31) / 32, RT, smem, st>>>(p);
+    lstm_fwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<64><<<(B + 63) / 64, RT, smem, st>>>(p);
+    lstm_fwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
   } else { set_last_error("ddls_lstm128_forward_v2: tile must be 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_fwd_v2_kernel launch");
@@ -519,10 +970,10 @@ extern "C" int ddls_lstm128_backward_v2(const float* dout, const float* x, const
   if (smem > 227 * 1024) { set_last_error("ddls_lstm128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
   if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<32><<<(B + 31) / 32, RT, smem, st>>>(p);
+    lstm_bwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<64><<<(B + 63) / 64, RT, smem, st>>>(p);
+    lstm_bwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
   } else { set_last_error("ddls_lstm128_backward_v2: tile must be 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_bwd_v2_kernel launch");
@@ -541,4 +992,46 @@ extern "C" int ddls_rnn128_wgrad(const void* a_img, const void* b_img, float* C,
       static_cast<const uint8_t*>(a_img), static_cast<const uint8_t*>(b_img), C, kgroups, b_ntotal, b_noff, ldc);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "rnn128_wgrad_kernel launch");
+}
+
+extern "C" int ddls_gru128_forward_v2(const float* x, const void* image, float* out, void* hs, void* rh, void* zrh,
+                                      void* hprev, int B, int T, int return_sequences, int save_for_backward, int tile,
+                                      void* stream) {
+  if (B <= 0 || T <= 0) { set_last_error("ddls_gru128_forward_v2: empty problem"); return 1; }
+  GruV2Fwd p{x, static_cast<const __nv_bfloat16*>(image), out, static_cast<uint4*>(hs), static_cast<uint4*>(rh),
+             static_cast<uint4*>(zrh), static_cast<float4*>(hprev), B, T, (B + 7) / 8, return_sequences, save_for_backward};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = pick_tile(B, tile);
+  const size_t smem = (size_t)R_KG * 48 * 128 + 2 * (size_t)RH * nb * 2 + (size_t)T * nb * 16 + (size_t)nb * 16;
+  if (smem > 227 * 1024) { set_last_error("ddls_gru128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
+  if (nb == 32) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gru_fwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
+  } else if (nb == 64) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gru_fwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
+  } else { set_last_error("ddls_gru128_forward_v2: tile must be 32 or 64"); return 1; }
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "gru_fwd_v2_kernel launch");
+}
+
+extern "C" int ddls_gru128_backward_v2(const float* dout, const float* x, const void* image, const void* zrh,
+                                       const void* hprev, void* da, float* d_wih, float* d_bias, int B, int T,
+                                       int return_sequences, int tile, void* stream) {
+  if (B <= 0 || T <= 0) { set_last_error("ddls_gru128_backward_v2: empty problem"); return 1; }
+  GruV2Bwd p{dout, x, static_cast<const __nv_bfloat16*>(image), static_cast<const uint4*>(zrh),
+             static_cast<const float4*>(hprev), static_cast<uint4*>(da), d_wih, d_bias, B, T, (B + 7) / 8, return_sequences};
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int nb = pick_tile(B, tile);
+  const size_t smem = (size_t)16 * 48 * 128 + 3 * (size_t)RH * nb * 2 + (size_t)nb * T * 4;
+  if (smem > 227 * 1024) { set_last_error("ddls_gru128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
+  if (nb == 32) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gru_bwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
+  } else if (nb == 64) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gru_bwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
+  } else { set_last_error("ddls_gru128_backward_v2: tile must be 32 or 64"); return 1; }
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "gru_bwd_v2_kernel launch");
 }

@@ -213,6 +213,19 @@ class DirectStep:
                                 dense.kernel.grad, dense.bias.grad)
             R.lstm_v2_backward(dh, x2, img, gates2, cs2, dz2, k.grad, b.grad, r.grad, B, T, False, hs2)
             return loss
+        if (not is_lstm) and R.use_v2():
+            key = ('gru_v2', B, T)
+            bufs = self._bufs.get(key)
+            if bufs is None:
+                bufs = self._bufs[key] = R.gru_v2_buffers(B, T, self.dev) + (
+                    torch.empty(18 * 48 * 64, dtype=bf, device=self.dev),)
+            hs2, rh2, zrh2, hprev2, da2, img = bufs
+            R.pack_image(r, k, b, 3, out=img)
+            R.gru_v2_forward(x2, img, h, hs2, rh2, zrh2, hprev2, B, T, False, True)
+            heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh,
+                                dense.kernel.grad, dense.bias.grad)
+            R.gru_v2_backward(dh, x2, img, zrh2, hprev2, da2, k.grad, b.grad, r.grad, B, T, False, hs2, rh2)
+            return loss
         if is_lstm:
             gates = self._buf('gates', (T, B, H, 4), bf)
             cs = self._buf('cs', (T, B, H), f32)

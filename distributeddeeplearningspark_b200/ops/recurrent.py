@@ -18,6 +18,9 @@ N.register('ddls_lstm128_forward_v2', [P, P, P, P, P, P, I, I, I, I, I, P])
 N.register('ddls_lstm128_backward_v2', [P, P, P, P, P, P, P, P, I, I, I, I, P])
 N.register('ddls_rnn128_wgrad', [P, P, P, I, I, I, I, I, P])
 
+N.register('ddls_gru128_forward_v2', [P, P, P, P, P, P, P, I, I, I, I, I, P])
+N.register('ddls_gru128_backward_v2', [P, P, P, P, P, P, P, P, I, I, I, I, P])
+
 H = 128
 
 
@@ -81,6 +84,74 @@ def native_available(x: torch.Tensor, units: int) -> bool:
 
 def _wgrad_split(k: int) -> int:
     return max(1, min(32, k // 64))
+
+
+def gru_v2_buffers(B: int, T: int, dev):
+    B8 = (B + 7) // 8
+    hs = torch.zeros(((T * B8 + 8) * H * 8,), dtype=torch.bfloat16, device=dev)
+    rh = torch.zeros(((T * B8 + 8) * H * 8,), dtype=torch.bfloat16, device=dev)
+    zrh = torch.empty((T * B8 * 3 * H * 8,), dtype=torch.bfloat16, device=dev)
+    hprev = torch.empty((T * B8 * H * 8,), dtype=torch.float32, device=dev)
+    da = torch.zeros(((T * B8 + 8) * 3 * H * 8,), dtype=torch.bfloat16, device=dev)
+    return hs, rh, zrh, hprev, da
+
+
+def gru_v2_forward(x2, img, out, hs, rh, zrh, hprev, B, T, return_sequences, save):
+    N.call('ddls_gru128_forward_v2', x2.data_ptr(), img.data_ptr(), out.data_ptr(), N.ptr(hs), N.ptr(rh), N.ptr(zrh),
+           N.ptr(hprev), B, T, int(return_sequences), int(save), 0, N.stream_ptr(x2.device))
+
+
+def gru_v2_backward(dout, x2, img, zrh, hprev, da, d_wih, d_bias, d_rec, B, T, return_sequences, hs, rh):
+    N.call('ddls_gru128_backward_v2', dout.data_ptr(), x2.data_ptr(), img.data_ptr(), zrh.data_ptr(), hprev.data_ptr(),
+           da.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(return_sequences), 0, N.stream_ptr(x2.device))
+    B8 = (B + 7) // 8
+    if T > 1:
+        st = N.stream_ptr(x2.device)
+        kg = kgroups_padded(T, B8)
+        b_img = da.data_ptr() + B8 * 3 * H * 16
+        # dU_z, dU_r: h_{t-1}^T · [d(az) | d(ar)] ;  dU_h: (r ⊙ h_{t-1})^T · d(ah)
+        N.call('ddls_rnn128_wgrad', hs.data_ptr(), b_img, d_rec.data_ptr(), kg, 2 * H, 3 * H, 0, d_rec.stride(0), st)
+        N.call('ddls_rnn128_wgrad', rh.data_ptr() + B8 * H * 16, b_img, d_rec.data_ptr() + 2 * H * 4, kg, H, 3 * H, 2 * H,
+               d_rec.stride(0), st)
+    else:
+        d_rec.zero_()
+
+
+class _GRU128v2(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, kernel, recurrent, bias, return_sequences):
+        B, T, _ = x.shape
+        dev = x.device
+        x2 = x.reshape(B, T).contiguous()
+        need_bwd = any(ctx.needs_input_grad)
+        out = torch.empty((B, T, H) if return_sequences else (B, H), dtype=torch.float32, device=dev)
+        img = pack_image(recurrent, kernel, bias, 3)
+        if need_bwd:
+            hs, rh, zrh, hprev, da = gru_v2_buffers(B, T, dev)
+        else:
+            hs = rh = zrh = hprev = da = None
+        gru_v2_forward(x2, img, out, hs, rh, zrh, hprev, B, T, return_sequences, need_bwd)
+        if need_bwd:
+            ctx.save_for_backward(x2, kernel, img, hs, rh, zrh, hprev, da)
+            ctx.return_sequences = return_sequences
+            ctx.dims = (B, T)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x2, kernel, img, hs, rh, zrh, hprev, da = ctx.saved_tensors
+        B, T = ctx.dims
+        dev = x2.device
+        small = torch.zeros(6 * H, dtype=torch.float32, device=dev)
+        d_wih, d_bias = small[:3 * H], small[3 * H:]
+        d_rec = torch.empty((H, 3 * H), dtype=torch.float32, device=dev)
+        gru_v2_backward(dout.contiguous(), x2, img, zrh, hprev, da, d_wih, d_bias, d_rec, B, T, ctx.return_sequences, hs, rh)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            B8 = (B + 7) // 8
+            daf = da[:T * B8 * 3 * H * 8].view(T, B8, 3 * H, 8).permute(0, 1, 3, 2).reshape(T, B8 * 8, 3 * H)[:, :B].float()
+            dx = (daf @ kernel.t()).permute(1, 0, 2).contiguous()
+        return dx, d_wih.view(1, 3 * H), d_rec, d_bias, None
 
 
 class _LSTM128v2(torch.autograd.Function):
@@ -221,4 +292,5 @@ class _GRU128(torch.autograd.Function):
 
 
 def gru_layer(x, kernel, recurrent, bias, return_sequences=False):
-    return _GRU128.apply(x, kernel, recurrent, bias, bool(return_sequences))
+    fn = _GRU128v2 if use_v2() else _GRU128
+    return fn.apply(x, kernel, recurrent, bias, bool(return_sequences))

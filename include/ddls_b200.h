@@ -91,6 +91,13 @@ int ddls_lstm128_forward_v2(const float* x, const void* image, float* out, void*
 int ddls_lstm128_backward_v2(const float* dout, const float* x, const void* image, const void* gates, const void* cs,
                              void* dz, float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile,
                              void* stream);
+/* GRU: hs, rh: [T][B8][128] x 16 B images (h_t, r_t*h_{t-1}); zrh: [T][B8][3][128] x 16 B (z, r, hh);
+ * hprev: [T][B8][128] x 32 B (fp32 h_{t-1}); da: [T][B8][384] x 16 B image of d(az), d(ar), d(ah). */
+int ddls_gru128_forward_v2(const float* x, const void* image, float* out, void* hs, void* rh, void* zrh, void* hprev,
+                           int B, int T, int return_sequences, int save_for_backward, int tile, void* stream);
+int ddls_gru128_backward_v2(const float* dout, const float* x, const void* image, const void* zrh, const void* hprev,
+                            void* da, float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile,
+                            void* stream);
 /* C[128, n] (ldc) = sum_g A_img[g]^T · B_img[g][b_noff : b_noff+n]; images as above, kgroups % 8 == 0, n % 64 == 0. */
 int ddls_rnn128_wgrad(const void* a_img, const void* b_img, float* C, int kgroups, int n, int b_ntotal, int b_noff,
                       int ldc, void* stream);
