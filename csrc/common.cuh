@@ -162,6 +162,24 @@ DDLS_DEVINL void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, ui
       "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate ? 1u : 0u)
       : "memory");
 }
+// Split form: descriptor low words (start address | LBO) are precomputed once per kernel and kept in
+// registers; the high word (SBO | version) is a constant per operand.  Keeps the per-MMA issue sequence short.
+DDLS_DEVINL constexpr uint32_t umma_desc_hi(uint32_t sbo_bytes) { return ((sbo_bytes >> 4) & 0x3FFFu) | (1u << 14); }
+DDLS_DEVINL uint32_t umma_desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+DDLS_DEVINL void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, uint32_t b_lo, uint32_t b_hi,
+                                uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\t"
+      "setp.ne.b32 p, %6, 0;\n\t"
+      "mov.b64 da, {%1, %2};\n\t"
+      "mov.b64 db, {%3, %4};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %5, p;\n\t}" ::"r"(tmem_d),
+      "r"(a_lo), "r"(a_hi), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate ? 1u : 0u)
+      : "memory");
+}
+
 // All previously issued UMMAs of this thread arrive on the mbarrier when complete
 // (implies tcgen05.fence::before_thread_sync).
 DDLS_DEVINL void umma_commit(uint64_t* bar) {

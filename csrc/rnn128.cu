@@ -133,23 +133,28 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
     // ================= MMA warp: the whole warp runs the (warp-uniform) loop, one elected lane issues =================
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
     const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), x_base = smem_u32(sX), z_base = smem_u32(sZero);
+    // descriptor low words never change: build them once, keep them in registers
+    constexpr uint32_t hi = umma_desc_hi(128);
+    // (start addresses are < 256 KB, so adding a 16-byte-unit offset never carries into the LBO field)
+    const uint32_t a_lo0 = umma_desc_lo(w_base, W_LBO), b_lo0 = umma_desc_lo(h_base, NB * 16);
+    const bool leader = elect_one();
     mbar_wait(&bar_w, 0);
     for (int t = 0; t < T; ++t) {
       if (t > 0) named_bar_sync(BAR_H, R_ALL);               // h_{t-1} is in shared memory, TMEM has been drained
       tc_fence_after();
-      if (elect_one()) {
+      if (leader) {
         const uint32_t xt = x_base + t * (NB * 16);
+        const uint32_t x_lo = umma_desc_lo(xt, z_base - xt);
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           if (t > 0) {
 #pragma unroll
             for (int ks = 0; ks < RH / 16; ++ks)
-              umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
-                        umma_desc(h_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+              umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + ks * 2 * W_LBO) >> 4), hi,
+                             b_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi, idesc, ks > 0);
           }
           // input projection + bias: image k-groups 16 (payload) / 17 (zeros) times [x rows of step t | zero group]
-          umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + 16 * W_LBO, W_LBO, 128),
-                    umma_desc(xt, z_base - xt, 128), idesc, t > 0);
+          umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + 16 * W_LBO) >> 4), hi, x_lo, hi, idesc, t > 0);
         }
         umma_commit(&bar_mma);
       }
@@ -279,15 +284,17 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   if (warp == 16) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
     const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
+    constexpr uint32_t a_hi = umma_desc_hi(MG * 128), b_hi = umma_desc_hi(128);
+    const uint32_t a_lo0 = umma_desc_lo(w_base, 128), b_lo0 = umma_desc_lo(z_base, NB * 16);
+    const bool leader = elect_one();
     mbar_wait(&bar_w, 0);
     for (int t = T - 1; t >= 1; --t) {
       named_bar_sync(BAR_H, R_ALL);                          // dz_t is in shared memory
       tc_fence_after();
-      if (elect_one()) {
-#pragma unroll 8
+      if (leader) {
+#pragma unroll
         for (int ks = 0; ks < GH / 16; ++ks)
-          umma_bf16(tmem, umma_desc(w_base + ks * 2 * 128, 128, MG * 128),
-                    umma_desc(z_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+          umma_bf16_lohi(tmem, a_lo0 + ((ks * 2 * 128) >> 4), a_hi, b_lo0 + ((ks * 2 * (NB * 16)) >> 4), b_hi, idesc, ks > 0);
         umma_commit(&bar_mma);
       }
       __syncwarp();
@@ -466,22 +473,26 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
     const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), r_base = smem_u32(sR), x_base = smem_u32(sX),
                    z_base = smem_u32(sZero);
+    constexpr uint32_t hi = umma_desc_hi(128);
+    const uint32_t a_lo0 = umma_desc_lo(w_base, W_LBO), h_lo0 = umma_desc_lo(h_base, NB * 16),
+                   r_lo0 = umma_desc_lo(r_base, NB * 16);
+    const bool leader = elect_one();
     mbar_wait(&bar_w, 0);
     for (int t = 0; t < T; ++t) {
       if (t > 0) named_bar_sync(BAR_H, R_ALL);
       tc_fence_after();
-      const uint32_t xt = x_base + t * (NB * 16);
-      if (elect_one()) {
+      if (leader) {
+        const uint32_t xt = x_base + t * (NB * 16);
+        const uint32_t x_lo = umma_desc_lo(xt, z_base - xt);
 #pragma unroll
         for (int g = 0; g < 3; ++g) {
           if (t > 0 && g < 2) {
 #pragma unroll
             for (int ks = 0; ks < RH / 16; ++ks)
-              umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
-                        umma_desc(h_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, ks > 0);
+              umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + ks * 2 * W_LBO) >> 4), hi,
+                             h_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi, idesc, ks > 0);
           }
-          umma_bf16(tmem + g * NB, umma_desc(w_base + g * 16 * 128 + 16 * W_LBO, W_LBO, 128),
-                    umma_desc(xt, z_base - xt, 128), idesc, t > 0 && g < 2);
+          umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + 16 * W_LBO) >> 4), hi, x_lo, hi, idesc, t > 0 && g < 2);
         }
         umma_commit(&bar_a);
       }
@@ -489,11 +500,11 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
       if (t > 0) {
         named_bar_sync(BAR_R, R_ALL);                        // r ⊙ h is in shared memory
         tc_fence_after();
-        if (elect_one()) {
+        if (leader) {
 #pragma unroll
           for (int ks = 0; ks < RH / 16; ++ks)
-            umma_bf16(tmem + 2 * NB, umma_desc(w_base + 2 * 16 * 128 + ks * 2 * W_LBO, W_LBO, 128),
-                      umma_desc(r_base + ks * 2 * (NB * 16), NB * 16, 128), idesc, true);
+            umma_bf16_lohi(tmem + 2 * NB, a_lo0 + ((2 * 16 * 128 + ks * 2 * W_LBO) >> 4), hi,
+                           r_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi, idesc, true);
           umma_commit(&bar_b);
         }
         __syncwarp();
@@ -655,32 +666,34 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   if (warp == 16) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
     const uint32_t w_base = smem_u32(sW), b1_base = smem_u32(sB1), b2_base = smem_u32(sB2);
+    constexpr uint32_t a_hi = umma_desc_hi(MG * 128), b_hi = umma_desc_hi(128);
+    const uint32_t a_lo0 = umma_desc_lo(w_base, 128), b1_lo0 = umma_desc_lo(b1_base, NB * 16),
+                   b2_lo0 = umma_desc_lo(b2_base, NB * 16);
+    constexpr uint32_t A_STEP = (2 * 128) >> 4, B_STEP = (2 * NB * 16) >> 4;       // per K = 16 step, in 16-byte units
+    const bool leader = elect_one();
     mbar_wait(&bar_w, 0);
     for (int t = T - 1; t >= 1; --t) {
       named_bar_sync(BAR_H, R_ALL);                          // d(az), d(ah) staged
       tc_fence_after();
-      if (elect_one()) {
-        // D1 (cols 0..NB)   = U_h · d(ah)ᵀ            (image columns 256..383 -> K chunks 32..47)
-        // D2 (cols NB..2NB) = U_z · d(az)ᵀ            (image columns 0..127   -> K chunks 0..15)
+      if (leader) {
+        // D1 (cols 0..NB)   = U_h · d(ah)ᵀ            (image columns 256..383 -> K chunk pairs 16..23)
+        // D2 (cols NB..2NB) = U_z · d(az)ᵀ            (image columns 0..127   -> K chunk pairs 0..7)
 #pragma unroll
         for (int ks = 0; ks < RH / 16; ++ks)
-          umma_bf16(tmem, umma_desc(w_base + (32 + ks * 2) * 128, 128, MG * 128),
-                    umma_desc(b1_base + (16 + ks * 2) * (NB * 16), NB * 16, 128), idesc, ks > 0);
+          umma_bf16_lohi(tmem, a_lo0 + (16 + ks) * A_STEP, a_hi, b1_lo0 + (8 + ks) * B_STEP, b_hi, idesc, ks > 0);
 #pragma unroll
         for (int ks = 0; ks < RH / 16; ++ks)
-          umma_bf16(tmem + NB, umma_desc(w_base + (ks * 2) * 128, 128, MG * 128),
-                    umma_desc(b1_base + (ks * 2) * (NB * 16), NB * 16, 128), idesc, ks > 0);
+          umma_bf16_lohi(tmem + NB, a_lo0 + ks * A_STEP, a_hi, b1_lo0 + ks * B_STEP, b_hi, idesc, ks > 0);
         umma_commit(&bar_1);
       }
       __syncwarp();
       named_bar_sync(BAR_R, R_ALL);                          // d(ar) staged
       tc_fence_after();
-      if (elect_one()) {
-        // D2 += U_r · d(ar)ᵀ                             (image columns 128..255 -> K chunks 16..31)
+      if (leader) {
+        // D2 += U_r · d(ar)ᵀ                             (image columns 128..255 -> K chunk pairs 8..15)
 #pragma unroll
         for (int ks = 0; ks < RH / 16; ++ks)
-          umma_bf16(tmem + NB, umma_desc(w_base + (16 + ks * 2) * 128, 128, MG * 128),
-                    umma_desc(b2_base + (ks * 2) * (NB * 16), NB * 16, 128), idesc, true);
+          umma_bf16_lohi(tmem + NB, a_lo0 + (8 + ks) * A_STEP, a_hi, b2_lo0 + ks * B_STEP, b_hi, idesc, true);
         umma_commit(&bar_2);
       }
       __syncwarp();
