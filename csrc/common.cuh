@@ -180,6 +180,33 @@ DDLS_DEVINL void umma_bf16_lohi(uint32_t tmem_d, uint32_t a_lo, uint32_t a_hi, u
       : "memory");
 }
 
+// "TS" form: the A operand comes from tensor memory (lane = M row, two bf16 K-elements per 32-bit column, low
+// half = even k), only B is read from shared memory.  With a small N the SS form is bound by re-reading the
+// 4 KB A tile from shared memory for every MMA; a TMEM-resident A (the recurrent weights) removes that.
+DDLS_DEVINL void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint32_t b_lo, uint32_t b_hi, uint32_t idesc,
+                              bool accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 db;\n\t"
+      "setp.ne.b32 p, %5, 0;\n\t"
+      "mov.b64 db, {%2, %3};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], db, %4, p;\n\t}" ::"r"(tmem_d),
+      "r"(tmem_a), "r"(b_lo), "r"(b_hi), "r"(idesc), "r"(accumulate ? 1u : 0u)
+      : "memory");
+}
+// registers -> TMEM: each thread of the warp writes 32 consecutive 32-bit columns of its own lane
+DDLS_DEVINL void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+      "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]),
+      "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]),
+      "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+      : "memory");
+}
+DDLS_DEVINL void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
 // All previously issued UMMAs of this thread arrive on the mbarrier when complete
 // (implies tcgen05.fence::before_thread_sync).
 DDLS_DEVINL void umma_commit(uint64_t* bar) {

@@ -113,7 +113,10 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
 
-  if (warp == 16) tmem_alloc(&tmem_s, 4 * NB);
+  // TMEM: [0, 4*NB) accumulators, [A_COL0, A_COL0 + 256) the four gate tiles of Uᵀ as the resident A operand
+  constexpr uint32_t A_COL0 = 4 * NB;
+  constexpr uint32_t TM_COLS = (4 * NB + 256) <= 256 ? 256 : 512;
+  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
   if (tid == R_EPI) {                                        // bulk TMA copies bring the whole weight image
@@ -139,6 +142,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
     const uint32_t a_lo0 = umma_desc_lo(w_base, W_LBO), b_lo0 = umma_desc_lo(h_base, NB * 16);
     const bool leader = elect_one();
     mbar_wait(&bar_w, 0);
+    named_bar_sync(BAR_R, R_ALL);                            // the epilogue warps have copied Uᵀ into TMEM
     for (int t = 0; t < T; ++t) {
       if (t > 0) named_bar_sync(BAR_H, R_ALL);               // h_{t-1} is in shared memory, TMEM has been drained
       tc_fence_after();
@@ -149,9 +153,9 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
         for (int g = 0; g < 4; ++g) {
           if (t > 0) {
 #pragma unroll
-            for (int ks = 0; ks < RH / 16; ++ks)
-              umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + ks * 2 * W_LBO) >> 4), hi,
-                             b_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi, idesc, ks > 0);
+            for (int ks = 0; ks < RH / 16; ++ks)      // A from TMEM: 8 columns (16 bf16) per K step
+              umma_bf16_ts(tmem + g * NB, tmem + A_COL0 + g * 64 + ks * 8, b_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi,
+                           idesc, ks > 0);
           }
           // input projection + bias: image k-groups 16 (payload) / 17 (zeros) times [x rows of step t | zero group]
           umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + 16 * W_LBO) >> 4), hi, x_lo, hi, idesc, t > 0);
@@ -165,6 +169,28 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
     const int q = warp & 3, cgp = warp >> 2;
     const int j = q * 32 + lane;
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    {
+      // Make the recurrent weights TMEM-resident: warp (q, g = cgp) copies gate tile g, rows 32q..32q+31.
+      // Row m = j of tile g is Uᵀ[g*128 + j][k], k = 0..127, read from the shared-memory image.
+      mbar_wait(&bar_w, 0);
+      const int m = cgp * RH + j;
+      const uint8_t* src = sW + (m >> 3) * 128 + (m & 7) * 2;
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        uint32_t v[32];
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+          const int k0 = half * 64 + 2 * i;
+          const uint32_t lo = *reinterpret_cast<const uint16_t*>(src + (k0 >> 3) * W_LBO + (k0 & 7) * 16);
+          const uint32_t hi16 = *reinterpret_cast<const uint16_t*>(src + ((k0 + 1) >> 3) * W_LBO + ((k0 + 1) & 7) * 16);
+          v[i] = lo | (hi16 << 16);
+        }
+        tmem_st32(t_lane + A_COL0 + cgp * 64 + half * 32, v);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      named_bar_arrive(BAR_R, R_ALL);
+    }
     float c[CH8 * 8];
 #pragma unroll
     for (int i = 0; i < CH8 * 8; ++i) c[i] = 0.f;
@@ -231,7 +257,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem, 4 * NB);
+  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
 }
 
 struct LstmV2Bwd {
