@@ -134,7 +134,8 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
 
   if (warp == 16) {
     // ================= MMA warp: the whole warp runs the (warp-uniform) loop, one elected lane issues =================
-    constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
+    constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);      // x step: A from the smem image (MN-major)
+    constexpr uint32_t idesc_ts = umma_idesc_bf16(128, NB, false, true);  // h steps: A from TMEM is K-major by construction
     const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), x_base = smem_u32(sX), z_base = smem_u32(sZero);
     // descriptor low words never change: build them once, keep them in registers
     constexpr uint32_t hi = umma_desc_hi(128);
@@ -155,7 +156,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
 #pragma unroll
             for (int ks = 0; ks < RH / 16; ++ks)      // A from TMEM: 8 columns (16 bf16) per K step
               umma_bf16_ts(tmem + g * NB, tmem + A_COL0 + g * 64 + ks * 8, b_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi,
-                           idesc, ks > 0);
+                           idesc_ts, ks > 0);
           }
           // input projection + bias: image k-groups 16 (payload) / 17 (zeros) times [x rows of step t | zero group]
           umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + 16 * W_LBO) >> 4), hi, x_lo, hi, idesc, t > 0);
