@@ -83,6 +83,43 @@ DDLS_DEVINL void unpack8(const uint4& p, float (&v)[8]) {
 #pragma unroll
   for (int i = 0; i < 4; ++i) { v[2 * i] = __low2float(h[i]); v[2 * i + 1] = __high2float(h[i]); }
 }
+// K-major view of the weight image (M = image row k, K = image column m): copy `nchunk16` x 16 columns of row
+// `row`, starting at 8-column chunk `c8_0`, into TMEM columns [tcol, tcol + nchunk16*8) of the calling thread's lane.
+template <int MG>
+DDLS_DEVINL void image_row_to_tmem(const uint8_t* sW, int row, int c8_0, int nchunk32, uint32_t taddr) {
+  const uint8_t* src = sW + (row >> 3) * (MG * 128) + (row & 7) * 16;
+  for (int h = 0; h < nchunk32; ++h) {            // 32 TMEM columns = 64 bf16 = 8 chunks of 16 bytes
+    uint32_t v[32];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+      const uint4 u = *reinterpret_cast<const uint4*>(src + (c8_0 + h * 8 + c) * 128);
+      v[4 * c] = u.x; v[4 * c + 1] = u.y; v[4 * c + 2] = u.z; v[4 * c + 3] = u.w;
+    }
+    tmem_st32(taddr + h * 32, v);
+  }
+  tmem_st_wait();
+}
+
+// MN-major view (M = image column m, K = image row k): copy the 128 K-values of column `m` (gathered 2 bytes
+// at a time from the image) into 64 TMEM columns of the calling thread's lane.
+template <int MG>
+DDLS_DEVINL void image_col_to_tmem(const uint8_t* sW, int m, uint32_t taddr) {
+  const uint8_t* src = sW + (m >> 3) * 128 + (m & 7) * 2;
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    uint32_t v[32];
+#pragma unroll
+    for (int i = 0; i < 32; ++i) {
+      const int k0 = half * 64 + 2 * i;
+      const uint32_t lo = *reinterpret_cast<const uint16_t*>(src + (k0 >> 3) * (MG * 128) + (k0 & 7) * 16);
+      const uint32_t hi16 = *reinterpret_cast<const uint16_t*>(src + ((k0 + 1) >> 3) * (MG * 128) + ((k0 + 1) & 7) * 16);
+      v[i] = lo | (hi16 << 16);
+    }
+    tmem_st32(taddr + half * 32, v);
+  }
+  tmem_st_wait();
+}
+
 DDLS_DEVINL float hs_grad(float a) { return (a > 0.f && a < 1.f) ? 0.2f : 0.f; }   // hard_sigmoid' from its output
 
 struct LstmV2Fwd {
@@ -174,21 +211,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
       // Make the recurrent weights TMEM-resident: warp (q, g = cgp) copies gate tile g, rows 32q..32q+31.
       // Row m = j of tile g is Uᵀ[g*128 + j][k], k = 0..127, read from the shared-memory image.
       mbar_wait(&bar_w, 0);
-      const int m = cgp * RH + j;
-      const uint8_t* src = sW + (m >> 3) * 128 + (m & 7) * 2;
-#pragma unroll
-      for (int half = 0; half < 2; ++half) {
-        uint32_t v[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const int k0 = half * 64 + 2 * i;
-          const uint32_t lo = *reinterpret_cast<const uint16_t*>(src + (k0 >> 3) * W_LBO + (k0 & 7) * 16);
-          const uint32_t hi16 = *reinterpret_cast<const uint16_t*>(src + ((k0 + 1) >> 3) * W_LBO + ((k0 + 1) & 7) * 16);
-          v[i] = lo | (hi16 << 16);
-        }
-        tmem_st32(t_lane + A_COL0 + cgp * 64 + half * 32, v);
-      }
-      tmem_st_wait();
+      image_col_to_tmem<MG>(sW, cgp * RH + j, t_lane + A_COL0 + cgp * 64);
       tc_fence_before();
       named_bar_arrive(BAR_R, R_ALL);
     }
@@ -288,7 +311,8 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
-  constexpr uint32_t TM_COLS = NB < 32 ? 32 : NB;
+  // TMEM: [0, NB) the dh accumulator, [A_COL0, A_COL0 + 256) U (128 x 512 bf16) as the resident A operand
+  constexpr uint32_t A_COL0 = 64, TM_COLS = 512;
 
   if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
@@ -311,17 +335,18 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   if (warp == 16) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
     const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
-    constexpr uint32_t a_hi = umma_desc_hi(MG * 128), b_hi = umma_desc_hi(128);
-    const uint32_t a_lo0 = umma_desc_lo(w_base, 128), b_lo0 = umma_desc_lo(z_base, NB * 16);
+    constexpr uint32_t b_hi = umma_desc_hi(128);
+    const uint32_t b_lo0 = umma_desc_lo(z_base, NB * 16);
+    (void)w_base;
     const bool leader = elect_one();
-    mbar_wait(&bar_w, 0);
+    named_bar_sync(BAR_R, R_ALL);                            // the epilogue warps have copied U into TMEM
     for (int t = T - 1; t >= 1; --t) {
       named_bar_sync(BAR_H, R_ALL);                          // dz_t is in shared memory
       tc_fence_after();
       if (leader) {
 #pragma unroll
-        for (int ks = 0; ks < GH / 16; ++ks)
-          umma_bf16_lohi(tmem, a_lo0 + ((ks * 2 * 128) >> 4), a_hi, b_lo0 + ((ks * 2 * (NB * 16)) >> 4), b_hi, idesc, ks > 0);
+        for (int ks = 0; ks < GH / 16; ++ks)                 // A from TMEM: 8 columns (16 gate columns) per K step
+          umma_bf16_ts(tmem, tmem + A_COL0 + ks * 8, b_lo0 + ((ks * 2 * (NB * 16)) >> 4), b_hi, idesc, ks > 0);
         umma_commit(&bar_mma);
       }
       __syncwarp();
@@ -330,6 +355,11 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
     const int q = warp & 3, cgp = warp >> 2;
     const int j = q * 32 + lane;
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    // warp (q, cgp) copies gate block cgp (128 columns = 64 TMEM columns) of rows 32q..32q+31 into TMEM
+    mbar_wait(&bar_w, 0);
+    image_row_to_tmem<MG>(sW, j, cgp * 16, 2, t_lane + A_COL0 + cgp * 64);
+    tc_fence_before();
+    named_bar_arrive(BAR_R, R_ALL);
     float dc[CH8 * 8];
 #pragma unroll
     for (int i = 0; i < CH8 * 8; ++i) dc[i] = 0.f;
@@ -475,7 +505,9 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
   uint8_t* sZero = sX + (size_t)p.T * NB * 16;
   __shared__ uint64_t bar_w, bar_a, bar_b;
   __shared__ uint32_t tmem_s;
-  constexpr uint32_t TM_COLS = NB <= 32 ? 128 : 256;
+  // TMEM: [0, 3*NB) accumulators z | r | candidate, [A_COL0, A_COL0 + 192) the three gate tiles of Uᵀ (resident A)
+  constexpr uint32_t A_COL0 = 3 * NB, TM_COLS = 512;
+  constexpr uint32_t BAR_W = 3;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
@@ -503,8 +535,10 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
     constexpr uint32_t hi = umma_desc_hi(128);
     const uint32_t a_lo0 = umma_desc_lo(w_base, W_LBO), h_lo0 = umma_desc_lo(h_base, NB * 16),
                    r_lo0 = umma_desc_lo(r_base, NB * 16);
+    constexpr uint32_t idesc_ts = umma_idesc_bf16(128, NB, false, true);   // A from TMEM (K-major by construction)
     const bool leader = elect_one();
     mbar_wait(&bar_w, 0);
+    named_bar_sync(BAR_W, R_ALL);                            // the epilogue warps have copied Uᵀ into TMEM
     for (int t = 0; t < T; ++t) {
       if (t > 0) named_bar_sync(BAR_H, R_ALL);
       tc_fence_after();
@@ -516,8 +550,8 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
           if (t > 0 && g < 2) {
 #pragma unroll
             for (int ks = 0; ks < RH / 16; ++ks)
-              umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + ks * 2 * W_LBO) >> 4), hi,
-                             h_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi, idesc, ks > 0);
+              umma_bf16_ts(tmem + g * NB, tmem + A_COL0 + g * 64 + ks * 8, h_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi,
+                           idesc_ts, ks > 0);
           }
           umma_bf16_lohi(tmem + g * NB, a_lo0 + ((g * 16 * 128 + 16 * W_LBO) >> 4), hi, x_lo, hi, idesc, t > 0 && g < 2);
         }
@@ -530,8 +564,8 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
         if (leader) {
 #pragma unroll
           for (int ks = 0; ks < RH / 16; ++ks)
-            umma_bf16_lohi(tmem + 2 * NB, a_lo0 + ((2 * 16 * 128 + ks * 2 * W_LBO) >> 4), hi,
-                           r_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi, idesc, true);
+            umma_bf16_ts(tmem + 2 * NB, tmem + A_COL0 + 2 * 64 + ks * 8, r_lo0 + ((ks * 2 * (NB * 16)) >> 4), hi,
+                         idesc_ts, true);
           umma_commit(&bar_b);
         }
         __syncwarp();
@@ -541,6 +575,10 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
     const int q = warp & 3, cgp = warp >> 2;
     const int j = q * 32 + lane;
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    mbar_wait(&bar_w, 0);
+    if (cgp < 3) image_col_to_tmem<MG>(sW, cgp * RH + j, t_lane + A_COL0 + cgp * 64);
+    tc_fence_before();
+    named_bar_arrive(BAR_W, R_ALL);
     float hreg[CH8 * 8];
 #pragma unroll
     for (int i = 0; i < CH8 * 8; ++i) hreg[i] = 0.f;
@@ -667,7 +705,9 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   float* sX = reinterpret_cast<float*>(sB2 + RH * NB * 2);
   __shared__ uint64_t bar_w, bar_1, bar_2;
   __shared__ uint32_t tmem_s;
-  constexpr uint32_t TM_COLS = 2 * NB < 32 ? 32 : 2 * NB;
+  // TMEM: [0, 2*NB) accumulators D1 | D2, [A_COL0, A_COL0 + 192) U (128 x 384 bf16) as the resident A operand
+  constexpr uint32_t A_COL0 = 128, TM_COLS = 512;
+  constexpr uint32_t BAR_W = 3;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
@@ -693,12 +733,12 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   if (warp == 16) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
     const uint32_t w_base = smem_u32(sW), b1_base = smem_u32(sB1), b2_base = smem_u32(sB2);
-    constexpr uint32_t a_hi = umma_desc_hi(MG * 128), b_hi = umma_desc_hi(128);
-    const uint32_t a_lo0 = umma_desc_lo(w_base, 128), b1_lo0 = umma_desc_lo(b1_base, NB * 16),
-                   b2_lo0 = umma_desc_lo(b2_base, NB * 16);
-    constexpr uint32_t A_STEP = (2 * 128) >> 4, B_STEP = (2 * NB * 16) >> 4;       // per K = 16 step, in 16-byte units
+    constexpr uint32_t b_hi = umma_desc_hi(128);
+    const uint32_t b1_lo0 = umma_desc_lo(b1_base, NB * 16), b2_lo0 = umma_desc_lo(b2_base, NB * 16);
+    (void)w_base;
+    constexpr uint32_t B_STEP = (2 * NB * 16) >> 4;          // per K = 16 step, in 16-byte units
     const bool leader = elect_one();
-    mbar_wait(&bar_w, 0);
+    named_bar_sync(BAR_W, R_ALL);                            // the epilogue warps have copied U into TMEM
     for (int t = T - 1; t >= 1; --t) {
       named_bar_sync(BAR_H, R_ALL);                          // d(az), d(ah) staged
       tc_fence_after();
@@ -707,10 +747,10 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
         // D2 (cols NB..2NB) = U_z · d(az)ᵀ            (image columns 0..127   -> K chunk pairs 0..7)
 #pragma unroll
         for (int ks = 0; ks < RH / 16; ++ks)
-          umma_bf16_lohi(tmem, a_lo0 + (16 + ks) * A_STEP, a_hi, b1_lo0 + (8 + ks) * B_STEP, b_hi, idesc, ks > 0);
+          umma_bf16_ts(tmem, tmem + A_COL0 + 128 + ks * 8, b1_lo0 + (8 + ks) * B_STEP, b_hi, idesc, ks > 0);
 #pragma unroll
         for (int ks = 0; ks < RH / 16; ++ks)
-          umma_bf16_lohi(tmem + NB, a_lo0 + ks * A_STEP, a_hi, b1_lo0 + ks * B_STEP, b_hi, idesc, ks > 0);
+          umma_bf16_ts(tmem + NB, tmem + A_COL0 + ks * 8, b1_lo0 + ks * B_STEP, b_hi, idesc, ks > 0);
         umma_commit(&bar_1);
       }
       __syncwarp();
@@ -720,7 +760,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
         // D2 += U_r · d(ar)ᵀ                             (image columns 128..255 -> K chunk pairs 8..15)
 #pragma unroll
         for (int ks = 0; ks < RH / 16; ++ks)
-          umma_bf16_lohi(tmem + NB, a_lo0 + (8 + ks) * A_STEP, a_hi, b2_lo0 + ks * B_STEP, b_hi, idesc, true);
+          umma_bf16_ts(tmem + NB, tmem + A_COL0 + 64 + ks * 8, b2_lo0 + ks * B_STEP, b_hi, idesc, true);
         umma_commit(&bar_2);
       }
       __syncwarp();
@@ -729,6 +769,10 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
     const int q = warp & 3, cgp = warp >> 2;
     const int j = q * 32 + lane;
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
+    mbar_wait(&bar_w, 0);
+    if (cgp < 3) image_row_to_tmem<MG>(sW, j, cgp * 16, 2, t_lane + A_COL0 + cgp * 64);
+    tc_fence_before();
+    named_bar_arrive(BAR_W, R_ALL);
     float dh[CH8 * 8];
 #pragma unroll
     for (int i = 0; i < CH8 * 8; ++i) dh[i] = 0.f;
