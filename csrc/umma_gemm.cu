@@ -14,12 +14,11 @@
 // tcgen05 kernel in this library relies on.  The reference has no GEMM of its own (Keras→TF Eigen on
 // CPU).
 #include "common.cuh"
+#include "gemm_pipe.cuh"
 #include "../include/ddls_b200.h"
 
 namespace ddls {
 
-constexpr int GEMM_BM = 128;
-constexpr int GEMM_KC = 64;       // K elements per pipeline stage
 constexpr int GEMM_THREADS = 128;
 
 struct GemmParams {
@@ -244,113 +243,18 @@ __global__ void __launch_bounds__(256) splitk_finish_kernel(const float* __restr
 // loop is throughput- rather than latency-bound — and the epilogue transposes through shared memory so
 // global stores are coalesced along the output row.
 // =================================================================================================
-constexpr int V2_THREADS = 256;
-constexpr int V2_STAGES = 4;
-
-template <int ROWS>
-DDLS_DEVINL void cpasync_kmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int row0, int nrows, int k0, int kend) {
-  constexpr int KCH = GEMM_KC / 8;
-  static_assert((ROWS * KCH) % V2_THREADS == 0, "tile must divide evenly over the CTA");
-#pragma unroll
-  for (int it = 0; it < ROWS * KCH / V2_THREADS; ++it) {
-    const int idx = threadIdx.x + it * V2_THREADS;
-    const int blk = idx >> 5, lane = idx & 31;
-    const int rblk = blk % (ROWS / 8), kblk = blk / (ROWS / 8);
-    const int r = rblk * 8 + (lane & 7), kc = kblk * 4 + (lane >> 3);
-    const int gr = row0 + r, gk = k0 + kc * 8;
-    const bool ok = gr < nrows && gk < kend;
-    const int valid = ok ? min(8, kend - gk) : 0;
-    cp_async16(smem + kc * (ROWS * 16) + r * 16, ok ? (const void*)(g + (size_t)gr * ld + gk) : (const void*)g, valid * 2);
-  }
-}
-template <int COLS>
-DDLS_DEVINL void cpasync_mnmajor(uint8_t* smem, const __nv_bfloat16* g, int ld, int col0, int ncols, int k0, int kend) {
-  constexpr int MNG = COLS / 8;
-  static_assert((GEMM_KC * MNG) % V2_THREADS == 0, "tile must divide evenly over the CTA");
-#pragma unroll
-  for (int it = 0; it < GEMM_KC * MNG / V2_THREADS; ++it) {
-    const int idx = threadIdx.x + it * V2_THREADS;
-    const int blk = idx >> 5, lane = idx & 31;
-    const int gblk = blk % (MNG / 4), kblk = blk / (MNG / 4);
-    const int mng = gblk * 4 + (lane >> 3), k = kblk * 8 + (lane & 7);
-    const int gk = k0 + k, gc = col0 + mng * 8;
-    const bool ok = gk < kend && gc < ncols;
-    const int valid = ok ? min(8, ncols - gc) : 0;
-    cp_async16(smem + (k >> 3) * (COLS * 16) + mng * 128 + (k & 7) * 16, ok ? (const void*)(g + (size_t)gk * ld + gc) : (const void*)g,
-               valid * 2);
-  }
-}
-
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(V2_THREADS, 1) umma_gemm_v2_kernel(GemmParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
-  constexpr int A_BYTES = GEMM_BM * GEMM_KC * 2, B_BYTES = BN * GEMM_KC * 2, STAGE = A_BYTES + B_BYTES;
   __shared__ uint64_t mma_done[V2_STAGES];
   __shared__ uint32_t tmem_base_s;
-  constexpr uint32_t TM_COLS = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
+  constexpr uint32_t TM_COLS = gemm_pipe_tmem_cols<BN>();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * GEMM_BM, n0 = blockIdx.y * BN;
   const int kbeg = blockIdx.z * p.k_per_split, kend = min(p.K, kbeg + p.k_per_split);
-  const __nv_bfloat16* A = static_cast<const __nv_bfloat16*>(p.A);
-  const __nv_bfloat16* B = static_cast<const __nv_bfloat16*>(p.B);
-
-  if (warp == 0) tmem_alloc(&tmem_base_s, TM_COLS);
-  if (threadIdx.x == 32) {
-    for (int s = 0; s < V2_STAGES; ++s) mbar_init(&mma_done[s], 1);
-    mbar_fence_init();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_d = tmem_base_s;
-  constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
-  const int nkb = (kend - kbeg + GEMM_KC - 1) / GEMM_KC;
-
-  auto issue_loads = [&](int kb) {
-    uint8_t* sa = smem + (kb % V2_STAGES) * STAGE;
-    uint8_t* sb = sa + A_BYTES;
-    const int k0 = kbeg + kb * GEMM_KC;
-    if (A_MN) cpasync_mnmajor<GEMM_BM>(sa, A, p.lda, m0, p.M, k0, kend);
-    else      cpasync_kmajor<GEMM_BM>(sa, A, p.lda, m0, p.M, k0, kend);
-    if (B_MN) cpasync_mnmajor<BN>(sb, B, p.ldb, n0, p.N, k0, kend);
-    else      cpasync_kmajor<BN>(sb, B, p.ldb, n0, p.N, k0, kend);
-  };
-  // prologue: fill STAGES-1 slots (always commit so group accounting stays uniform)
-  for (int kb = 0; kb < V2_STAGES - 1; ++kb) {
-    if (kb < nkb) issue_loads(kb);
-    cp_async_commit();
-  }
-  uint32_t waits[V2_STAGES] = {};
-  for (int kb = 0; kb < nkb; ++kb) {
-    const int s = kb % V2_STAGES;
-    // refill the slot that k-block kb-1 used, once its MMAs have drained
-    const int nxt = kb + V2_STAGES - 1;
-    if (nxt < nkb) {
-      const int ns = nxt % V2_STAGES;
-      if (kb >= 1) { mbar_wait(&mma_done[ns], waits[ns] & 1); ++waits[ns]; }
-      issue_loads(nxt);
-    }
-    cp_async_commit();
-    cp_async_wait<V2_STAGES - 1>();       // k-block kb has landed (for this thread)
-    fence_proxy_async_smem();
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      tc_fence_after();
-      const uint32_t a_base = smem_u32(smem + s * STAGE), b_base = a_base + A_BYTES;
-#pragma unroll
-      for (int ks = 0; ks < GEMM_KC / 16; ++ks)
-        umma_bf16(tmem_d, umma_desc(a_base + ks * 2 * (GEMM_BM * 16u), GEMM_BM * 16u, 128u),
-                  umma_desc(b_base + ks * 2 * (BN * 16u), BN * 16u, 128u), idesc, (kb | ks) != 0);
-      umma_commit(&mma_done[s]);
-    }
-  }
-  cp_async_wait<0>();
-  for (int s = 0; s < V2_STAGES; ++s) {
-    const uint32_t commits = nkb > s ? (nkb - s + V2_STAGES - 1) / V2_STAGES : 0;
-    while (waits[s] < commits) { mbar_wait(&mma_done[s], waits[s] & 1); ++waits[s]; }
-  }
-  tc_fence_after();
-  __syncthreads();    // every pipeline slot is idle: reuse it as the epilogue transpose buffer
+  const uint32_t tmem_d = gemm_pipe_run<BN, A_MN, B_MN>(smem, mma_done, &tmem_base_s, static_cast<const __nv_bfloat16*>(p.A),
+                                                         p.lda, p.M, m0, static_cast<const __nv_bfloat16*>(p.B), p.ldb, p.N,
+                                                         n0, kbeg, kend);
 
   // ---- epilogue: TMEM -> registers -> smem [128 rows][BN+1] fp32 chunks of 32 columns -> coalesced rows
   const bool relu = p.flags & DDLS_GEMM_RELU, has_bias = (p.flags & DDLS_GEMM_BIAS);

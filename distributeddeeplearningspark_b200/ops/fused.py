@@ -25,6 +25,11 @@ def _plan(model):
             and ls[1].activation == 'relu' and ls[3].activation == 'relu' and ls[7].activation == 'relu' \
             and ls[9].activation == 'softmax' and ls[8].units <= 32:
         plan = {'kind': 'cnn', 'conv1': ls[0], 'conv2': ls[2], 'dense1': ls[6], 'dense2': ls[8]}
+    elif len(ls) >= 2 and kinds[-1] == 'Dense' and all(k == 'LSTM' for k in kinds[:-1]) \
+            and ls[-1].activation in (None, 'linear') and ls[-1].units <= 4 and model.input_shape[-1] == 1 \
+            and all(l.units % 128 == 0 for l in ls[:-1]) and all(l.return_sequences for l in ls[:-2]) \
+            and not ls[-2].return_sequences and (len(ls) > 2 or ls[0].units > 128):
+        plan = {'kind': 'stacked_lstm', 'lstms': ls[:-1], 'dense': ls[-1]}
     model._fused_plan = plan
     return plan
 
@@ -44,6 +49,20 @@ def try_forward(model, x: torch.Tensor) -> Optional[torch.Tensor]:
         if h.is_cuda and not torch.is_grad_enabled():
             return heads.dense_linear(h, plan['dense'].kernel, plan['dense'].bias)
         return plan['dense'](h)
+    if plan['kind'] == 'stacked_lstm' and not torch.is_grad_enabled():
+        from .. import _native as N
+        from . import heads, lstm_big
+        if lstm_big.supported(plan['lstms'], x):
+            B, T, _ = x.shape
+            key = ('stacked_infer', B, T)
+            cache = model.__dict__.setdefault('_fused_cache', {})
+            bufs = cache.get(key)
+            if bufs is None:
+                bufs = cache[key] = lstm_big.StackedLSTMBuffers(plan['lstms'], B, T, x.device)
+            st = N.stream_ptr(x.device)
+            lstm_big.prepare_weights(plan['lstms'], bufs, st)
+            h = lstm_big.forward(plan['lstms'], bufs, x.reshape(B, T).contiguous(), st, save=False)
+            return heads.dense_linear(h, plan['dense'].kernel, plan['dense'].bias)
     if plan['kind'] == 'cnn' and not torch.is_grad_enabled():
         from . import heads
         a = _cnn_trunk(plan, x)
@@ -96,6 +115,9 @@ class DirectStep:
             self.flat.attach_grads()
         self._bufs = {}
         self.dev = self.flat.device
+        # called with each parameter as soon as its gradient is final, so a DistributedOptimizer can launch the
+        # bucket's allreduce on its side stream while the rest of the backward kernels are still running
+        self.grad_ready = getattr(optimizer, '_on_grad', None) if hasattr(optimizer, 'buckets') else None
         if self.kind == 'cnn':
             d1 = self.plan['dense1']
             self.ld1 = (d1.kernel.shape[1] + 7) // 8 * 8
@@ -114,7 +136,15 @@ class DirectStep:
         if plan['kind'] == 'cnn' and loss_name == 'categorical_crossentropy':
             from . import cnn
             return cnn.native_available(plan, x) and plan['dense1'].kernel.shape[1] <= 256 and x.shape[0] <= 1024
+        if plan['kind'] == 'stacked_lstm' and loss_name in ('mean_squared_error', 'mse'):
+            from . import lstm_big
+            return lstm_big.supported(plan['lstms'], x)
         return False
+
+    def _ready(self, *params):
+        if self.grad_ready is not None:
+            for p in params:
+                self.grad_ready(p)
 
     def _buf(self, name, shape, dtype):
         key = (name, tuple(shape), dtype)
@@ -125,7 +155,38 @@ class DirectStep:
         return t
 
     def run(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        return self._run_cnn(x, y) if self.kind == 'cnn' else self._run_rnn(x, y)
+        if self.kind == 'cnn':
+            return self._run_cnn(x, y)
+        if self.kind == 'stacked_lstm':
+            return self._run_stacked(x, y)
+        return self._run_rnn(x, y)
+
+    # ------------------------------------------------------------------ stacked large-hidden LSTM
+    def _run_stacked(self, x, y):
+        from .. import _native as N
+        from . import heads, lstm_big
+        lstms, dense = self.plan['lstms'], self.plan['dense']
+        B, T, _ = x.shape
+        st = N.stream_ptr(self.dev)
+        key = ('stacked', B, T)
+        bufs = self._bufs.get(key)
+        if bufs is None:
+            bufs = self._bufs[key] = lstm_big.StackedLSTMBuffers(lstms, B, T, self.dev)
+        x2 = x.reshape(B, T).contiguous()
+        O = dense.kernel.shape[1]
+        Hl = lstms[-1].units
+        pred = self._buf('pred', (B, O), torch.float32)
+        loss = self._buf('loss', (1,), torch.float32)
+        dh = self._buf('dh', (B, Hl), torch.float32)
+        lstm_big.prepare_weights(lstms, bufs, st)
+        h = lstm_big.forward(lstms, bufs, x2, st, save=True)
+        heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh, dense.kernel.grad,
+                            dense.bias.grad)
+        self._ready(dense.bias, dense.kernel)
+        lstm_big.backward(lstms, bufs, x2, dh, st)
+        for l in reversed(lstms):
+            self._ready(l.bias, l.recurrent_kernel, l.kernel)
+        return loss
 
     # ------------------------------------------------------------------ CNN
     def _run_cnn(self, x, y):
@@ -160,7 +221,9 @@ class DirectStep:
             scr = self._bufs[('head_scratch', B)] = heads.softmax_xent_scratch(B, self.dev)
         heads.softmax_xent_raw(a3, d2.kernel, d2.bias, y.contiguous(), None, loss, None, dz3, ld, d2.kernel.grad,
                                d2.bias.grad, d1.bias.grad, True, scr)
+        self._ready(d2.bias, d2.kernel, d1.bias)
         gemm_bf16(flat, dz3[:, :F], a_mn_major=True, b_mn_major=True, out=d1.kernel.grad)
+        self._ready(d1.kernel)                    # 99 % of the gradient bytes: its allreduce overlaps the conv backward
         gemm_bf16(dz3[:, :F], w1s, out=dflat)
         N.call('ddls_cnn_unpool_bwd', dflat.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), dz2.data_ptr(),
                c2.bias.grad.data_ptr(), B, st)
@@ -175,6 +238,7 @@ class DirectStep:
             g1 = self._buf('g1', (320,), f32)
             N.call('ddls_cnn_conv1_wgrad', x.data_ptr(), dz1.data_ptr(), g1.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
             g1k.view(-1).copy_(g1[:288]); g1b.copy_(g1[288:])
+        self._ready(c2.bias, c2.kernel, c1.bias, c1.kernel)
         return loss
 
     # ------------------------------------------------------------------ LSTM / GRU regressor
@@ -212,6 +276,7 @@ class DirectStep:
             heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh,
                                 dense.kernel.grad, dense.bias.grad)
             R.lstm_v2_backward(dh, x2, img, gates2, cs2, dz2, k.grad, b.grad, r.grad, B, T, False, hs2)
+            self._ready(dense.bias, dense.kernel, b, r, k)
             return loss
         if (not is_lstm) and R.use_v2():
             key = ('gru_v2', B, T)
@@ -225,6 +290,7 @@ class DirectStep:
             heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh,
                                 dense.kernel.grad, dense.bias.grad)
             R.gru_v2_backward(dh, x2, img, zrh2, hprev2, da2, k.grad, b.grad, r.grad, B, T, False, hs2, rh2)
+            self._ready(dense.bias, dense.kernel, b, r, k)
             return loss
         if is_lstm:
             gates = self._buf('gates', (T, B, H, 4), bf)

@@ -88,7 +88,7 @@ class DistributedOptimizer:
             self.flat = _GradOnlyFlat(params, self.comm)
             self._generic = True
         self.device = self.flat.device
-        bucket_bytes = bucket_bytes or env_int('DDLS_BUCKET_BYTES', 32 << 20)
+        bucket_bytes = bucket_bytes or env_int('DDLS_BUCKET_BYTES', 2 << 20)
         self.buckets = [_Bucket(lo, hi, idxs) for lo, hi, idxs in
                         plan_buckets(self.flat.segments(), max(1, bucket_bytes // 4))]
         self._bucket_of: Dict[int, _Bucket] = {}
@@ -109,9 +109,11 @@ class DistributedOptimizer:
 
     # ------------------------------------------------------------------ hooks
     def _on_grad(self, p: torch.Tensor) -> None:
-        if self._passes + 1 < self.backward_passes_per_step:
-            return  # keep accumulating locally
-        b = self._bucket_of[id(p)]
+        if self.size == 1 or self._passes + 1 < self.backward_passes_per_step:
+            return  # nothing to reduce / keep accumulating locally
+        b = self._bucket_of.get(id(p))
+        if b is None or b.launched:
+            return
         b.pending -= 1
         if b.pending == 0:
             self._launch(b)

@@ -102,6 +102,22 @@ int ddls_gru128_backward_v2(const float* dout, const float* x, const void* image
 int ddls_rnn128_wgrad(const void* a_img, const void* b_img, float* C, int kgroups, int n, int b_ntotal, int b_noff,
                       int ldc, void* stream);
 
+/* ---- large-hidden LSTM (csrc/lstm_big.cu; BASELINE.json config 4: hidden 1024, seq 168) ------------------
+ * 4H-wide tensors use the permuted column order n = (unit/32)*128 + gate*32 + unit%32.  H % 128 == 0. */
+int ddls_lstm_big_perm_cast(const float* src, void* dst_bf16, int rows, int H, void* stream);   /* [rows,4H] Keras -> perm bf16 */
+int ddls_lstm_big_perm_vec(const float* src, float* dst, int H, void* stream);                 /* [4H] Keras -> perm */
+int ddls_lstm_big_unperm(const float* src, float* dst, int rows, int H, int accumulate, void* stream);
+/* out[keras col] += sum_r w[r]*X[r][perm col] (w NULL: column sums); X bf16 [R,4H]; caller zeroes out. */
+int ddls_lstm_big_colsum(const void* X, const float* w, float* out, int R, int H, void* stream);
+/* One time step: gates from h_prev·U (+ zx or x*w_ih) + bias; writes c_next, h_next (bf16), gates (bf16, perm). */
+int ddls_lstm_big_step_fwd(const void* h_prev, const void* u_perm, const void* zx, const float* x, int x_stride,
+                           const float* wih_perm, const float* bias_perm, const float* c_prev, float* c_next,
+                           void* h_next, float* h_out_f32, void* gates, int B, int H, void* stream);
+/* One BPTT step: dh = dz_next·U^T (+dout); writes dz (bf16, perm) for this step, updates dc in place. */
+int ddls_lstm_big_step_bwd(const void* dz_next, const void* u_perm, const void* dout_bf16, const float* dout_f32,
+                           const void* gates, const float* c_t, const float* c_prev, float* dc, void* dz, int B, int H,
+                           int use_acc, int first, void* stream);
+
 /* ---- persistent GRU(128) recurrence, tcgen05 (Keras GRU reset_after=False, ddl_nyiso_aztk.py:201-203) ----
  * Gate order z,r,h.  When save_for_backward: hs [T,B,H] bf16 (h_t), rh [T,B,H] bf16 (r_t*h_{t-1}),
  * gates [T,B,H] float4 (z, r, hh, h_{t-1}). */

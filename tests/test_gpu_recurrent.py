@@ -125,3 +125,34 @@ def test_step_engine_trains_nyiso_models_with_cuda_graph(make):
             x[:32], model.layers[0].kernel, model.layers[0].recurrent_kernel, model.layers[0].bias)
         ref = h @ model.layers[1].kernel + model.layers[1].bias
     assert float((pred - ref).abs().max()) < 2e-2
+
+
+def test_stacked_big_lstm_direct_step_matches_autograd_reference():
+    """Large-hidden stacked LSTM (per-step fused GEMM kernels) vs torch autograd on the Keras equations."""
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.ops.fused import DirectStep
+    from distributeddeeplearningspark_b200.trainers import mean_squared_error
+    dev = torch.device('cuda', 0)
+    torch.manual_seed(0)
+    B, T = 96, 7
+    m = ddls.models.stacked_lstm(units=256, len_seq=T, num_layers=2, seed=5).to(dev)
+    x = torch.rand(B, T, 1, device=dev); y = torch.rand(B, 1, device=dev)
+    h = x
+    for l in m.layers[:-1]:
+        h = L.lstm_reference(h, l.kernel, l.recurrent_kernel, l.bias, l.return_sequences)
+    ref = mean_squared_error(h @ m.layers[-1].kernel + m.layers[-1].bias, y)
+    ref.backward()
+    gref = [p.grad.clone() for p in m.parameters()]
+    opt = ddls.optim.KerasAdam(m.parameters())
+    assert DirectStep.supported(m, opt, 'mean_squared_error', x)
+    ds = DirectStep(m, opt, 'mean_squared_error')
+    assert ds.kind == 'stacked_lstm'
+    loss = ds.run(x, y)
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(ref)) < 2e-2 * max(abs(float(ref)), 1e-3), (float(loss), float(ref))
+    for (n, p), g in zip(m.named_parameters(), gref):
+        l2 = float((p.grad - g).norm() / (g.norm() + 1e-12))
+        assert l2 < 5e-2, (n, l2)
+    with torch.no_grad():
+        pred = m(x)
+    assert float((pred - (h @ m.layers[-1].kernel + m.layers[-1].bias)).abs().max()) < 2e-2
