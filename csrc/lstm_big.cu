@@ -172,11 +172,13 @@ struct BigBwd {
   int first;                     // 1 at t = T-1: dc starts from zero
 };
 
+// Tile = 128 batch rows x 32 hidden units: K = 4H is long, so narrow column tiles (4H/32... H/32 of them) keep
+// all SMs busy (4 x 32 = 128 CTAs at B = 512, H = 1024) instead of 32 fat ones.
 __global__ void __launch_bounds__(V2_THREADS, 1) lstm_big_bwd_kernel(BigBwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t mma_done[V2_STAGES];
   __shared__ uint32_t tmem_slot;
-  constexpr int BN = 128;
+  constexpr int BN = 32;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = blockIdx.x * GEMM_BM, n0 = blockIdx.y * BN;      // n0: first hidden unit of this tile
   const int G = 4 * p.H;
@@ -184,37 +186,36 @@ __global__ void __launch_bounds__(V2_THREADS, 1) lstm_big_bwd_kernel(BigBwd p) {
                                                          0, p.use_acc ? G : 0);
   float* sT = reinterpret_cast<float*>(smem);                      // [128][33]
   const int q4 = warp & 3, half = warp >> 2;
-  for (int c0 = 0; c0 < BN; c0 += 32) {
+  {
     uint32_t v[16];
-    tmem_ld16(tmem + (static_cast<uint32_t>(q4 * 32) << 16) + c0 + half * 16, v);
+    tmem_ld16(tmem + (static_cast<uint32_t>(q4 * 32) << 16) + half * 16, v);
     tmem_ld_wait();
     const int r = q4 * 32 + lane;
 #pragma unroll
     for (int j = 0; j < 16; ++j) sT[r * 33 + half * 16 + j] = p.use_acc ? __uint_as_float(v[j]) : 0.f;
-    __syncthreads();
-    const int unit = n0 + c0 + lane;
-    const int pc = (unit >> 5) * 128 + (unit & 31);                // permuted column of gate 0 of this unit
-    for (int rr = warp * 16; rr < warp * 16 + 16; ++rr) {
-      const int b = m0 + rr;
-      if (b >= p.B) break;
-      const size_t o = (size_t)b * p.H + unit;
-      float dh = sT[rr * 33 + lane];
-      if (p.dout_bf16 != nullptr) dh += __bfloat162float(p.dout_bf16[o]);
-      if (p.dout_f32 != nullptr) dh += p.dout_f32[o];
-      const __nv_bfloat16* gs = p.gates + (size_t)b * G + pc;
-      const float gi = __bfloat162float(gs[0]), gf = __bfloat162float(gs[32]);
-      const float gg = __bfloat162float(gs[64]), go = __bfloat162float(gs[96]);
-      const float tc = fast_tanh(p.c_t[o]);
-      const float dcv = fmaf(dh * go, 1.f - tc * tc, p.first ? 0.f : p.dc[o]);
-      const float zo = dh * tc * ((go > 0.f && go < 1.f) ? 0.2f : 0.f);
-      const float zi = dcv * gg * ((gi > 0.f && gi < 1.f) ? 0.2f : 0.f);
-      const float zf = dcv * p.c_prev[o] * ((gf > 0.f && gf < 1.f) ? 0.2f : 0.f);
-      const float zg = dcv * gi * (1.f - gg * gg);
-      p.dc[o] = dcv * gf;
-      __nv_bfloat16* zd = p.dz + (size_t)b * G + pc;
-      zd[0] = __float2bfloat16(zi); zd[32] = __float2bfloat16(zf); zd[64] = __float2bfloat16(zg); zd[96] = __float2bfloat16(zo);
-    }
-    __syncthreads();
+  }
+  __syncthreads();
+  const int unit = n0 + lane;
+  const int pc = (unit >> 5) * 128 + (unit & 31);                  // permuted column of gate 0 of this unit
+  for (int rr = warp * 16; rr < warp * 16 + 16; ++rr) {
+    const int b = m0 + rr;
+    if (b >= p.B) break;
+    const size_t o = (size_t)b * p.H + unit;
+    float dh = sT[rr * 33 + lane];
+    if (p.dout_bf16 != nullptr) dh += __bfloat162float(p.dout_bf16[o]);
+    if (p.dout_f32 != nullptr) dh += p.dout_f32[o];
+    const __nv_bfloat16* gs = p.gates + (size_t)b * G + pc;
+    const float gi = __bfloat162float(gs[0]), gf = __bfloat162float(gs[32]);
+    const float gg = __bfloat162float(gs[64]), go = __bfloat162float(gs[96]);
+    const float tc = fast_tanh(p.c_t[o]);
+    const float dcv = fmaf(dh * go, 1.f - tc * tc, p.first ? 0.f : p.dc[o]);
+    const float zo = dh * tc * ((go > 0.f && go < 1.f) ? 0.2f : 0.f);
+    const float zi = dcv * gg * ((gi > 0.f && gi < 1.f) ? 0.2f : 0.f);
+    const float zf = dcv * p.c_prev[o] * ((gf > 0.f && gf < 1.f) ? 0.2f : 0.f);
+    const float zg = dcv * gi * (1.f - gg * gg);
+    p.dc[o] = dcv * gf;
+    __nv_bfloat16* zd = p.dz + (size_t)b * G + pc;
+    zd[0] = __float2bfloat16(zi); zd[32] = __float2bfloat16(zf); zd[64] = __float2bfloat16(zg); zd[96] = __float2bfloat16(zo);
   }
   tc_fence_before();
   __syncthreads();
@@ -287,9 +288,9 @@ extern "C" int ddls_lstm_big_step_bwd(const void* dz_next, const void* u_perm, c
   BigBwd p{static_cast<const __nv_bfloat16*>(dz_next), static_cast<const __nv_bfloat16*>(u_perm),
            static_cast<const __nv_bfloat16*>(dout_bf16), dout_f32, static_cast<const __nv_bfloat16*>(gates), c_t, c_prev,
            dc, static_cast<__nv_bfloat16*>(dz), B, H, use_acc, first};
-  const int smem = gemm_pipe_smem_bytes<128>();
+  const int smem = gemm_pipe_smem_bytes<32>();
   DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_big_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  dim3 grid((B + 127) / 128, H / 128);
+  dim3 grid((B + 127) / 128, H / 32);
   lstm_big_bwd_kernel<<<grid, V2_THREADS, smem, ST(stream)>>>(p);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_big_bwd_kernel launch");

@@ -310,7 +310,7 @@ template <bool A_MN, bool B_MN>
 static int dispatch_bn_v2(const GemmParams& p, int splits, cudaStream_t st) {
   if (p.N <= 32) return launch_gemm_v2<32, A_MN, B_MN>(p, splits, st);
   if (p.N <= 64) return launch_gemm_v2<64, A_MN, B_MN>(p, splits, st);
-  if (p.N <= 128 || p.N >= 1024) return launch_gemm_v2<128, A_MN, B_MN>(p, splits, st);   // wide N: more CTAs
+  if (p.N <= 128 || (p.N >= 1024 && p.M < 4096)) return launch_gemm_v2<128, A_MN, B_MN>(p, splits, st);   // wide N, few rows: more CTAs
   return launch_gemm_v2<256, A_MN, B_MN>(p, splits, st);
 }
 

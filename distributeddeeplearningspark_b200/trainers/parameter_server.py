@@ -64,6 +64,56 @@ class CollectiveCenter:
         return int(round(float(t.item())))
 
 
+class MulticastCenter:
+    """Asynchronous center variable in NVSwitch multicast memory (K19): a commit is ONE kernel that computes
+    ``scale * (W - W_pulled)`` and adds it to every replica with ``multimem.red`` (the switch applies it everywhere),
+    then pulls the local replica; ranks never wait for each other, like the original dist-keras server.  Without a
+    multicast mapping the same kernel falls back to peer atomics.  ``num_updates`` is a replicated commit counter,
+    which is also what DynSGD's staleness term reads."""
+
+    def __init__(self, comm, flat_params: torch.Tensor, staleness_aware: bool = False):
+        import ctypes
+        from .. import _native as N
+        self._N, self._ctypes = N, ctypes
+        self.comm = comm
+        self.staleness_aware = staleness_aware
+        n = flat_params.numel()
+        self.n = n
+        self.center = comm.alloc(n, torch.float32)
+        self.updates = comm.alloc(4, torch.int32)
+        self.center_off = comm.offset_of(self.center)
+        self.updates_off = comm.offset_of(self.updates)
+        self.pulled = flat_params.detach().clone()
+        self.last_update = torch.zeros(1, dtype=torch.int32, device=flat_params.device)
+        self.center.copy_(flat_params)          # every rank holds identical parameters after the initial broadcast
+        torch.cuda.synchronize(flat_params.device)
+        comm.barrier()
+        torch.cuda.synchronize(flat_params.device)
+        self.local_commits = 0
+        self.rounds = 0
+
+    def commit_pull(self, flat_params: torch.Tensor, scale: float, active: bool = True) -> None:
+        if not active:
+            return
+        N = self._N
+        N.call('ddls_comm_adag_commit', self._ctypes.byref(self.comm.desc), flat_params.data_ptr(), self.pulled.data_ptr(),
+               self.center_off, self.updates_off, self.n, scale, int(self.staleness_aware), self.last_update.data_ptr(),
+               torch.cuda.current_stream(flat_params.device).cuda_stream)
+        torch.autograd.graph.increment_version(flat_params)
+        self.local_commits += 1
+        self.rounds += 1
+
+    def finalize(self) -> None:
+        """Wait until every rank's last commit has landed (call once, after the training loop)."""
+        dev = self.center.device
+        torch.cuda.synchronize(dev)
+        self.comm.barrier()
+        torch.cuda.synchronize(dev)
+
+    def total_updates(self) -> int:
+        return int(self.updates[0].item())
+
+
 class ParameterServerView:
     """What ``trainer.parameter_server`` exposes after training."""
 

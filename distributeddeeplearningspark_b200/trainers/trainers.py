@@ -30,7 +30,7 @@ from ..data.frame import DataFrame
 from ..models.sequential import Sequential, deserialize_model, serialize_model
 from ..utils.logging import get_logger
 from .engine import StepEngine
-from .parameter_server import CollectiveCenter, ParameterServerView
+from .parameter_server import CollectiveCenter, MulticastCenter, ParameterServerView
 
 
 # ----------------------------------------------------------------------------
@@ -81,8 +81,13 @@ def _worker(spec: Dict) -> Dict:
                           seed=spec.get('seed') or 0, carry_over=True)
     window = int(spec.get('communication_window', 1))
     center = None
-    if mode in ('adag', 'dynsgd') :
-        center = CollectiveCenter(comm, flat.flat_params, staleness_aware=(mode == 'dynsgd'))
+    async_center = False
+    if mode in ('adag', 'dynsgd'):
+        # GPUs with a peer-memory communicator: asynchronous center in multicast memory (DDLS_ADAG=sync forces
+        # the lock-step collective emulation, which is also what CPU/gloo and single-rank runs use)
+        async_center = (type(comm).__name__ == 'PeerMemoryComm' and os.environ.get('DDLS_ADAG', 'async') != 'sync')
+        cls = MulticastCenter if async_center else CollectiveCenter
+        center = cls(comm, flat.flat_params, staleness_aware=(mode == 'dynsgd'))
     n_batches = len(feeder)
     if mode in ('adag', 'dynsgd'):
         my_rounds = n_batches // window
@@ -104,8 +109,11 @@ def _worker(spec: Dict) -> Dict:
         if center is not None and it % window == 0:
             center.commit_pull(flat.flat_params, 1.0 / window if mode == 'adag' else 1.0, active=True)
     if center is not None:
-        for _ in range(max_rounds - my_rounds):  # keep peers' collectives matched
-            center.commit_pull(flat.flat_params, 0.0, active=False)
+        if async_center:
+            center.finalize()
+        else:
+            for _ in range(max_rounds - my_rounds):  # keep peers' collectives matched
+                center.commit_pull(flat.flat_params, 0.0, active=False)
         flat.flat_params.copy_(center.center)
         num_updates = center.total_updates()
     else:

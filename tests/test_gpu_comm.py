@@ -126,6 +126,17 @@ def _multi_rank_checks():
         assert float(y.max()) == float(root) == float(y.min())
     g = ddls.allgather(torch.tensor([[float(r), 2.0 * r]], device=dev))
     assert g.tolist() == [[float(i), 2.0 * i] for i in range(n)]
+    # asynchronous ADAG center in multicast memory: center = init + sum over ranks/commits of scale*(W - pulled)
+    from distributeddeeplearningspark_b200.trainers import MulticastCenter
+    wflat = torch.full((4096,), 1.0, device=dev)
+    center = MulticastCenter(comm, wflat, staleness_aware=False)
+    for k in range(3):
+        wflat += float(r + 1)                       # "local training" moved the weights by (r+1)
+        center.commit_pull(wflat, 0.5)              # commit 0.5*(r+1) to every replica, then pull
+    center.finalize()
+    expect = 1.0 + 3 * 0.5 * sum(range(1, n + 1))
+    assert abs(float(center.center.min()) - expect) < 1e-4 and abs(float(center.center.max()) - expect) < 1e-4
+    assert center.total_updates() == 3 * n
     # synchronous training: identical weights on every rank after a few steps
     model = ddls.models.nyiso_lstm(seed=r).to(dev)
     opt = ddls.optim.KerasAdam(model.parameters(), comm=comm)
