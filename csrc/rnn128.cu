@@ -71,8 +71,16 @@ DDLS_DEVINL void build_x_image(uint8_t* sX, uint8_t* sZero, const float* __restr
 // column group warp >> 2), warp 16 only issues MMAs.  Per step the epilogue (a) reads its accumulators, does the
 // gate math and writes the next N-side operand to shared memory, (b) ARRIVES on a named barrier the MMA warp is
 // waiting on, and only then (c) writes the backward stash to global memory — so (c) overlaps the next MMAs.
-constexpr int R_EPI = 512;          // epilogue threads
-constexpr int R_ALL = R_EPI + 32;   // + MMA warp
+// Batch tile NB -> column groups: NB >= 32 uses 4 (16 epilogue warps), NB = 16 uses 2 (8 epilogue warps).  A batch of
+// 32 therefore runs as two 16-row CTAs on two SMs: half the epilogue work and half the stash traffic per SM.
+template <int NB>
+struct RCfg {
+  static constexpr int NCG = NB >= 32 ? 4 : 2;       // column groups
+  static constexpr int EPI = NCG * 4 * 32;           // epilogue threads
+  static constexpr int ALL = EPI + 32;               // + MMA warp
+  static constexpr int MMA_WARP = NCG * 4;
+  static constexpr int CH8 = NB / (8 * NCG);         // 8-column chunks per epilogue thread
+};
 constexpr uint32_t BAR_H = 1, BAR_R = 2;
 
 DDLS_DEVINL uint4 pack8(const float (&v)[8]) {
@@ -134,12 +142,12 @@ struct LstmV2Fwd {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
+__global__ void __launch_bounds__(RCfg<NB>::ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int GH = 4 * RH, MG = GH / 8;
   constexpr uint32_t W_LBO = MG * 128;                       // 8192: k-group stride of the image
   constexpr int W_BYTES = R_KG * MG * 128;                   // 147,456
-  constexpr int CH8 = NB / 32;                               // 8-column chunks per epilogue thread
+  constexpr int CH8 = RCfg<NB>::CH8, R_ALL = RCfg<NB>::ALL, R_EPI = RCfg<NB>::EPI, NCG = RCfg<NB>::NCG;
   uint8_t* sW = smem;
   uint8_t* sH = sW + W_BYTES;                                // [16][NB/8][8][8] bf16
   uint8_t* sX = sH + RH * NB * 2;                            // [T][NB*16 B]
@@ -153,7 +161,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   // TMEM: [0, 4*NB) accumulators, [A_COL0, A_COL0 + 256) the four gate tiles of Uᵀ as the resident A operand
   constexpr uint32_t A_COL0 = 4 * NB;
   constexpr uint32_t TM_COLS = (4 * NB + 256) <= 256 ? 256 : 512;
-  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
   if (tid == R_EPI) {                                        // bulk TMA copies bring the whole weight image
@@ -169,7 +177,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   tc_fence_after();
   const uint32_t tmem = tmem_s;
 
-  if (warp == 16) {
+  if (warp == RCfg<NB>::MMA_WARP) {
     // ================= MMA warp: the whole warp runs the (warp-uniform) loop, one elected lane issues =================
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);      // x step: A from the smem image (MN-major)
     constexpr uint32_t idesc_ts = umma_idesc_bf16(128, NB, false, true);  // h steps: A from TMEM is K-major by construction
@@ -211,7 +219,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
       // Make the recurrent weights TMEM-resident: warp (q, g = cgp) copies gate tile g, rows 32q..32q+31.
       // Row m = j of tile g is Uᵀ[g*128 + j][k], k = 0..127, read from the shared-memory image.
       mbar_wait(&bar_w, 0);
-      image_col_to_tmem<MG>(sW, cgp * RH + j, t_lane + A_COL0 + cgp * 64);
+      for (int g = cgp; g < 4; g += NCG) image_col_to_tmem<MG>(sW, g * RH + j, t_lane + A_COL0 + g * 64);
       tc_fence_before();
       named_bar_arrive(BAR_R, R_ALL);
     }
@@ -281,7 +289,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_dealloc(tmem, TM_COLS);
 }
 
 struct LstmV2Bwd {
@@ -298,11 +306,11 @@ struct LstmV2Bwd {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
+__global__ void __launch_bounds__(RCfg<NB>::ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int GH = 4 * RH, MG = GH / 8;
   constexpr int W_BYTES = 16 * MG * 128;                     // hidden k-groups only: 131,072
-  constexpr int CH8 = NB / 32;
+  constexpr int CH8 = RCfg<NB>::CH8, R_ALL = RCfg<NB>::ALL, R_EPI = RCfg<NB>::EPI, NCG = RCfg<NB>::NCG;
   uint8_t* sW = smem;                                        // image as K-major A: LBO = 128, SBO = MG*128
   uint8_t* sZ = sW + W_BYTES;                                // dz MN-major B: [64 k-groups][NB/8][8][8]
   float* sX = reinterpret_cast<float*>(sZ + GH * NB * 2);    // [NB][T]
@@ -314,7 +322,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   // TMEM: [0, NB) the dh accumulator, [A_COL0, A_COL0 + 256) U (128 x 512 bf16) as the resident A operand
   constexpr uint32_t A_COL0 = 64, TM_COLS = 512;
 
-  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
   if (tid == R_EPI) {
@@ -332,7 +340,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   tc_fence_after();
   const uint32_t tmem = tmem_s;
 
-  if (warp == 16) {
+  if (warp == RCfg<NB>::MMA_WARP) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
     const uint32_t w_base = smem_u32(sW), z_base = smem_u32(sZ);
     constexpr uint32_t b_hi = umma_desc_hi(128);
@@ -357,7 +365,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
     // warp (q, cgp) copies gate block cgp (128 columns = 64 TMEM columns) of rows 32q..32q+31 into TMEM
     mbar_wait(&bar_w, 0);
-    image_row_to_tmem<MG>(sW, j, cgp * 16, 2, t_lane + A_COL0 + cgp * 64);
+    for (int g = cgp; g < 4; g += NCG) image_row_to_tmem<MG>(sW, j, g * 16, 2, t_lane + A_COL0 + g * 64);
     tc_fence_before();
     named_bar_arrive(BAR_R, R_ALL);
     float dc[CH8 * 8];
@@ -472,7 +480,7 @@ __global__ void __launch_bounds__(R_ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_dealloc(tmem, TM_COLS);
 }
 
 // ======================================================================================================
@@ -492,12 +500,12 @@ struct GruV2Fwd {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
+__global__ void __launch_bounds__(RCfg<NB>::ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int GH = 3 * RH, MG = GH / 8;                    // 384, 48
   constexpr uint32_t W_LBO = MG * 128;                       // 6144
   constexpr int W_BYTES = R_KG * MG * 128;                   // 110,592
-  constexpr int CH8 = NB / 32;
+  constexpr int CH8 = RCfg<NB>::CH8, R_ALL = RCfg<NB>::ALL, R_EPI = RCfg<NB>::EPI, NCG = RCfg<NB>::NCG;
   uint8_t* sW = smem;
   uint8_t* sH = sW + W_BYTES;
   uint8_t* sR = sH + RH * NB * 2;
@@ -512,7 +520,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
 
-  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_a, 1); mbar_init(&bar_b, 1); mbar_fence_init(); }
   __syncthreads();
   if (tid == R_EPI) {
@@ -528,7 +536,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
   tc_fence_after();
   const uint32_t tmem = tmem_s;
 
-  if (warp == 16) {
+  if (warp == RCfg<NB>::MMA_WARP) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, true, true);
     const uint32_t w_base = smem_u32(sW), h_base = smem_u32(sH), r_base = smem_u32(sR), x_base = smem_u32(sX),
                    z_base = smem_u32(sZero);
@@ -576,7 +584,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
     const int j = q * 32 + lane;
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
     mbar_wait(&bar_w, 0);
-    if (cgp < 3) image_col_to_tmem<MG>(sW, cgp * RH + j, t_lane + A_COL0 + cgp * 64);
+    for (int g = cgp; g < 3; g += NCG) image_col_to_tmem<MG>(sW, g * RH + j, t_lane + A_COL0 + g * 64);
     tc_fence_before();
     named_bar_arrive(BAR_W, R_ALL);
     float hreg[CH8 * 8];
@@ -677,7 +685,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_dealloc(tmem, TM_COLS);
 }
 
 struct GruV2Bwd {
@@ -694,11 +702,11 @@ struct GruV2Bwd {
 };
 
 template <int NB>
-__global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
+__global__ void __launch_bounds__(RCfg<NB>::ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   constexpr int GH = 3 * RH, MG = GH / 8;
   constexpr int W_BYTES = 16 * MG * 128;                     // 98,304
-  constexpr int CH8 = NB / 32;
+  constexpr int CH8 = RCfg<NB>::CH8, R_ALL = RCfg<NB>::ALL, R_EPI = RCfg<NB>::EPI, NCG = RCfg<NB>::NCG;
   uint8_t* sW = smem;                                        // image as K-major A (M = h_{t-1} unit, K = gate column)
   uint8_t* sB1 = sW + W_BYTES;                               // [d(az) | d(ah)]ᵀ : k-groups 0..15 = az, 16..31 = ah
   uint8_t* sB2 = sB1 + 2 * RH * NB * 2;                      // d(ar)ᵀ
@@ -712,7 +720,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   const int b0 = blockIdx.x * NB;
   const int T = p.T, B = p.B;
 
-  if (warp == 16) tmem_alloc(&tmem_s, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_1, 1); mbar_init(&bar_2, 1); mbar_fence_init(); }
   __syncthreads();
   if (tid == R_EPI) {
@@ -730,7 +738,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   tc_fence_after();
   const uint32_t tmem = tmem_s;
 
-  if (warp == 16) {
+  if (warp == RCfg<NB>::MMA_WARP) {
     constexpr uint32_t idesc = umma_idesc_bf16(128, NB, false, true);
     const uint32_t w_base = smem_u32(sW), b1_base = smem_u32(sB1), b2_base = smem_u32(sB2);
     constexpr uint32_t b_hi = umma_desc_hi(128);
@@ -770,7 +778,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
     const int j = q * 32 + lane;
     const uint32_t t_lane = tmem + (static_cast<uint32_t>(q * 32) << 16);
     mbar_wait(&bar_w, 0);
-    if (cgp < 3) image_row_to_tmem<MG>(sW, j, cgp * 16, 2, t_lane + A_COL0 + cgp * 64);
+    for (int g = cgp; g < 3; g += NCG) image_row_to_tmem<MG>(sW, j, g * 16, 2, t_lane + A_COL0 + g * 64);
     tc_fence_before();
     named_bar_arrive(BAR_W, R_ALL);
     float dh[CH8 * 8];
@@ -910,7 +918,7 @@ __global__ void __launch_bounds__(R_ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 16) tmem_dealloc(tmem, TM_COLS);
+  if (warp == RCfg<NB>::MMA_WARP) tmem_dealloc(tmem, TM_COLS);
 }
 
 // ------------------------------------------------------------------------------------------------------
@@ -1019,6 +1027,7 @@ extern "C" int ddls_rnn128_pack(const float* recurrent, const float* w_ih, const
 
 static int pick_tile(int B, int tile) {
   if (tile > 0) return tile;
+  if (B <= 16 * 148) return 16;          // small batches: spread over more SMs (B = 32 -> two 16-row CTAs)
   return (B <= 32 * 148) ? 32 : 64;
 }
 
@@ -1031,13 +1040,16 @@ extern "C" int ddls_lstm128_forward_v2(const float* x, const void* image, float*
   const int nb = pick_tile(B, tile);
   const size_t smem = (size_t)R_KG * 64 * 128 + (size_t)RH * nb * 2 + (size_t)T * nb * 16 + (size_t)nb * 16;
   if (smem > 227 * 1024) { set_last_error("ddls_lstm128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
-  if (nb == 32) {
+  if (nb == 16) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lstm_fwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+  } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
+    lstm_fwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
-  } else { set_last_error("ddls_lstm128_forward_v2: tile must be 32 or 64"); return 1; }
+    lstm_fwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+  } else { set_last_error("ddls_lstm128_forward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_fwd_v2_kernel launch");
 }
@@ -1052,13 +1064,16 @@ extern "C" int ddls_lstm128_backward_v2(const float* dout, const float* x, const
   const int nb = pick_tile(B, tile);
   const size_t smem = (size_t)16 * 64 * 128 + (size_t)4 * RH * nb * 2 + (size_t)nb * T * 4;
   if (smem > 227 * 1024) { set_last_error("ddls_lstm128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
-  if (nb == 32) {
+  if (nb == 16) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    lstm_bwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+  } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
+    lstm_bwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
-  } else { set_last_error("ddls_lstm128_backward_v2: tile must be 32 or 64"); return 1; }
+    lstm_bwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+  } else { set_last_error("ddls_lstm128_backward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_bwd_v2_kernel launch");
 }
@@ -1088,13 +1103,16 @@ extern "C" int ddls_gru128_forward_v2(const float* x, const void* image, float* 
   const int nb = pick_tile(B, tile);
   const size_t smem = (size_t)R_KG * 48 * 128 + 2 * (size_t)RH * nb * 2 + (size_t)T * nb * 16 + (size_t)nb * 16;
   if (smem > 227 * 1024) { set_last_error("ddls_gru128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
-  if (nb == 32) {
+  if (nb == 16) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gru_fwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+  } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_fwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
+    gru_fwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_fwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
-  } else { set_last_error("ddls_gru128_forward_v2: tile must be 32 or 64"); return 1; }
+    gru_fwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+  } else { set_last_error("ddls_gru128_forward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "gru_fwd_v2_kernel launch");
 }
@@ -1109,13 +1127,16 @@ extern "C" int ddls_gru128_backward_v2(const float* dout, const float* x, const 
   const int nb = pick_tile(B, tile);
   const size_t smem = (size_t)16 * 48 * 128 + 3 * (size_t)RH * nb * 2 + (size_t)nb * T * 4;
   if (smem > 227 * 1024) { set_last_error("ddls_gru128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
-  if (nb == 32) {
+  if (nb == 16) {
+    DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gru_bwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+  } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_bwd_v2_kernel<32><<<(B + 31) / 32, R_ALL, smem, st>>>(p);
+    gru_bwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_bwd_v2_kernel<64><<<(B + 63) / 64, R_ALL, smem, st>>>(p);
-  } else { set_last_error("ddls_gru128_backward_v2: tile must be 32 or 64"); return 1; }
+    gru_bwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+  } else { set_last_error("ddls_gru128_backward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "gru_bwd_v2_kernel launch");
 }

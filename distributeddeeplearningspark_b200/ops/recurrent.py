@@ -24,6 +24,12 @@ N.register('ddls_gru128_backward_v2', [P, P, P, P, P, P, P, P, I, I, I, I, P])
 H = 128
 
 
+def _tile() -> int:
+    """Batch rows per CTA for the v2 kernels (0 = pick by batch size; DDLS_RNN_TILE forces 16/32/64)."""
+    import os
+    return int(os.environ.get('DDLS_RNN_TILE', '0'))
+
+
 def use_v2() -> bool:
     import os
     return os.environ.get('DDLS_RNN_V1', '0') != '1'
@@ -55,13 +61,14 @@ def lstm_v2_buffers(B: int, T: int, dev, zero: bool = True):
 
 def lstm_v2_forward(x2, img, out, hs, gates, cs, B, T, return_sequences, save):
     N.call('ddls_lstm128_forward_v2', x2.data_ptr(), img.data_ptr(), out.data_ptr(), N.ptr(hs), N.ptr(gates), N.ptr(cs),
-           B, T, int(return_sequences), int(save), 0, N.stream_ptr(x2.device))
+           B, T, int(return_sequences), int(save), _tile(), N.stream_ptr(x2.device))
 
 
 def lstm_v2_backward(dout, x2, img, gates, cs, dz, d_wih, d_bias, d_rec, B, T, return_sequences, hs):
     """BPTT + recurrent weight gradient.  d_wih / d_bias are accumulated into, d_rec [128,512] is overwritten."""
     N.call('ddls_lstm128_backward_v2', dout.data_ptr(), x2.data_ptr(), img.data_ptr(), gates.data_ptr(), cs.data_ptr(),
-           dz.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(return_sequences), 0, N.stream_ptr(x2.device))
+           dz.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(return_sequences), _tile(),
+           N.stream_ptr(x2.device))
     B8 = (B + 7) // 8
     if T > 1:
         b_img = dz.data_ptr() + B8 * 4 * H * 16          # k-groups of t >= 1
@@ -98,12 +105,13 @@ def gru_v2_buffers(B: int, T: int, dev):
 
 def gru_v2_forward(x2, img, out, hs, rh, zrh, hprev, B, T, return_sequences, save):
     N.call('ddls_gru128_forward_v2', x2.data_ptr(), img.data_ptr(), out.data_ptr(), N.ptr(hs), N.ptr(rh), N.ptr(zrh),
-           N.ptr(hprev), B, T, int(return_sequences), int(save), 0, N.stream_ptr(x2.device))
+           N.ptr(hprev), B, T, int(return_sequences), int(save), _tile(), N.stream_ptr(x2.device))
 
 
 def gru_v2_backward(dout, x2, img, zrh, hprev, da, d_wih, d_bias, d_rec, B, T, return_sequences, hs, rh):
     N.call('ddls_gru128_backward_v2', dout.data_ptr(), x2.data_ptr(), img.data_ptr(), zrh.data_ptr(), hprev.data_ptr(),
-           da.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(return_sequences), 0, N.stream_ptr(x2.device))
+           da.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(return_sequences), _tile(),
+           N.stream_ptr(x2.device))
     B8 = (B + 7) // 8
     if T > 1:
         st = N.stream_ptr(x2.device)

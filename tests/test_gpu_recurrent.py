@@ -52,6 +52,29 @@ def test_recurrent_forward_backward_match_fp32(cell, B, T, seq, gen, monkeypatch
         assert _rel(g, gr) < 4e-2, (name, _rel(g, gr))
 
 
+@pytest.mark.parametrize('tile', [16, 32, 64])
+@pytest.mark.parametrize('cell', ['lstm', 'gru'])
+def test_recurrent_v2_every_tile_size(cell, tile, monkeypatch):
+    from distributeddeeplearningspark_b200.ops import recurrent as R
+    monkeypatch.setenv('DDLS_RNN_TILE', str(tile))
+    monkeypatch.setenv('DDLS_RNN_V1', '0')
+    dev = torch.device('cuda', 0)
+    k, r, b = _make(cell, 3, dev)
+    B, T = 150, 11
+    x = torch.rand(B, T, 1, device=dev)
+    ref = (L.lstm_reference if cell == 'lstm' else L.gru_reference)(x, k, r, b, False)
+    w = torch.randn_like(ref)
+    (ref * w).sum().backward()
+    gref = [t.grad.clone() for t in (k, r, b)]
+    for t in (k, r, b):
+        t.grad = None
+    out = (R.lstm_layer if cell == 'lstm' else R.gru_layer)(x, k, r, b, False)
+    assert _rel(out, ref.detach()) < 2e-2
+    (out * w).sum().backward()
+    for g, gr in zip((k.grad, r.grad, b.grad), gref):
+        assert _rel(g, gr) < 4e-2
+
+
 def test_dense_mse_head_matches_autograd():
     from distributeddeeplearningspark_b200.ops import heads
     dev = torch.device('cuda', 0)
