@@ -335,6 +335,10 @@ static int dispatch_bn(const GemmParams& p, int splits, cudaStream_t st) {
 
 }  // namespace ddls
 
+namespace ddls {
+bool tma_gemm_applicable(const void* A, const void* B, const void* C, int M, int N, int K, int lda, int ldb, int ldc,
+                         unsigned flags);
+}
 extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda,
                               int ldb, int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags,
                               void* workspace, size_t workspace_bytes, void* stream) {
@@ -350,6 +354,8 @@ extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float
   splits = (K + kps - 1) / kps;
   p.k_per_split = kps;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (splits == 1 && M >= 256 && tma_gemm_applicable(A, B, C, M, N, K, lda, ldb, ldc, flags))
+    return ddls_gemm_tma(A, B, C, bias, M, N, K, lda, ldb, ldc, a_mn_major, b_mn_major, flags, stream);
   const unsigned epi = flags & (DDLS_GEMM_RELU | DDLS_GEMM_BIAS | DDLS_GEMM_OUT_BF16 | DDLS_GEMM_ACCUMULATE);
   if (splits > 1) {
     const size_t need = (size_t)splits * M * N * sizeof(float);

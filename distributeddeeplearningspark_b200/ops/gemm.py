@@ -7,7 +7,7 @@ import torch
 
 from .. import _native as N
 
-RELU, BIAS, OUT_BF16, A_F32, B_F32, ACCUMULATE = 1, 2, 4, 16, 32, 128
+RELU, BIAS, OUT_BF16, A_F32, B_F32, ACCUMULATE, FORCE_V1, NO_TMA = 1, 2, 4, 16, 32, 128, 256, 512
 
 _WORKSPACES: Dict[torch.device, torch.Tensor] = {}
 
@@ -24,7 +24,7 @@ def workspace(device, nbytes: int) -> torch.Tensor:
 
 def gemm_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = None, relu: bool = False,
               out_dtype=torch.float32, a_mn_major: bool = False, b_mn_major: bool = False, split_k: int = 1,
-              out: Optional[torch.Tensor] = None, accumulate: bool = False) -> torch.Tensor:
+              out: Optional[torch.Tensor] = None, accumulate: bool = False, no_tma: bool = False) -> torch.Tensor:
     """C[M,N] = A·Bᵀ.  ``a`` is [M,K] (or [K,M] if ``a_mn_major``); ``b`` is [N,K] (or [K,N] if ``b_mn_major``).
     Operands may be bf16 or fp32 (fp32 is rounded to bf16 while staging into shared memory)."""
     assert a.is_cuda and b.is_cuda and a.stride(-1) == 1 and b.stride(-1) == 1
@@ -37,6 +37,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, bias: Optional[torch.Tensor] = N
     flags = (RELU if relu else 0) | (BIAS if bias is not None else 0) | (OUT_BF16 if out.dtype == torch.bfloat16 else 0)
     flags |= (A_F32 if a.dtype == torch.float32 else 0) | (B_F32 if b.dtype == torch.float32 else 0)
     flags |= ACCUMULATE if accumulate else 0
+    flags |= NO_TMA if no_tma else 0
     split_k = max(1, min(split_k, (K + 63) // 64))
     ws_ptr, ws_bytes = 0, 0
     if split_k > 1:

@@ -30,6 +30,7 @@ unsigned long long ddls_launch_count(void);
 #define DDLS_GEMM_SPLITK_WS 64u   /* internal */
 #define DDLS_GEMM_ACCUMULATE 128u /* C += result (fp32 C) */
 #define DDLS_GEMM_FORCE_V1 256u   /* use the register-staged mainloop even when the cp.async one applies */
+#define DDLS_GEMM_NO_TMA 512u     /* do not route large problems to the TMA / warp-specialised kernel */
 /* C[M,N] = op(A)·op(B)ᵀ (+bias, ReLU, cast).  a_mn_major=0: A is [M,K] row-major; 1: A is [K,M]
  * row-major.  Same for B over N.  Operands are bf16, or fp32 with the *_F32 flags.  split_k>1 writes
  * fp32 partial tiles to `workspace` (split_k*M*N*4 bytes of scratch) and a second kernel sums them
@@ -37,6 +38,10 @@ unsigned long long ddls_launch_count(void);
 int ddls_gemm_bf16(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
                    int ldc, int a_mn_major, int b_mn_major, int split_k, unsigned flags, void* workspace,
                    size_t workspace_bytes, void* stream);
+/* The persistent TMA-fed, warp-specialised kernel (csrc/tma_gemm.cu) directly: bf16 operands, 16-byte aligned
+ * bases, lda/ldb/N multiples of 8, no split-K.  ddls_gemm_bf16 routes to it on its own for M >= 256, split_k == 1. */
+int ddls_gemm_tma(const void* A, const void* B, void* C, const float* bias, int M, int N, int K, int lda, int ldb,
+                  int ldc, int a_mn_major, int b_mn_major, unsigned flags, void* stream);
 
 /* ---- fused optimizers over a flat fp32 parameter space --------------------------------------
  * Keras-2 update rules named by the reference ('adam' ddl_mnist_aztk.py:195, ddl_nyiso_aztk.py:255;
