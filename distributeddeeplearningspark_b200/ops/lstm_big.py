@@ -15,6 +15,9 @@ N.register('ddls_lstm_big_perm_vec', [P, P, I, P])
 N.register('ddls_lstm_big_unperm', [P, P, I, I, I, P])
 N.register('ddls_lstm_big_colsum', [P, P, P, I, I, P])
 N.register('ddls_lstm_big_step_fwd', [P, P, P, P, I, P, P, P, P, P, P, P, I, I, P])
+N.register('ddls_lstm_big_zx1', [P, P, P, P, I, I, I, P])
+N.register('ddls_lstm_big_step_fwd2', [P, P, P, P, P, P, I, I, I, I, P])
+N.register('ddls_lstm_big_step_bwd2', [P, P, P, P, P, P, P, I, I, I, I, P])
 N.register('ddls_lstm_big_step_bwd', [P, P, P, P, P, P, P, P, P, I, I, I, I, P])
 
 
@@ -30,7 +33,7 @@ class StackedLSTMBuffers:
         self.gates = [torch.empty((T, B, 4 * h), dtype=bf, device=dev) for h in self.H]
         self.dz = [torch.empty((T, B, 4 * h), dtype=bf, device=dev) for h in self.H]
         self.dc = [torch.empty((B, h), dtype=f32, device=dev) for h in self.H]
-        self.zx = [None] + [torch.empty((T, B, 4 * h), dtype=bf, device=dev) for h in self.H[1:]]
+        self.zx = [torch.empty((T, B, 4 * h), dtype=bf, device=dev) for h in self.H]
         self.dx = [None] + [torch.empty((T, B, self.H[i - 1]), dtype=bf, device=dev) for i in range(1, len(layers))]
         self.u_perm = [torch.empty((h, 4 * h), dtype=bf, device=dev) for h in self.H]
         self.w_perm = [None] + [torch.empty((self.H[i - 1], 4 * self.H[i]), dtype=bf, device=dev)
@@ -69,18 +72,18 @@ def forward(layers, bufs: StackedLSTMBuffers, x2: torch.Tensor, st: int, save: b
     for i, l in enumerate(layers):
         h = l.units
         last_layer = i == len(layers) - 1
-        if i > 0:
+        if i == 0:
+            N.call('ddls_lstm_big_zx1', x2.data_ptr(), bufs.wih_perm.data_ptr(), bufs.b_perm[0].data_ptr(),
+                   bufs.zx[0].data_ptr(), B, T, h, st)
+        else:
             hin = bufs.H[i - 1]
-            gemm_bf16(bufs.hs[i - 1][1:].reshape(T * B, hin), bufs.w_perm[i], b_mn_major=True,
+            gemm_bf16(bufs.hs[i - 1][1:].reshape(T * B, hin), bufs.w_perm[i], bias=bufs.b_perm[i], b_mn_major=True,
                       out=bufs.zx[i].view(T * B, 4 * h))
         hs, cs = bufs.hs[i], bufs.cs[i]
         for t in range(T):
-            N.call('ddls_lstm_big_step_fwd', hs[t].data_ptr(), bufs.u_perm[i].data_ptr(),
-                   bufs.zx[i][t].data_ptr() if i > 0 else 0, (x2.data_ptr() + 4 * t) if i == 0 else 0, T,
-                   bufs.wih_perm.data_ptr() if i == 0 else 0, bufs.b_perm[i].data_ptr(), cs[t].data_ptr(),
-                   cs[t + 1].data_ptr(), hs[t + 1].data_ptr(),
-                   bufs.h_last.data_ptr() if (last_layer and t == T - 1) else 0,
-                   bufs.gates[i][t].data_ptr() if save else 0, B, h, st)
+            N.call('ddls_lstm_big_step_fwd2', hs.data_ptr(), bufs.u_perm[i].data_ptr(), bufs.zx[i].data_ptr(),
+                   cs.data_ptr(), bufs.gates[i].data_ptr() if save else 0,
+                   bufs.h_last.data_ptr() if (last_layer and t == T - 1) else 0, B, T, h, t, st)
     return bufs.h_last
 
 
@@ -95,11 +98,9 @@ def backward(layers, bufs: StackedLSTMBuffers, x2: torch.Tensor, dh_last: torch.
         top = i == L - 1
         dz, gates, cs = bufs.dz[i], bufs.gates[i], bufs.cs[i]
         for t in reversed(range(T)):
-            first = t == T - 1
-            N.call('ddls_lstm_big_step_bwd', dz[t + 1].data_ptr() if not first else 0, bufs.u_perm[i].data_ptr(),
-                   bufs.dx[i + 1][t].data_ptr() if not top else 0, dh_last.data_ptr() if (top and first) else 0,
-                   gates[t].data_ptr(), cs[t + 1].data_ptr(), cs[t].data_ptr(), bufs.dc[i].data_ptr(), dz[t].data_ptr(),
-                   B, h, int(not first), int(first), st)
+            N.call('ddls_lstm_big_step_bwd2', dz.data_ptr(), bufs.u_perm[i].data_ptr(),
+                   bufs.dx[i + 1][t].data_ptr() if not top else 0, dh_last.data_ptr() if (top and t == T - 1) else 0,
+                   gates.data_ptr(), cs.data_ptr(), bufs.dc[i].data_ptr(), B, T, h, t, st)
         dz2 = dz.view(T * B, 4 * h)
         g = bufs.gtmp.view(-1)[:h * 4 * h].view(h, 4 * h)
         # recurrent kernel: dU = sum_t h_{t-1}^T dZ_t

@@ -122,6 +122,19 @@ int ddls_lstm_big_step_fwd(const void* h_prev, const void* u_perm, const void* z
 int ddls_lstm_big_step_bwd(const void* dz_next, const void* u_perm, const void* dout_bf16, const float* dout_f32,
                            const void* gates, const float* c_t, const float* c_prev, float* dc, void* dz, int B, int H,
                            int use_acc, int first, void* stream);
+/* Second-generation step kernels on the TMA mainloop (csrc/lstm_big_tma.cu).  zx1: input projection of a first layer
+ * with input dimension 1, zx[t][b][:] = x[b][t]*wih_perm + bias_perm (bf16).  step_fwd2 runs time step t of one layer
+ * over whole-sequence buffers: hs [T+1][B][H] bf16 (hs[0] = initial state), cs [T+1][B][H] fp32, zx [T][B][4H] bf16
+ * with the bias folded in, gates [T][B][4H] bf16 (or NULL); it writes hs[t+1], cs[t+1], gates[t]. */
+int ddls_lstm_big_zx1(const float* x, const float* wih_perm, const float* bias_perm, void* zx, int B, int T, int H,
+                      void* stream);
+int ddls_lstm_big_step_fwd2(const void* hs, const void* u_perm, const void* zx, float* cs, void* gates, float* h_out_f32,
+                            int B, int T, int H, int t, void* stream);
+/* BPTT step t on whole-sequence buffers (dz [T][B][4H] bf16, gates, cs as above, dc [B][H] fp32 scratch): K = 4H is
+ * split over a 4-CTA cluster whose partial accumulators are exchanged through distributed shared memory. */
+int ddls_lstm_big_step_bwd2(void* dz, const void* u_perm, const void* dout_bf16, const float* dout_f32, const void* gates,
+                            const float* cs, float* dc, int B, int T, int H, int t, void* stream);
+
 
 /* ---- persistent GRU(128) recurrence, tcgen05 (Keras GRU reset_after=False, ddl_nyiso_aztk.py:201-203) ----
  * Gate order z,r,h.  When save_for_backward: hs [T,B,H] bf16 (h_t), rh [T,B,H] bf16 (r_t*h_{t-1}),
