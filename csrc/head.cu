@@ -215,6 +215,88 @@ __global__ void __launch_bounds__(MH_THREADS, 1) head_mse_kernel(const float* __
   }
 }
 
+// Large-batch variant (B*H beyond what one CTA does in a few microseconds, e.g. the scaled stacked LSTM's
+// [512 x 1024] head): two launches, every output still overwritten.
+//   rows kernel: one warp per batch row -> pred, dh (= dL/dpred · wdᵀ)
+//   cols kernel: 32 hidden columns per CTA over all rows -> dwd; CTA 0 also reduces the loss and dbd
+template <int O>
+__global__ void __launch_bounds__(256) head_mse_rows_kernel(const float* __restrict__ h, const float* __restrict__ wd,
+                                                            const float* __restrict__ bd, const float* __restrict__ y,
+                                                            float* __restrict__ pred, float* __restrict__ dh, int B, int H) {
+  const int lane = threadIdx.x & 31, b = blockIdx.x * 8 + (threadIdx.x >> 5);
+  if (b >= B) return;
+  const float inv = 1.0f / ((float)B * (float)O);
+  float acc[O];
+#pragma unroll
+  for (int o = 0; o < O; ++o) acc[o] = 0.f;
+  for (int j = lane; j < H; j += 32) {
+    const float hv = h[(size_t)b * H + j];
+#pragma unroll
+    for (int o = 0; o < O; ++o) acc[o] = fmaf(hv, wd[j * O + o], acc[o]);
+  }
+  float d[O];
+#pragma unroll
+  for (int o = 0; o < O; ++o) {
+    const float pr = warp_sum(acc[o]) + bd[o];
+    if (lane == 0) pred[(size_t)b * O + o] = pr;
+    d[o] = (y != nullptr) ? 2.f * (pr - y[(size_t)b * O + o]) * inv : 0.f;
+  }
+  if (y == nullptr) return;
+  for (int j = lane; j < H; j += 32) {
+    float g = 0.f;
+#pragma unroll
+    for (int o = 0; o < O; ++o) g = fmaf(d[o], wd[j * O + o], g);
+    dh[(size_t)b * H + j] = g;
+  }
+}
+
+template <int O>
+__global__ void __launch_bounds__(256) head_mse_cols_kernel(const float* __restrict__ h, const float* __restrict__ y,
+                                                            const float* __restrict__ pred, float* __restrict__ loss,
+                                                            float* __restrict__ dwd, float* __restrict__ dbd, int B, int H) {
+  __shared__ float red[8][32][O];
+  __shared__ float red2[8][O + 1];
+  const int lane = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int j = blockIdx.x * 32 + lane;
+  const float inv = 1.0f / ((float)B * (float)O);
+  float acc[O], dsum[O], lsum = 0.f;
+#pragma unroll
+  for (int o = 0; o < O; ++o) { acc[o] = 0.f; dsum[o] = 0.f; }
+  for (int b = ry; b < B; b += 8) {
+    const float hv = (j < H) ? h[(size_t)b * H + j] : 0.f;
+#pragma unroll
+    for (int o = 0; o < O; ++o) {
+      const float e = pred[(size_t)b * O + o] - y[(size_t)b * O + o];
+      acc[o] = fmaf(hv, 2.f * e * inv, acc[o]);
+      dsum[o] += 2.f * e * inv;
+      lsum += e * e * inv;
+    }
+  }
+#pragma unroll
+  for (int o = 0; o < O; ++o) red[ry][lane][o] = acc[o];
+  if (lane == 0) {
+#pragma unroll
+    for (int o = 0; o < O; ++o) red2[ry][o] = dsum[o];
+    red2[ry][O] = lsum;
+  }
+  __syncthreads();
+  if (ry == 0 && j < H) {
+#pragma unroll
+    for (int o = 0; o < O; ++o) {
+      float g = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) g += red[r][lane][o];
+      dwd[j * O + o] = g;
+    }
+  }
+  if (blockIdx.x == 0 && threadIdx.x <= O) {
+    float g = 0.f;
+#pragma unroll
+    for (int r = 0; r < 8; ++r) g += red2[r][threadIdx.x];
+    if (threadIdx.x < O) dbd[threadIdx.x] = g; else loss[0] = g;
+  }
+}
+
 }  // namespace ddls
 
 using namespace ddls;
@@ -223,6 +305,23 @@ extern "C" int ddls_dense_mse(const float* h, const float* wd, const float* bd, 
                               float* loss, float* dh, float* dwd, float* dbd, int B, int H, int O, void* stream) {
   if (B <= 0) return 0;
   if (O > HD_MAX_O || O < 1) { set_last_error("ddls_dense_mse: supports 1 <= O <= 4 (got O=%d)", O); return 1; }
+  cudaStream_t st0 = static_cast<cudaStream_t>(stream);
+  if ((size_t)B * H > 32768) {
+#define DDLS_LAUNCH_MSE_BIG(OO)                                                                                    \
+  {                                                                                                                 \
+    head_mse_rows_kernel<OO><<<(B + 7) / 8, 256, 0, st0>>>(h, wd, bd, y, pred, dh, B, H);                          \
+    if (y != nullptr) head_mse_cols_kernel<OO><<<(H + 31) / 32, 256, 0, st0>>>(h, y, pred, loss, dwd, dbd, B, H);   \
+  }
+    switch (O) {
+      case 1: DDLS_LAUNCH_MSE_BIG(1) break;
+      case 2: DDLS_LAUNCH_MSE_BIG(2) break;
+      case 3: DDLS_LAUNCH_MSE_BIG(3) break;
+      default: DDLS_LAUNCH_MSE_BIG(4) break;
+    }
+#undef DDLS_LAUNCH_MSE_BIG
+    count_launch(y != nullptr ? 2 : 1);
+    return check_cuda(cudaGetLastError(), "head_mse rows/cols launch");
+  }
   const size_t smem = (size_t)B * O * sizeof(float);
   if (smem > 160 * 1024) { set_last_error("ddls_dense_mse: batch %d too large for the single-CTA head", B); return 1; }
   cudaStream_t st = static_cast<cudaStream_t>(stream);

@@ -57,21 +57,46 @@ __global__ void __launch_bounds__(256) unperm_kernel(const float* __restrict__ s
   }
 }
 
-// out[keras col] (+)= sum_r w[r] * X[r][perm col]   (X bf16 [R][4H] permuted; w == nullptr -> plain column sums).
-// Each CTA reduces a slab of rows for 256 columns and adds its partial with one atomic per column.
+// out_plain[keras col] += sum_r X[r][perm col];  out_w[keras col] += sum_r w[r] * X[r][perm col]   (either may be null)
+// X bf16 [R][4H] permuted.  One pass over X computes both: a CTA owns 512 columns x 256 rows, a thread 8 columns
+// (16-byte loads) of every 4th row; partials meet in shared memory and leave with one atomic per column.
+constexpr int CS_ROWS = 256;
 __global__ void __launch_bounds__(256) colsum_perm_kernel(const __nv_bfloat16* __restrict__ X, const float* __restrict__ w,
-                                                          float* __restrict__ out, int R, int H, int rows_per_cta) {
+                                                          float* __restrict__ out_plain, float* __restrict__ out_w, int R,
+                                                          int H) {
+  __shared__ float red[2][4][512];
   const int G = 4 * H;
-  const int n = blockIdx.x * 256 + threadIdx.x;
-  const int r0 = blockIdx.y * rows_per_cta, r1 = min(R, r0 + rows_per_cta);
-  if (n >= G) return;
-  float acc = 0.f;
-  for (int r = r0; r < r1; ++r) {
-    const float v = __bfloat162float(X[(size_t)r * G + n]);
-    acc = fmaf(w != nullptr ? w[r] : 1.f, v, acc);
+  const int tx = threadIdx.x & 63, ty = threadIdx.x >> 6;
+  const int col = blockIdx.x * 512 + tx * 8;
+  const int r0 = blockIdx.y * CS_ROWS, r1 = min(R, r0 + CS_ROWS);
+  float a[8], aw[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { a[j] = 0.f; aw[j] = 0.f; }
+  if (col < G) {
+#pragma unroll 4
+    for (int r = r0 + ty; r < r1; r += 4) {
+      const uint4 q = *reinterpret_cast<const uint4*>(X + (size_t)r * G + col);
+      const float wv = (w != nullptr) ? __ldg(w + r) : 0.f;
+      const uint32_t u[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float lo = __uint_as_float(u[i] << 16), hi = __uint_as_float(u[i] & 0xFFFF0000u);
+        a[2 * i] += lo; a[2 * i + 1] += hi;
+        aw[2 * i] = fmaf(wv, lo, aw[2 * i]); aw[2 * i + 1] = fmaf(wv, hi, aw[2 * i + 1]);
+      }
+    }
   }
-  const int ub = n >> 7, g = (n >> 5) & 3, u = n & 31;
-  atomicAdd(out + g * H + ub * 32 + u, acc);
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { red[0][ty][tx * 8 + j] = a[j]; red[1][ty][tx * 8 + j] = aw[j]; }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 512; c += 256) {
+    const int n = blockIdx.x * 512 + c;
+    if (n >= G) continue;
+    const int ub = n >> 7, g = (n >> 5) & 3, u = n & 31;
+    const int k = g * H + ub * 32 + u;
+    if (out_plain != nullptr) atomicAdd(out_plain + k, red[0][0][c] + red[0][1][c] + red[0][2][c] + red[0][3][c]);
+    if (out_w != nullptr) atomicAdd(out_w + k, red[1][0][c] + red[1][1][c] + red[1][2][c] + red[1][3][c]);
+  }
 }
 
 struct BigFwd {
@@ -258,10 +283,11 @@ extern "C" int ddls_lstm_big_unperm(const float* src, float* dst, int rows, int 
   return check_cuda(cudaGetLastError(), "unperm_kernel launch");
 }
 
-extern "C" int ddls_lstm_big_colsum(const void* X, const float* w, float* out, int R, int H, void* stream) {
-  const int rows_per_cta = 512;
-  dim3 grid((4 * H + 255) / 256, (R + rows_per_cta - 1) / rows_per_cta);
-  colsum_perm_kernel<<<grid, 256, 0, ST(stream)>>>(static_cast<const __nv_bfloat16*>(X), w, out, R, H, rows_per_cta);
+extern "C" int ddls_lstm_big_colsum(const void* X, const float* w, float* out_plain, float* out_weighted, int R, int H,
+                                    void* stream) {
+  if (check_big(1, H, "ddls_lstm_big_colsum")) return 1;
+  dim3 grid((4 * H + 511) / 512, (R + CS_ROWS - 1) / CS_ROWS);
+  colsum_perm_kernel<<<grid, 256, 0, ST(stream)>>>(static_cast<const __nv_bfloat16*>(X), w, out_plain, out_weighted, R, H);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "colsum_perm_kernel launch");
 }

@@ -221,6 +221,8 @@ struct BigBwd2 {
 using BwdPipe = TmaPipe<128, false, false, 4>;
 constexpr int BB_RECV_LD = 132;                                   // floats per received row (padded: conflict-free v4)
 constexpr int BB_RECV_BYTES = 4 * 32 * BB_RECV_LD * 4;
+constexpr int BB_THREADS = 320;                                   // producer, MMA, 4 TMEM warps + 4 more for phase 2
+constexpr int BB_ROWS_PER_WARP = 4;
 constexpr int BB_SMEM = BwdPipe::STAGES * BwdPipe::STAGE_BYTES + BB_RECV_BYTES + 1024;
 
 DDLS_DEVINL uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
@@ -235,7 +237,7 @@ DDLS_DEVINL void st_cluster_v4(uint32_t addr, float a, float b, float c, float d
   asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-__global__ void __cluster_dims__(1, 1, 4) __launch_bounds__(BF_THREADS, 1)
+__global__ void __cluster_dims__(1, 1, 4) __launch_bounds__(BB_THREADS, 1)
 lstm_big_bwd2_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_constant__ CUtensorMap tu, BigBwd2 p) {
   using Pipe = BwdPipe;
   constexpr int S = Pipe::STAGES;
@@ -262,6 +264,30 @@ lstm_big_bwd2_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_const
   const uint32_t tmem = tmem_slot;
   const int kblocks = p.H / 64;                       // this CTA's quarter of K = 4H
   const int k_base = crank * p.H;
+  // Phase-2 operands do not depend on the GEMM: warps 2..9 fetch theirs now, behind the mainloop.
+  const int e = warp - 2;
+  const int unit = n0 + 4 * lane;
+  const int pc = (unit >> 5) * 128 + (unit & 31);
+  uint2 pre_g[BB_ROWS_PER_WARP][4], pre_do[BB_ROWS_PER_WARP];
+  float4 pre_ct[BB_ROWS_PER_WARP], pre_cp[BB_ROWS_PER_WARP], pre_dc[BB_ROWS_PER_WARP];
+  if (warp >= 2) {
+#pragma unroll
+    for (int rr = 0; rr < BB_ROWS_PER_WARP; ++rr) {
+      const int b = m0 + 32 * (int)crank + e * BB_ROWS_PER_WARP + rr;
+      pre_dc[rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+      pre_do[rr] = make_uint2(0u, 0u);
+      if (b < p.B) {
+        const size_t o = (size_t)b * p.H + unit;
+        const __nv_bfloat16* gs = p.gates + (size_t)b * G + pc;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) pre_g[rr][g] = *reinterpret_cast<const uint2*>(gs + g * 32);
+        pre_ct[rr] = *reinterpret_cast<const float4*>(p.c_t + o);
+        pre_cp[rr] = *reinterpret_cast<const float4*>(p.c_prev + o);
+        if (!p.first) pre_dc[rr] = *reinterpret_cast<const float4*>(p.dc + o);
+        if (p.dout_bf16 != nullptr) pre_do[rr] = *reinterpret_cast<const uint2*>(p.dout_bf16 + o);
+      }
+    }
+  }
 
   if (p.use_acc) {
     if (warp == 0) {
@@ -291,19 +317,19 @@ lstm_big_bwd2_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_const
     }
   }
   cluster_wait();                                     // every CTA of the cluster has started
-  if (p.use_acc && warp >= 2) {
+  if (p.use_acc && warp >= 2 && warp < 6) {
     // phase 1: rows 32q..32q+31 of this CTA's partial go to CTA q, slot = my rank
     const int quad = warp & 3;
     mbar_wait(&tfull, 0);
     tc_fence_after();
     const uint32_t dst = map_to_cta(smem_u32(recv + (crank * 32 + lane) * BB_RECV_LD), quad);
 #pragma unroll
-    for (int c = 0; c < 128; c += 32) {
-      uint32_t v[32];
-      tmem_ld32(tmem + (static_cast<uint32_t>(quad * 32) << 16) + c, v);
+    for (int c = 0; c < 128; c += 16) {
+      uint32_t v[16];
+      tmem_ld16(tmem + (static_cast<uint32_t>(quad * 32) << 16) + c, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int j = 0; j < 32; j += 4)
+      for (int j = 0; j < 16; j += 4)
         st_cluster_v4(dst + (c + j) * 4, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
                       __uint_as_float(v[j + 3]));
     }
@@ -313,12 +339,9 @@ lstm_big_bwd2_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_const
   cluster_wait();                                     // all partials have landed; no remote access after this point
   if (warp >= 2) {
     // phase 2: this CTA owns batch rows m0 + 32*crank .. +31, units n0 .. n0+127; lane = 4 consecutive units
-    const int e = warp - 2;
-    const int unit = n0 + 4 * lane;
-    const int pc = (unit >> 5) * 128 + (unit & 31);
-#pragma unroll 2
-    for (int rr = 0; rr < 8; ++rr) {
-      const int row = e * 8 + rr;
+#pragma unroll
+    for (int rr = 0; rr < BB_ROWS_PER_WARP; ++rr) {
+      const int row = e * BB_ROWS_PER_WARP + rr;
       const int b = m0 + 32 * (int)crank + row;
       if (b >= p.B) continue;
       float dh[4] = {0.f, 0.f, 0.f, 0.f};
@@ -331,7 +354,7 @@ lstm_big_bwd2_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_const
       }
       const size_t o = (size_t)b * p.H + unit;
       if (p.dout_bf16 != nullptr) {
-        const uint2 q = *reinterpret_cast<const uint2*>(p.dout_bf16 + o);
+        const uint2 q = pre_do[rr];
         dh[0] += __uint_as_float(q.x << 16); dh[1] += __uint_as_float(q.x & 0xFFFF0000u);
         dh[2] += __uint_as_float(q.y << 16); dh[3] += __uint_as_float(q.y & 0xFFFF0000u);
       }
@@ -340,17 +363,13 @@ lstm_big_bwd2_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_const
         dh[0] += q.x; dh[1] += q.y; dh[2] += q.z; dh[3] += q.w;
       }
       float gt[4][4];
-      const __nv_bfloat16* gs = p.gates + (size_t)b * G + pc;
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
-        const uint2 q = *reinterpret_cast<const uint2*>(gs + g * 32);
+        const uint2 q = pre_g[rr][g];
         gt[g][0] = __uint_as_float(q.x << 16); gt[g][1] = __uint_as_float(q.x & 0xFFFF0000u);
         gt[g][2] = __uint_as_float(q.y << 16); gt[g][3] = __uint_as_float(q.y & 0xFFFF0000u);
       }
-      const float4 ct4 = *reinterpret_cast<const float4*>(p.c_t + o);
-      const float4 cp4 = *reinterpret_cast<const float4*>(p.c_prev + o);
-      float4 dc4 = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (!p.first) dc4 = *reinterpret_cast<const float4*>(p.dc + o);
+      const float4 ct4 = pre_ct[rr], cp4 = pre_cp[rr], dc4 = pre_dc[rr];
       const float ct[4] = {ct4.x, ct4.y, ct4.z, ct4.w}, cpv[4] = {cp4.x, cp4.y, cp4.z, cp4.w};
       float dcv[4] = {dc4.x, dc4.y, dc4.z, dc4.w};
       float zi[4], zf[4], zg[4], zo[4];
@@ -453,7 +472,7 @@ extern "C" int ddls_lstm_big_step_bwd2(void* dz, const void* u_perm, const void*
             last ? 0 : t + 1, last ? 0 : 1, last};
   DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_big_bwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BB_SMEM));
   dim3 grid((B + 127) / 128, H / 128, 4);
-  lstm_big_bwd2_kernel<<<grid, BF_THREADS, BB_SMEM, ST(stream)>>>(tdz, tu, p);
+  lstm_big_bwd2_kernel<<<grid, BB_THREADS, BB_SMEM, ST(stream)>>>(tdz, tu, p);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_big_bwd2_kernel launch");
 }

@@ -13,7 +13,7 @@ P, I = N.c_void_p, N.c_int
 N.register('ddls_lstm_big_perm_cast', [P, P, I, I, P])
 N.register('ddls_lstm_big_perm_vec', [P, P, I, P])
 N.register('ddls_lstm_big_unperm', [P, P, I, I, I, P])
-N.register('ddls_lstm_big_colsum', [P, P, P, I, I, P])
+N.register('ddls_lstm_big_colsum', [P, P, P, P, I, I, P])
 N.register('ddls_lstm_big_step_fwd', [P, P, P, P, I, P, P, P, P, P, P, P, I, I, P])
 N.register('ddls_lstm_big_zx1', [P, P, P, P, I, I, I, P])
 N.register('ddls_lstm_big_step_fwd2', [P, P, P, P, P, P, I, I, I, I, P])
@@ -106,11 +106,12 @@ def backward(layers, bufs: StackedLSTMBuffers, x2: torch.Tensor, dh_last: torch.
         # recurrent kernel: dU = sum_t h_{t-1}^T dZ_t
         gemm_bf16(bufs.hs[i][:T].reshape(T * B, h), dz2, a_mn_major=True, b_mn_major=True, out=g)
         N.call('ddls_lstm_big_unperm', g.data_ptr(), l.recurrent_kernel.grad.data_ptr(), h, h, 0, st)
-        N.call('ddls_lstm_big_colsum', dz2.data_ptr(), 0, l.bias.grad.data_ptr(), T * B, h, st)
         if i == 0:
             bufs.xw.view(T, B).copy_(x2.t())
-            N.call('ddls_lstm_big_colsum', dz2.data_ptr(), bufs.xw.data_ptr(), l.kernel.grad.data_ptr(), T * B, h, st)
+            N.call('ddls_lstm_big_colsum', dz2.data_ptr(), bufs.xw.data_ptr(), l.bias.grad.data_ptr(),
+                   l.kernel.grad.data_ptr(), T * B, h, st)
         else:
+            N.call('ddls_lstm_big_colsum', dz2.data_ptr(), 0, l.bias.grad.data_ptr(), 0, T * B, h, st)
             hin = bufs.H[i - 1]
             xin = bufs.hs[i - 1][1:].reshape(T * B, hin)
             gw = bufs.gtmp.view(-1)[:hin * 4 * h].view(hin, 4 * h)

@@ -113,7 +113,7 @@ int ddls_lstm_big_perm_cast(const float* src, void* dst_bf16, int rows, int H, v
 int ddls_lstm_big_perm_vec(const float* src, float* dst, int H, void* stream);                 /* [4H] Keras -> perm */
 int ddls_lstm_big_unperm(const float* src, float* dst, int rows, int H, int accumulate, void* stream);
 /* out[keras col] += sum_r w[r]*X[r][perm col] (w NULL: column sums); X bf16 [R,4H]; caller zeroes out. */
-int ddls_lstm_big_colsum(const void* X, const float* w, float* out, int R, int H, void* stream);
+int ddls_lstm_big_colsum(const void* X, const float* w, float* out_plain, float* out_weighted, int R, int H, void* stream);
 /* One time step: gates from h_prev·U (+ zx or x*w_ih) + bias; writes c_next, h_next (bf16), gates (bf16, perm). */
 int ddls_lstm_big_step_fwd(const void* h_prev, const void* u_perm, const void* zx, const float* x, int x_stride,
                            const float* wih_perm, const float* bias_perm, const float* c_prev, float* c_next,

@@ -79,7 +79,7 @@ def test_dense_mse_head_matches_autograd():
     from distributeddeeplearningspark_b200.ops import heads
     dev = torch.device('cuda', 0)
     torch.manual_seed(0)
-    for B, H, O in ((32, 128, 1), (77, 128, 3), (5, 64, 1)):
+    for B, H, O in ((32, 128, 1), (77, 128, 3), (5, 64, 1), (300, 520, 1), (130, 1024, 2)):   # last two: multi-CTA path
         h = torch.randn(B, H, device=dev, requires_grad=True)
         w = (torch.randn(H, O, device=dev) * 0.1).requires_grad_(True)
         b = torch.randn(O, device=dev).requires_grad_(True)
@@ -94,7 +94,7 @@ def test_dense_mse_head_matches_autograd():
         torch.testing.assert_close(pred, (h @ w + b).detach(), rtol=1e-4, atol=1e-5)
         (3.0 * loss).backward()                      # non-unit seed must be honoured outside the step engine
         for g, r_ in zip((h.grad, w.grad, b.grad), gr):
-            torch.testing.assert_close(g, 3.0 * r_, rtol=1e-3, atol=1e-6)
+            torch.testing.assert_close(g, 3.0 * r_, rtol=1e-3, atol=5e-6)
         torch.testing.assert_close(heads.dense_linear(h.detach(), w.detach(), b.detach()), pred)
 
 
@@ -157,7 +157,7 @@ def test_stacked_big_lstm_direct_step_matches_autograd_reference():
     from distributeddeeplearningspark_b200.trainers import mean_squared_error
     dev = torch.device('cuda', 0)
     torch.manual_seed(0)
-    B, T = 96, 7
+    B, T = 200, 7            # two batch tiles (one ragged), 4-CTA clusters in BPTT
     m = ddls.models.stacked_lstm(units=256, len_seq=T, num_layers=2, seed=5).to(dev)
     x = torch.rand(B, T, 1, device=dev); y = torch.rand(B, 1, device=dev)
     h = x
