@@ -2,8 +2,9 @@
 //
 //   warp 0   : TMA producer (one thread): box loads of the A/B K-blocks into a 4- or 6-deep ring
 //   warp 1   : MMA issuer (one thread) + TMEM owner; accumulators are double-buffered in TMEM (2 x BN columns)
-//   warps 2-5: epilogue — tcgen05.ld of a finished accumulator, bias / ReLU / cast / accumulate, 16-byte stores —
-//              overlapped with the next tile's MMAs
+//   warps 2-9: epilogue (two warps per TMEM lane quadrant, half of the columns each) — tcgen05.ld of a finished
+//              accumulator, bias (staged once per tile in shared memory) / ReLU / cast / accumulate, 16-byte
+//              stores — overlapped with the next tile's MMAs
 // Tiles are 128 x BN (BN = 256 when N >= 256), visited n-fastest by a static persistent schedule so the CTAs
 // running at the same time share A tiles in L2.  Used for the big GEMMs of the scaled stacked LSTM (hoisted input
 // projection, dX, the K = B·T weight gradients) where the cp.async kernel of umma_gemm.cu reached 13% of peak.
@@ -21,7 +22,7 @@ struct TmaGemmParams {
   int tiles_m, tiles_n;
 };
 
-constexpr int TG_THREADS = 192;
+constexpr int TG_THREADS = 320;
 
 template <int BN, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(TG_THREADS, 1)
@@ -32,10 +33,11 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant__ 
   uint8_t* smem = align1024(smem_raw);
   __shared__ uint64_t full[S], empty[S], tfull[2], tempty[2];
   __shared__ uint32_t tmem_slot;
+  __shared__ __align__(16) float sbias[2][BN];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) {
     for (int s = 0; s < S; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 4); }
+    for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], 8); }
     mbar_fence_init();
     tma_prefetch_desc(&ta);
     tma_prefetch_desc(&tb);
@@ -82,17 +84,23 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant__ 
     }
   } else {
     const int quad = warp & 3;                               // TMEM lane quadrant this warp may read
+    const int half = (warp - 2) >> 2;                        // which half of the tile's columns
+    const int et = threadIdx.x - 64;                         // 0..255 among the epilogue threads
     const bool relu = p.flags & DDLS_GEMM_RELU, has_bias = (p.flags & DDLS_GEMM_BIAS) && p.bias != nullptr;
     const bool out_bf16 = p.flags & DDLS_GEMM_OUT_BF16, accumulate = p.flags & DDLS_GEMM_ACCUMULATE;
     int lt = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
       const int m0 = (tile / p.tiles_n) * Pipe::BM, n0 = (tile % p.tiles_n) * BN;
       const int acc = lt & 1, aph = (lt >> 1) & 1;
+      if (has_bias) {                                        // sbias[acc] was last read two tiles ago
+        if (et < BN) sbias[acc][et] = (n0 + et < p.N) ? __ldg(p.bias + n0 + et) : 0.f;
+        named_bar_sync(1, 256);
+      }
       mbar_wait(&tfull[acc], aph);
       tc_fence_after();
       const int row = m0 + quad * 32 + lane;
 #pragma unroll 1
-      for (int c = 0; c < BN; c += 32) {
+      for (int c = half * (BN / 2); c < (half + 1) * (BN / 2); c += 32) {
         uint32_t v[32];
         tmem_ld32(tmem + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN + c, v);
         tmem_ld_wait();
@@ -103,7 +111,10 @@ tma_gemm_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant__ 
           for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
           if (has_bias) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j) if (col + j < p.N) f[j] += __ldg(p.bias + col + j);
+            for (int j = 0; j < 32; j += 4) {
+              const float4 bq = *reinterpret_cast<const float4*>(&sbias[acc][c + j]);
+              f[j] += bq.x; f[j + 1] += bq.y; f[j + 2] += bq.z; f[j + 3] += bq.w;
+            }
           }
           if (relu) {
 #pragma unroll

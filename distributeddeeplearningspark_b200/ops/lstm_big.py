@@ -14,11 +14,12 @@ N.register('ddls_lstm_big_perm_cast', [P, P, I, I, P])
 N.register('ddls_lstm_big_perm_vec', [P, P, I, P])
 N.register('ddls_lstm_big_unperm', [P, P, I, I, I, P])
 N.register('ddls_lstm_big_colsum', [P, P, P, P, I, I, P])
-N.register('ddls_lstm_big_step_fwd', [P, P, P, P, I, P, P, P, P, P, P, P, I, I, P])
 N.register('ddls_lstm_big_zx1', [P, P, P, P, I, I, I, P])
 N.register('ddls_lstm_big_step_fwd2', [P, P, P, P, P, P, I, I, I, I, P])
+N.register('ddls_lstm_big_seq_tiles_per_launch', [I, I])
+N.register('ddls_lstm_big_seq_fwd', [P, P, P, P, P, P, P, I, I, I, P])
+N.register('ddls_lstm_big_seq_bwd', [P, P, P, P, P, P, P, I, I, I, P])
 N.register('ddls_lstm_big_step_bwd2', [P, P, P, P, P, P, P, I, I, I, I, P])
-N.register('ddls_lstm_big_step_bwd', [P, P, P, P, P, P, P, P, P, I, I, I, I, P])
 
 
 class StackedLSTMBuffers:
@@ -43,6 +44,15 @@ class StackedLSTMBuffers:
         self.h_last = torch.empty((B, self.H[-1]), dtype=f32, device=dev)
         self.gtmp = torch.empty((max(self.H), 4 * max(self.H)), dtype=f32, device=dev)   # permuted weight-gradient staging
         self.xw = torch.empty(T * B, dtype=f32, device=dev)
+        self.sync = torch.zeros(32 * max(4, (B + 127) // 128), dtype=torch.int32, device=dev)   # step-barrier counters
+
+
+def use_seq(h: int, backward: bool) -> bool:
+    """Whole-sequence persistent kernels unless DDLS_LSTM_BIG_SEQ=0 or the layer is too wide for one wave of CTAs."""
+    import os
+    if os.environ.get('DDLS_LSTM_BIG_SEQ', '1') == '0':
+        return False
+    return int(N.lib().ddls_lstm_big_seq_tiles_per_launch(h, int(backward))) >= 1
 
 
 def supported(layers, x: torch.Tensor) -> bool:
@@ -80,6 +90,11 @@ def forward(layers, bufs: StackedLSTMBuffers, x2: torch.Tensor, st: int, save: b
             gemm_bf16(bufs.hs[i - 1][1:].reshape(T * B, hin), bufs.w_perm[i], bias=bufs.b_perm[i], b_mn_major=True,
                       out=bufs.zx[i].view(T * B, 4 * h))
         hs, cs = bufs.hs[i], bufs.cs[i]
+        if use_seq(h, False):
+            N.call('ddls_lstm_big_seq_fwd', hs.data_ptr(), bufs.u_perm[i].data_ptr(), bufs.zx[i].data_ptr(), cs.data_ptr(),
+                   bufs.gates[i].data_ptr() if save else 0, bufs.h_last.data_ptr() if last_layer else 0,
+                   bufs.sync.data_ptr(), B, T, h, st)
+            continue
         for t in range(T):
             N.call('ddls_lstm_big_step_fwd2', hs.data_ptr(), bufs.u_perm[i].data_ptr(), bufs.zx[i].data_ptr(),
                    cs.data_ptr(), bufs.gates[i].data_ptr() if save else 0,
@@ -97,10 +112,14 @@ def backward(layers, bufs: StackedLSTMBuffers, x2: torch.Tensor, dh_last: torch.
         h = l.units
         top = i == L - 1
         dz, gates, cs = bufs.dz[i], bufs.gates[i], bufs.cs[i]
-        for t in reversed(range(T)):
+        for t in (reversed(range(T)) if not use_seq(h, True) else ()):
             N.call('ddls_lstm_big_step_bwd2', dz.data_ptr(), bufs.u_perm[i].data_ptr(),
                    bufs.dx[i + 1][t].data_ptr() if not top else 0, dh_last.data_ptr() if (top and t == T - 1) else 0,
                    gates.data_ptr(), cs.data_ptr(), bufs.dc[i].data_ptr(), B, T, h, t, st)
+        if use_seq(h, True):
+            N.call('ddls_lstm_big_seq_bwd', dz.data_ptr(), bufs.u_perm[i].data_ptr(),
+                   bufs.dx[i + 1].data_ptr() if not top else 0, dh_last.data_ptr() if top else 0, gates.data_ptr(),
+                   cs.data_ptr(), bufs.sync.data_ptr(), B, T, h, st)
         dz2 = dz.view(T * B, 4 * h)
         g = bufs.gtmp.view(-1)[:h * 4 * h].view(h, 4 * h)
         # recurrent kernel: dU = sum_t h_{t-1}^T dZ_t

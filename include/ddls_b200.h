@@ -114,14 +114,6 @@ int ddls_lstm_big_perm_vec(const float* src, float* dst, int H, void* stream);  
 int ddls_lstm_big_unperm(const float* src, float* dst, int rows, int H, int accumulate, void* stream);
 /* out[keras col] += sum_r w[r]*X[r][perm col] (w NULL: column sums); X bf16 [R,4H]; caller zeroes out. */
 int ddls_lstm_big_colsum(const void* X, const float* w, float* out_plain, float* out_weighted, int R, int H, void* stream);
-/* One time step: gates from h_prev·U (+ zx or x*w_ih) + bias; writes c_next, h_next (bf16), gates (bf16, perm). */
-int ddls_lstm_big_step_fwd(const void* h_prev, const void* u_perm, const void* zx, const float* x, int x_stride,
-                           const float* wih_perm, const float* bias_perm, const float* c_prev, float* c_next,
-                           void* h_next, float* h_out_f32, void* gates, int B, int H, void* stream);
-/* One BPTT step: dh = dz_next·U^T (+dout); writes dz (bf16, perm) for this step, updates dc in place. */
-int ddls_lstm_big_step_bwd(const void* dz_next, const void* u_perm, const void* dout_bf16, const float* dout_f32,
-                           const void* gates, const float* c_t, const float* c_prev, float* dc, void* dz, int B, int H,
-                           int use_acc, int first, void* stream);
 /* Second-generation step kernels on the TMA mainloop (csrc/lstm_big_tma.cu).  zx1: input projection of a first layer
  * with input dimension 1, zx[t][b][:] = x[b][t]*wih_perm + bias_perm (bf16).  step_fwd2 runs time step t of one layer
  * over whole-sequence buffers: hs [T+1][B][H] bf16 (hs[0] = initial state), cs [T+1][B][H] fp32, zx [T][B][4H] bf16
@@ -134,6 +126,17 @@ int ddls_lstm_big_step_fwd2(const void* hs, const void* u_perm, const void* zx, 
  * split over a 4-CTA cluster whose partial accumulators are exchanged through distributed shared memory. */
 int ddls_lstm_big_step_bwd2(void* dz, const void* u_perm, const void* dout_bf16, const float* dout_f32, const void* gates,
                             const float* cs, float* dc, int B, int T, int H, int t, void* stream);
+/* Whole-sequence persistent kernels (csrc/lstm_big_seq.cu): ONE cooperative launch per layer (per group of batch tiles
+ * that fits the SMs) runs all T steps with c / dc in registers and a per-batch-tile step barrier.  `sync` is a device
+ * array of at least 32*ceil(B/128) uint32 (scratch, zeroed by the call; one 128-byte line per batch tile).  dout: [T][B][H] bf16 gradient from the layer
+ * above (or NULL), dout_last: [B][H] fp32 gradient of the final hidden state (or NULL).
+ * ddls_lstm_big_seq_tiles_per_launch returns how many 128-row batch tiles one launch holds (0 = layer too wide: use the
+ * per-step kernels). */
+int ddls_lstm_big_seq_tiles_per_launch(int H, int backward);
+int ddls_lstm_big_seq_fwd(void* hs, const void* u_perm, const void* zx, float* cs, void* gates, float* h_out_f32, void* sync,
+                          int B, int T, int H, void* stream);
+int ddls_lstm_big_seq_bwd(void* dz, const void* u_perm, const void* dout, const float* dout_last, const void* gates,
+                          const float* cs, void* sync, int B, int T, int H, void* stream);
 
 
 /* ---- persistent GRU(128) recurrence, tcgen05 (Keras GRU reset_after=False, ddl_nyiso_aztk.py:201-203) ----

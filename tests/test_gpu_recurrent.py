@@ -150,8 +150,11 @@ def test_step_engine_trains_nyiso_models_with_cuda_graph(make):
     assert float((pred - ref).abs().max()) < 2e-2
 
 
-def test_stacked_big_lstm_direct_step_matches_autograd_reference():
-    """Large-hidden stacked LSTM (per-step fused GEMM kernels) vs torch autograd on the Keras equations."""
+@pytest.mark.parametrize('seq', ['1', '0'])
+def test_stacked_big_lstm_direct_step_matches_autograd_reference(seq, monkeypatch):
+    """Large-hidden stacked LSTM vs torch autograd on the Keras equations: whole-sequence persistent kernels
+    (seq=1, csrc/lstm_big_seq.cu) and the per-step kernels (seq=0, csrc/lstm_big_tma.cu)."""
+    monkeypatch.setenv('DDLS_LSTM_BIG_SEQ', seq)
     import distributeddeeplearningspark_b200 as ddls
     from distributeddeeplearningspark_b200.ops.fused import DirectStep
     from distributeddeeplearningspark_b200.trainers import mean_squared_error
