@@ -11,8 +11,9 @@
 //     -> TMA load of the consumer.
 // Forward roles: warp 0 weight producer, warp 1 MMA issuer, warps 2-9 epilogue, warp 10 h/zx producer.  The epilogue
 // stores h_t first, fences and posts its arrival, and only then writes the BPTT stash (c_t, gates).
-// Backward: K = 4H split over a 4-CTA cluster with the DSMEM exchange of lstm_big_bwd2_kernel; warps 2-9 run the
-// gate-derivative phase, warp 10 is the dZ producer.
+// Backward: K = 4H split over a 4-CTA cluster; partial accumulators are exchanged with bulk DSMEM copies that
+// complete on the receiver's mbarrier (no per-step cluster barrier); warps 2-9 run the gate-derivative phase,
+// warp 10 is the dZ producer.
 // (Keras LSTM semantics: /root/reference/ddl_nyiso_aztk.py:249-251.)
 #include <cstdio>
 #include <cstdlib>
@@ -320,7 +321,7 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = align1024(smem_raw);
   float* recv = reinterpret_cast<float*>(smem + S * Pipe::STAGE_BYTES);     // [slot 4][row 32][SB_RECV_LD]
-  __shared__ uint64_t full[S], empty[S], tfull, tempty;
+  __shared__ uint64_t full[S], empty[S], tfull, tempty, recv_full, stage_free;
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m0 = (p.m_tile0 + blockIdx.x) * 128, n0 = blockIdx.y * 128;
@@ -332,6 +333,8 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
     for (int s = 0; s < S; ++s) { mbar_init(&full[s], 2); mbar_init(&empty[s], 1); }
     mbar_init(&tfull, 1);
     mbar_init(&tempty, 8);
+    mbar_init(&recv_full, 1);
+    mbar_init(&stage_free, 1);
     mbar_fence_init();
     tma_prefetch_desc(&tdz); tma_prefetch_desc(&tu);
   }
@@ -359,6 +362,7 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
     const int t = T - 1 - i;
     if (warp == 0) {
       if (lane == 0 && i > 0) {
+        if (i >= 2) mbar_wait(&stage_free, (i - 2) & 1);     // last step's staging copies have left the ring
         for (int kb = 0; kb < kblocks; ++kb) {
           const int it = (i - 1) * kblocks + kb, s = it % S, ph = (it / S) & 1;
           mbar_wait(&empty[s], ph ^ 1);
@@ -369,6 +373,7 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
     } else if (warp == 10) {
       if (lane == 0 && i > 0) {
         wait_counter(counter, group * (uint32_t)i, i);
+        if (i >= 2) mbar_wait(&stage_free, (i - 2) & 1);
         stamp(p.trace, i, 0);
         for (int kb = 0; kb < kblocks; ++kb) {
           const int it = (i - 1) * kblocks + kb, s = it % S, ph = (it / S) & 1;
@@ -393,14 +398,21 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
         stamp(p.trace, i, 2);
       }
     }
-    // operands of the gate-derivative phase do not depend on the GEMM: fetch them behind the mainloop
-    uint2 pre_g[SB_ROWS][4], pre_do[SB_ROWS];
-    float4 pre_ct[SB_ROWS], pre_cp[SB_ROWS];
+    // Everything of the gate-derivative phase that does not depend on dh is fetched AND evaluated behind the mainloop:
+    //   d = dh*cA + dc;  dZ_o = dh*cO;  dZ_i = d*cI;  dZ_f = d*cF;  dZ_g = d*cG;  dc' = d*cD.
+    float cA[SB_ROWS][4], cO[SB_ROWS][4], cI[SB_ROWS][4], cF[SB_ROWS][4], cG[SB_ROWS][4], cD[SB_ROWS][4];
+    uint2 pre_do[SB_ROWS];
     if (warp >= 2 && warp < 10) {
+      uint2 pre_g[SB_ROWS][4];
+      float4 pre_ct[SB_ROWS], pre_cp[SB_ROWS];
 #pragma unroll
       for (int rr = 0; rr < SB_ROWS; ++rr) {
         const int b = m0 + 32 * (int)crank + e * SB_ROWS + rr;
         pre_do[rr] = make_uint2(0u, 0u);
+        pre_ct[rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+        pre_cp[rr] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+        for (int g = 0; g < 4; ++g) pre_g[rr][g] = make_uint2(0u, 0u);
         if (b < p.B) {
           const size_t o = (size_t)b * p.H + unit;
           const __nv_bfloat16* gs = p.gates + (size_t)t * bg + (size_t)b * G + pc;
@@ -411,33 +423,72 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
           if (p.dout != nullptr) pre_do[rr] = *reinterpret_cast<const uint2*>(p.dout + (size_t)t * bh + o);
         }
       }
-    }
-    if (i > 0) {
-      if (warp >= 2 && warp < 10) {
-        // phase 1: rows 32q..32q+31 of this CTA's partial go to CTA q, slot = my rank (two warps per quadrant,
-        // 64 columns each)
-        const int quad = warp & 3, chalf = (warp - 2) >> 2;
-        mbar_wait(&tfull, (i - 1) & 1);
-        tc_fence_after();
-        if (threadIdx.x == 64) stamp(p.trace, i, 3);
-        const uint32_t dst = seq_map_to_cta(smem_u32(recv + (crank * 32 + lane) * SB_RECV_LD), quad);
 #pragma unroll
-        for (int c = chalf * 64; c < chalf * 64 + 64; c += 16) {
-          uint32_t v[16];
-          tmem_ld16(tmem + (static_cast<uint32_t>(quad * 32) << 16) + c, v);
-          tmem_ld_wait();
+      for (int rr = 0; rr < SB_ROWS; ++rr) {
+        float gt[4][4];
 #pragma unroll
-          for (int j = 0; j < 16; j += 4)
-            seq_st_cluster_v4(dst + (c + j) * 4, __uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
-                              __uint_as_float(v[j + 3]));
+        for (int g = 0; g < 4; ++g) {
+          const uint2 q = pre_g[rr][g];
+          gt[g][0] = __uint_as_float(q.x << 16); gt[g][1] = __uint_as_float(q.x & 0xFFFF0000u);
+          gt[g][2] = __uint_as_float(q.y << 16); gt[g][3] = __uint_as_float(q.y & 0xFFFF0000u);
         }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty);
+        const float ct[4] = {pre_ct[rr].x, pre_ct[rr].y, pre_ct[rr].z, pre_ct[rr].w};
+        const float cpv[4] = {pre_cp[rr].x, pre_cp[rr].y, pre_cp[rr].z, pre_cp[rr].w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float gi = gt[0][j], gf = gt[1][j], gg = gt[2][j], go = gt[3][j];
+          const float tc = fast_tanh(ct[j]);
+          cA[rr][j] = go * (1.f - tc * tc);
+          cO[rr][j] = tc * ((go > 0.f && go < 1.f) ? 0.2f : 0.f);
+          cI[rr][j] = gg * ((gi > 0.f && gi < 1.f) ? 0.2f : 0.f);
+          cF[rr][j] = cpv[j] * ((gf > 0.f && gf < 1.f) ? 0.2f : 0.f);
+          cG[rr][j] = gi * (1.f - gg * gg);
+          cD[rr][j] = gf;
+        }
       }
+    }
+    if (i > 0 && warp >= 2 && warp < 10) {
+      // phase 1: the finished partial accumulator goes TMEM -> local staging (aliasing the operand ring, idle now)
+      // -> four bulk DSMEM copies: rows 32q..32q+31 to CTA q's receive slot [my rank], completing on CTA q's
+      // recv_full barrier.  No cluster barrier: the receiver waits on its own mbarrier.
+      const int quad = warp & 3, chalf = (warp - 2) >> 2;
+      float* stg = reinterpret_cast<float*>(smem);           // [row 128][SB_RECV_LD]
+      mbar_wait(&tfull, (i - 1) & 1);
+      tc_fence_after();
+      if (threadIdx.x == 64) stamp(p.trace, i, 3);
+      float* srow = stg + (quad * 32 + lane) * SB_RECV_LD;
+#pragma unroll
+      for (int c = chalf * 64; c < chalf * 64 + 64; c += 16) {
+        uint32_t v[16];
+        tmem_ld16(tmem + (static_cast<uint32_t>(quad * 32) << 16) + c, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 16; j += 4)
+          *reinterpret_cast<float4*>(srow + c + j) = make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]),
+                                                                 __uint_as_float(v[j + 2]), __uint_as_float(v[j + 3]));
+      }
+      tc_fence_before();
       __syncwarp();
-      seq_cluster_arrive();
-      seq_cluster_wait();                             // all four partials of my rows have landed
+      if (lane == 0) mbar_arrive(&tempty);
+      fence_proxy_async_smem();                              // staging was written by the generic proxy
+      named_bar_sync(2, 256);
+      if (warp == 2 && lane == 0) {
+        constexpr uint32_t SLOT_BYTES = 32 * SB_RECV_LD * 4;
+        mbar_expect_tx(&recv_full, 4 * SLOT_BYTES);          // four senders (one of them is this CTA)
+#pragma unroll
+        for (uint32_t q = 0; q < 4; ++q) {
+          const uint32_t dst = seq_map_to_cta(smem_u32(recv + crank * 32 * SB_RECV_LD), q);
+          const uint32_t bar = seq_map_to_cta(smem_u32(&recv_full), q);
+          asm volatile(
+              "cp.async.bulk.shared::cluster.shared::cta.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+              "r"(smem_u32(stg + q * 32 * SB_RECV_LD)), "r"(SLOT_BYTES), "r"(bar)
+              : "memory");
+        }
+        tma_bulk_commit();
+        tma_bulk_wait_read();                                // staging has been read: the operand ring may be refilled
+        mbar_arrive(&stage_free);
+      }
+      mbar_wait(&recv_full, (i - 1) & 1);                    // all four partials of my rows have landed
       if (threadIdx.x == 64) stamp(p.trace, i, 4);
     }
     if (warp >= 2 && warp < 10) {
@@ -464,27 +515,16 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
           const float4 q = *reinterpret_cast<const float4*>(p.dout_last + o);
           dh[0] += q.x; dh[1] += q.y; dh[2] += q.z; dh[3] += q.w;
         }
-        float gt[4][4];
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const uint2 q = pre_g[rr][g];
-          gt[g][0] = __uint_as_float(q.x << 16); gt[g][1] = __uint_as_float(q.x & 0xFFFF0000u);
-          gt[g][2] = __uint_as_float(q.y << 16); gt[g][3] = __uint_as_float(q.y & 0xFFFF0000u);
-        }
-        const float ct[4] = {pre_ct[rr].x, pre_ct[rr].y, pre_ct[rr].z, pre_ct[rr].w};
-        const float cpv[4] = {pre_cp[rr].x, pre_cp[rr].y, pre_cp[rr].z, pre_cp[rr].w};
         float dcv[4] = {dc[rr].x, dc[rr].y, dc[rr].z, dc[rr].w};
         float zi[4], zf[4], zg[4], zo[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float gi = gt[0][j], gf = gt[1][j], gg = gt[2][j], go = gt[3][j];
-          const float tc = fast_tanh(ct[j]);
-          const float d = fmaf(dh[j] * go, 1.f - tc * tc, dcv[j]);
-          zo[j] = dh[j] * tc * ((go > 0.f && go < 1.f) ? 0.2f : 0.f);
-          zi[j] = d * gg * ((gi > 0.f && gi < 1.f) ? 0.2f : 0.f);
-          zf[j] = d * cpv[j] * ((gf > 0.f && gf < 1.f) ? 0.2f : 0.f);
-          zg[j] = d * gi * (1.f - gg * gg);
-          dcv[j] = d * gf;
+          const float d = fmaf(dh[j], cA[rr][j], dcv[j]);
+          zo[j] = dh[j] * cO[rr][j];
+          zi[j] = d * cI[rr][j];
+          zf[j] = d * cF[rr][j];
+          zg[j] = d * cG[rr][j];
+          dcv[j] = d * cD[rr][j];
         }
         dc[rr] = make_float4(dcv[0], dcv[1], dcv[2], dcv[3]);
         __nv_bfloat16* zd = p.dz + (size_t)t * bg + (size_t)b * G + pc;

@@ -68,9 +68,29 @@ struct TmaPipe {
     }
   }
 
+  // Separate A / B rings (the operands of one K-block need not sit next to each other).
+  static DDLS_DEVINL void load_a_at(uint32_t a, uint64_t* full, const CUtensorMap* ta, int m0, int k0, int z) {
+    if constexpr (A_MN) {
+#pragma unroll
+      for (int j = 0; j < BM / 64; ++j) tma_load_3d(a + j * 8192, ta, full, m0 + j * 64, k0, z);
+    } else {
+      tma_load_3d(a, ta, full, k0, m0, z);
+    }
+  }
+  static DDLS_DEVINL void load_b_at(uint32_t b, uint64_t* full, const CUtensorMap* tb, int n0, int k0, int z) {
+    if constexpr (B_MN) {
+#pragma unroll
+      for (int j = 0; j < BN / 64; ++j) tma_load_3d(b + j * 8192, tb, full, n0 + j * 64, k0, z);
+    } else {
+      tma_load_3d(b, tb, full, k0, n0, z);
+    }
+  }
+
   // --- MMA issuer (one thread): the four K=16 MMAs of one stage ---
   static DDLS_DEVINL void mma_stage(const uint8_t* stage, uint32_t tmem_d, bool first_block) {
-    const uint32_t a = smem_u32(stage), b = a + A_BYTES;
+    mma_at(smem_u32(stage), smem_u32(stage) + A_BYTES, tmem_d, first_block);
+  }
+  static DDLS_DEVINL void mma_at(uint32_t a, uint32_t b, uint32_t tmem_d, bool first_block) {
 #pragma unroll
     for (int k16 = 0; k16 < BK / 16; ++k16) {
       const uint32_t a_lo = A_MN ? umma_desc_lo(a + k16 * 2048, 8192) : umma_desc_lo(a + k16 * 32, 16);
