@@ -71,7 +71,7 @@ def main():
     args = ap.parse_args()
     import distributeddeeplearningspark_b200 as ddls
     from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, PeerMemoryComm
-    os.environ.setdefault('DDLS_HEAP_MB', str(max(768, 20 * args.max_mb)))
+    os.environ.setdefault('DDLS_HEAP_MB', str(768 + 44 * args.max_mb))   # buffer + one-shot staging (2 x N x message) at N = 8
     ddls.init()
     comm = ddls.runtime.communicator()
     assert isinstance(comm, PeerMemoryComm), f'peer-memory communicator unavailable: {type(comm).__name__}'
