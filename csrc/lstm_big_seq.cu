@@ -27,6 +27,7 @@ DDLS_DEVINL void fence_proxy_async_all() { asm volatile("fence.proxy.async;" :::
 DDLS_DEVINL void red_release_gpu_add(uint32_t* p, uint32_t v) {
   asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
+DDLS_DEVINL void fence_acq_rel_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 DDLS_DEVINL void red_relaxed_gpu_add(uint32_t* p, uint32_t v) {
   asm volatile("red.relaxed.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -246,7 +247,7 @@ lstm_big_seq_fwd_kernel(const __grid_constant__ CUtensorMap th, const __grid_con
                              pack_bf16x2(hv[8 * j + 4], hv[8 * j + 5]), pack_bf16x2(hv[8 * j + 6], hv[8 * j + 7]));
       }
       if (threadIdx.x == 64) stamp(p.trace, t, 5);    // h stores issued
-      __threadfence();
+      fence_acq_rel_gpu();                            // this thread's stores are visible at gpu scope
       named_bar_sync(1, 256);
       if (warp == 2 && lane == 0) {
         stamp(p.trace, t, 6);                         // fences done
@@ -535,7 +536,7 @@ lstm_big_seq_bwd_kernel(const __grid_constant__ CUtensorMap tdz, const __grid_co
       }
       // publish dZ_t
       if (threadIdx.x == 64) stamp(p.trace, i, 5);
-      __threadfence();
+      fence_acq_rel_gpu();                            // this thread's stores are visible at gpu scope
       named_bar_sync(1, 256);
       if (warp == 2 && lane == 0) {
         stamp(p.trace, i, 6);
