@@ -30,6 +30,9 @@ class Row(dict):
             return list(self.values())[k]
         return dict.__getitem__(self, k)
 
+    def asDict(self) -> dict:
+        return dict(self)
+
 
 class _NaFunctions:
     def __init__(self, df: 'DataFrame'):

@@ -142,8 +142,12 @@ class Trainer:
     def __init__(self, keras_model: Sequential, loss: str, worker_optimizer: str = 'adam', metrics=('accuracy',),
                  features_col: str = 'features', label_col: str = 'label', batch_size: int = 32, num_epoch: int = 1,
                  num_workers: int = 1, backend=None, seed: Optional[int] = None, checkpoint: Optional[str] = None,
-                 optimizer_kwargs: Optional[dict] = None):
+                 optimizer_kwargs: Optional[dict] = None, master_port: int = 5000, parallelism_factor: int = 1):
         self.master_model = serialize_model(keras_model)
+        # dist-keras attributes kept for API parity: there is no socket server to bind (the center variable lives in
+        # symmetric / multicast GPU memory), and one rank owns one GPU, so these two are informational only.
+        self.master_port = int(master_port)
+        self.parallelism_factor = int(parallelism_factor)
         self.loss = loss
         self.worker_optimizer = worker_optimizer
         self.metrics = list(metrics)

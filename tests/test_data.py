@@ -124,3 +124,27 @@ def test_feeder_carry_over_counts_and_content():
     assert got[2] == [8.0, 9.0, 0.0, 1.0]                # batch straddles the epoch boundary
     f2 = DeviceFeeder({'x': x}, batch_size=4, device='cpu', num_epoch=2)
     assert len(list(f2)) == 4                            # per-epoch drop_last
+
+
+def test_distkeras_utils_surface():
+    """The ``distkeras.utils`` helpers of SURVEY.md §2.2 E11."""
+    import numpy as np
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200 import utils as U
+    from distributeddeeplearningspark_b200.data.frame import DataFrame, Row
+    r = U.new_dataframe_row(Row(a=1, b=2.0), 'c', [1, 2])
+    assert r.a == 1 and r.c == [1, 2] and r.asDict() == {'a': 1, 'b': 2.0, 'c': [1, 2]}
+    np.testing.assert_array_equal(U.to_one_hot_encoded_dense(2, 4), [0, 0, 1, 0])
+    df = DataFrame({'x': np.arange(10.0), 'y': np.arange(10) % 2})
+    assert U.precache(df, 2) == 10
+    sh = U.shuffle(df, seed=3)
+    assert sorted(np.asarray(sh['x']).tolist()) == list(range(10))
+    m = ddls.models.nyiso_gru(seed=1)
+    blob = U.serialize_keras_model(m)
+    m2 = U.deserialize_keras_model(blob)
+    for a, b in zip(m.get_weights(), m2.get_weights()):
+        np.testing.assert_array_equal(a, b)
+    assert U.history_executors_average([[1.0, 3.0, 5.0], [3.0, 5.0]]) == [2.0, 4.0]
+    assert U.history_executor([[1.0], [2.0]], 1) == [2.0]
+    t = ddls.trainers.ADAG(m, 'adagrad', 'mean_squared_error', num_workers=2)
+    assert t.master_port == 5000 and t.parallelism_factor == 1 and t.communication_window == 12
