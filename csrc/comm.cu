@@ -103,7 +103,9 @@ template <> struct WireOps<__nv_bfloat16> {
 
 struct ArParams {
   uint64_t in_off, out_off;   // fp32 [n] in each heap (may alias)
-  uint64_t stage_off;         // staging [2 parities][world][n] wire elements
+  uint64_t stage_off;         // staging: two parity halves, each [world][n] wire elements
+  uint64_t parity_bytes;      // size of one half — FIXED per staging region, not derived from n: a fast rank may already
+                              // push call k+1 (other parity, possibly larger n) while a slow one still reads call k
   uint64_t n;                 // elements, multiple of 4
   float scale;
 };
@@ -123,7 +125,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_kernel(CommCtx
   const uint64_t lo = blockIdx.x * per, hi = min(nvec, lo + per);
   const float4* in = reinterpret_cast<const float4*>(c.base[rank] + p.in_off);
   const uint64_t slot_vecs = nvec;                       // one slot = n wire elements
-  const uint64_t parity_vecs = slot_vecs * c.world;
+  const uint64_t parity_vecs = p.parity_bytes / sizeof(V);
   const uint64_t par = (e0 >> 1) & 1u;
   // push my slice to every peer's staging slot [parity][rank]
 #pragma unroll 4
@@ -162,6 +164,93 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_kernel(CommCtx
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// one-shot, "flag-in-data" variant for small messages (<= 256 KB by default): every 8-byte packet carries 4 bytes of
+// payload and the epoch number, so there is NO separate flag round and NO system-scope fence — a receiver simply
+// polls each packet until its flag equals the current epoch (8-byte stores are single-copy atomic over NVLink).
+// Costs 2x the wire bytes, removes one NVLink round trip (the release fence) from the critical path.
+// Staging: its own zero-initialised region, [2 parities][world][n] packets.
+// ---------------------------------------------------------------------------------------------------------
+DDLS_DEVINL void st_volatile_v4(uint4* p, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.volatile.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+DDLS_DEVINL uint4 ld_volatile_v4(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+DDLS_DEVINL uint4 ll_wait(const CommCtx& c, const uint4* p, uint32_t epoch, int rank, int from) {
+  uint4 v = ld_volatile_v4(p);
+  if (v.y == epoch && v.w == epoch) return v;
+  const uint64_t t0 = globaltimer_ns();
+  uint32_t spins = 0;
+  for (;;) {
+    v = ld_volatile_v4(p);
+    if (v.y == epoch && v.w == epoch) return v;
+    if ((++spins & 1023u) == 0 && globaltimer_ns() - t0 > c.timeout_ns) {
+      printf("ddls comm (ll): rank %d timed out waiting for rank %d at epoch %u (saw %u/%u)\n", rank, from, epoch, v.y, v.w);
+      __trap();
+    }
+  }
+}
+
+template <typename Wire>
+__global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(CommCtx c, ArParams p) {
+  constexpr bool F32 = sizeof(Wire) == 4;
+  constexpr int Q = F32 ? 2 : 1;                          // 16-byte stores per 4 elements
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t e0 = read_epoch(c, rank);
+  const uint32_t epoch = e0 + 1;
+  const uint64_t nvec = p.n / 4;
+  const uint64_t slot_q = nvec * Q, parity_q = p.parity_bytes / 16;
+  const uint64_t par = (e0 >> 1) & 1u;
+  const float4* in = reinterpret_cast<const float4*>(c.base[rank] + p.in_off);
+  float4* out = reinterpret_cast<float4*>(c.base[rank] + p.out_off);
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  const uint64_t first = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  for (uint64_t i = first; i < nvec; i += stride) {
+    const float4 x = in[i];
+    uint32_t w[4];
+    if (F32) { w[0] = __float_as_uint(x.x); w[1] = __float_as_uint(x.y); w[2] = __float_as_uint(x.z); w[3] = __float_as_uint(x.w); }
+    else { w[0] = pack_bf16x2(x.x, x.y); w[1] = pack_bf16x2(x.z, x.w); w[2] = 0; w[3] = 0; }
+    for (int d = 1; d < c.world; ++d) {
+      const int r = (rank + d) % c.world;
+      uint4* dst = reinterpret_cast<uint4*>(c.base[r] + p.stage_off) + par * parity_q + (uint64_t)rank * slot_q + i * Q;
+      st_volatile_v4(dst, w[0], epoch, w[1], epoch);
+      if (F32) st_volatile_v4(dst + 1, w[2], epoch, w[3], epoch);
+    }
+  }
+  const uint4* stage = reinterpret_cast<const uint4*>(c.base[rank] + p.stage_off) + par * parity_q;
+  for (uint64_t i = first; i < nvec; i += stride) {
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const float4 mine = in[i];
+    for (int r = 0; r < c.world; ++r) {                   // fixed rank order => identical bits on every rank
+      float v[4];
+      if (r == rank) {
+        if (F32) { v[0] = mine.x; v[1] = mine.y; v[2] = mine.z; v[3] = mine.w; }
+        else {
+          const uint32_t a = pack_bf16x2(mine.x, mine.y), b = pack_bf16x2(mine.z, mine.w);
+          v[0] = __uint_as_float(a << 16); v[1] = __uint_as_float(a & 0xFFFF0000u);
+          v[2] = __uint_as_float(b << 16); v[3] = __uint_as_float(b & 0xFFFF0000u);
+        }
+      } else {
+        const uint4* src = stage + (uint64_t)r * slot_q + i * Q;
+        const uint4 a = ll_wait(c, src, epoch, rank, r);
+        if (F32) {
+          const uint4 b = ll_wait(c, src + 1, epoch, rank, r);
+          v[0] = __uint_as_float(a.x); v[1] = __uint_as_float(a.z); v[2] = __uint_as_float(b.x); v[3] = __uint_as_float(b.z);
+        } else {
+          v[0] = __uint_as_float(a.x << 16); v[1] = __uint_as_float(a.x & 0xFFFF0000u);
+          v[2] = __uint_as_float(a.z << 16); v[3] = __uint_as_float(a.z & 0xFFFF0000u);
+        }
+      }
+      acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3];
+    }
+    out[i] = make_float4(acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale);
+  }
+  advance_epoch(c, rank, e0 + 2);
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // two-shot: reduce-scatter by push -> reduce own slice -> all-gather by push.  out must be symmetric.
 // ---------------------------------------------------------------------------------------------------------
 template <typename Wire>
@@ -179,7 +268,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_twoshot_kernel(CommCtx
   const float4* in = reinterpret_cast<const float4*>(c.base[rank] + p.in_off);
   const uint64_t par = (e0 >> 1) & 1u;
   const uint64_t slot_vecs = nvec;
-  const uint64_t parity_vecs = slot_vecs * c.world;
+  const uint64_t parity_vecs = p.parity_bytes / sizeof(V);
   for (int d = 1; d < c.world; ++d) {
     const int r = (rank + d) % c.world;
     const uint64_t lo = blo + r * per_rank, hi = min(bhi, lo + per_rank);
@@ -391,7 +480,8 @@ static int pick_blocks(uint64_t n, int requested) {
 using namespace ddls;
 
 extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64_t out_off,
-                                   uint64_t stage_off, uint64_t n, float scale, int wire_bf16, int blocks, void* stream) {
+                                   uint64_t stage_off, uint64_t stage_bytes, uint64_t n, float scale, int wire_bf16,
+                                   int blocks, void* stream) {
   CommCtx c;
   if (make_ctx(d, &c)) return 1;
   if (n == 0) return 0;
@@ -399,13 +489,29 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
     set_last_error("ddls_comm_allreduce: n must be a multiple of 4 and offsets 16-byte aligned");
     return 1;
   }
-  ArParams p{in_off, out_off, stage_off, n, scale};
+  const uint64_t parity_bytes = (stage_bytes / 2) & ~static_cast<uint64_t>(15);
+  if (algo != DDLS_AR_NVLS) {
+    const uint64_t per_elem = (algo == DDLS_AR_ONESHOT_LL) ? (wire_bf16 ? 4 : 8) : (wire_bf16 ? 2 : 4);
+    if ((uint64_t)d->world * n * per_elem > parity_bytes) {
+      set_last_error("ddls_comm_allreduce: staging region of %llu bytes is too small for %llu elements x %d ranks",
+                     (unsigned long long)stage_bytes, (unsigned long long)n, d->world);
+      return 1;
+    }
+  }
+  ArParams p{in_off, out_off, stage_off, parity_bytes, n, scale};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nb = pick_blocks(n, blocks);
   switch (algo) {
     case DDLS_AR_ONESHOT:
       return wire_bf16 ? launch(d, allreduce_oneshot_kernel<__nv_bfloat16>, nb, COMM_THREADS, st, c, p)
                        : launch(d, allreduce_oneshot_kernel<float>, nb, COMM_THREADS, st, c, p);
+    case DDLS_AR_ONESHOT_LL: {
+      int lb = blocks > 0 ? blocks : (int)((n / 4 + COMM_THREADS - 1) / COMM_THREADS);     // one 16-byte vector per thread
+      if (lb > 64) lb = 64;
+      if (lb < 1) lb = 1;
+      return wire_bf16 ? launch(d, allreduce_oneshot_ll_kernel<__nv_bfloat16>, lb, COMM_THREADS, st, c, p)
+                       : launch(d, allreduce_oneshot_ll_kernel<float>, lb, COMM_THREADS, st, c, p);
+    }
     case DDLS_AR_TWOSHOT:
       return wire_bf16 ? launch(d, allreduce_twoshot_kernel<__nv_bfloat16>, nb, COMM_THREADS, st, c, p)
                        : launch(d, allreduce_twoshot_kernel<float>, nb, COMM_THREADS, st, c, p);

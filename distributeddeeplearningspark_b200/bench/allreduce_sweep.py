@@ -70,7 +70,7 @@ def main():
     ap.add_argument('--graph', action='store_true', help='also time inside a CUDA graph (8 calls per replay)')
     args = ap.parse_args()
     import distributeddeeplearningspark_b200 as ddls
-    from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, PeerMemoryComm
+    from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_ONESHOT_LL, AR_TWOSHOT, PeerMemoryComm
     os.environ.setdefault('DDLS_HEAP_MB', str(768 + 44 * args.max_mb))   # buffer + one-shot staging (2 x N x message) at N = 8
     ddls.init()
     comm = ddls.runtime.communicator()
@@ -89,11 +89,14 @@ def main():
         iters = 200 if nbytes <= (1 << 20) else (50 if nbytes <= (32 << 20) else 10)
         row = {'bytes': nbytes, 'nccl_us': _time(lambda: dist.all_reduce(tn), iters, dev)}
         algos = [('oneshot', AR_ONESHOT), ('twoshot', AR_TWOSHOT)] + ([('nvls', AR_NVLS)] if comm.mc_base else [])
+        if nbytes <= comm._ll_elems * 4:
+            algos.insert(0, ('ll', AR_ONESHOT_LL))
         for name, a in algos:
             if name == 'oneshot' and nbytes > (16 << 20):
                 continue
             us = _time(lambda: comm.allreduce_(t, ddls.Sum, algo=a), iters, dev)
-            link_bytes = {'oneshot': (n - 1) * nbytes, 'twoshot': 2 * (n - 1) / n * nbytes, 'nvls': nbytes}[name]
+            link_bytes = {'ll': 2 * (n - 1) * nbytes, 'oneshot': (n - 1) * nbytes, 'twoshot': 2 * (n - 1) / n * nbytes,
+                          'nvls': nbytes}[name]
             row[name + '_us'] = us
             if args.graph and nbytes <= (4 << 20):
                 row[name + '_graph_us'] = _time_graph(lambda: comm.allreduce_(t, ddls.Sum, algo=a), dev)

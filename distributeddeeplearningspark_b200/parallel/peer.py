@@ -41,7 +41,8 @@ FLAGS_OFF = 0
 SEQ_OFF = 2048
 ALIGN = 256
 
-AR_ONESHOT, AR_TWOSHOT, AR_NVLS = 0, 1, 2
+AR_ONESHOT, AR_TWOSHOT, AR_NVLS, AR_ONESHOT_LL = 0, 1, 2, 3
+LL_MAX_BYTES_DEFAULT = 256 << 10     # flag-in-data one-shot up to this message size
 
 
 class CommDesc(ctypes.Structure):
@@ -61,7 +62,7 @@ N.register('ddls_mc_create', [I, N.c_size_t, ctypes.POINTER(ctypes.c_ulonglong),
 N.register('ddls_mc_import', [I, ctypes.POINTER(ctypes.c_ulonglong)])
 N.register('ddls_mc_add_device', [ctypes.c_ulonglong, I])
 N.register('ddls_mc_bind_and_map', [ctypes.c_ulonglong, ctypes.c_ulonglong, N.c_size_t, I, ctypes.POINTER(P)])
-N.register('ddls_comm_allreduce', [DP, I, U64, U64, U64, U64, F, I, I, P])
+N.register('ddls_comm_allreduce', [DP, I, U64, U64, U64, U64, U64, F, I, I, P])
 N.register('ddls_comm_broadcast', [DP, U64, U64, I, I, I, P])
 N.register('ddls_comm_allgather', [DP, U64, U64, U64, I, P])
 N.register('ddls_comm_barrier', [DP, P])
@@ -90,6 +91,15 @@ class _HeapBase:
         self._top = CONTROL_BYTES
         self._stage_off = 0
         self._stage_elems = 0
+        self._stage_bytes = 0
+        self._ll_off = self._ll_elems = self._ll_bytes = 0
+
+    def _init_ll_stage(self, world: int) -> None:
+        """Reserve the flag-in-data staging region.  The caller zeroes it (and, across processes, synchronises)
+        BEFORE any collective can run: a packet's flag word must never hold anything but an epoch number."""
+        self._ll_elems = env_int('DDLS_LL_MAX_BYTES', LL_MAX_BYTES_DEFAULT) // 4
+        self._ll_bytes = 2 * world * self._ll_elems * 8
+        self._ll_off = self._alloc_off(self._ll_bytes)
 
     def _alloc_off(self, nbytes: int) -> int:
         off = (self._top + ALIGN - 1) // ALIGN * ALIGN
@@ -99,19 +109,28 @@ class _HeapBase:
         self._top = off + nbytes
         return off
 
-    def _ensure_stage(self, n_elems: int, world: int) -> int:
-        """Staging region for push collectives: [2 parities][world][n] fp32 slots."""
+    def _ensure_stage(self, n_elems: int, world: int, algo: int = AR_ONESHOT):
+        """(offset, bytes) of the staging region for push collectives: two fixed parity halves of [world][n] slots.
+        The flag-in-data algorithm has its own zero-initialised region (8 bytes per element), never shared with
+        the others, so a packet's flag word can only ever hold an epoch number."""
+        if algo == AR_ONESHOT_LL:
+            if n_elems > self._ll_elems:
+                raise ValueError(f'flag-in-data allreduce is limited to {self._ll_elems * 4} bytes (DDLS_LL_MAX_BYTES)')
+            return self._ll_off, self._ll_bytes
         if n_elems > self._stage_elems:
             want = max(n_elems, 1 << 20)
-            self._stage_off = self._alloc_off(2 * world * want * 4)
+            self._stage_bytes = 2 * world * want * 4
+            self._stage_off = self._alloc_off(self._stage_bytes)
             self._stage_elems = want
-        return self._stage_off
+        return self._stage_off, self._stage_bytes
 
     def select_algo(self, nbytes: int, symmetric_out: bool, have_mc: bool) -> int:
         one_max = env_int('DDLS_ONESHOT_MAX_BYTES', 1 << 20)
         forced = env_str('DDLS_ALLREDUCE_ALGO', '')
         if forced:
-            return {'oneshot': AR_ONESHOT, 'twoshot': AR_TWOSHOT, 'nvls': AR_NVLS}[forced]
+            return {'oneshot': AR_ONESHOT, 'twoshot': AR_TWOSHOT, 'nvls': AR_NVLS, 'll': AR_ONESHOT_LL}[forced]
+        if nbytes <= self._ll_elems * 4:
+            return AR_ONESHOT_LL
         if nbytes <= one_max or not symmetric_out:
             return AR_ONESHOT
         return AR_NVLS if have_mc else AR_TWOSHOT
@@ -176,6 +195,9 @@ class PeerMemoryComm(Communicator, _HeapBase):
         self.desc.flags_off, self.desc.seq_off = FLAGS_OFF, SEQ_OFF
         self._scratch_off = self._alloc_off(64 << 20)   # staging for tensors that are not heap-resident
         self._scratch_bytes = 64 << 20
+        self._init_ll_stage(size)
+        self._heap_u8[self._ll_off:self._ll_off + self._ll_bytes].zero_()
+        torch.cuda.synchronize(device)
         dist.barrier(device_ids=[self.dev_index])
 
     # ------------------------------------------------------------------ fd exchange
@@ -270,9 +292,9 @@ class PeerMemoryComm(Communicator, _HeapBase):
         off = self.offset_of(t) if (n % 4 == 0 and t.is_contiguous()) else None
         if off is not None and off % 16 == 0:
             a = algo if algo is not None else self.select_algo(n * 4, True, bool(self.mc_base))
-            stage = self._ensure_stage(n, self.size) if a != AR_NVLS else 0
-            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, n, scale, int(wire_bf16), 0,
-                   self._stream())
+            stage, sbytes = self._ensure_stage(n, self.size, a) if a != AR_NVLS else (0, 0)
+            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, sbytes, n, scale, int(wire_bf16),
+                   0, self._stream())
             torch.autograd.graph.increment_version(t)     # raw-pointer kernels bypass torch's version counter
             return t
         # not heap-resident: bounce through the scratch region (chunked)
@@ -286,9 +308,9 @@ class PeerMemoryComm(Communicator, _HeapBase):
             if m4 > m:
                 scratch[m:m4].zero_()
             a = algo if algo is not None else self.select_algo(m4 * 4, True, bool(self.mc_base))
-            stage = self._ensure_stage(m4, self.size) if a != AR_NVLS else 0
-            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, self._scratch_off, self._scratch_off, stage, m4,
-                   scale, int(wire_bf16), 0, self._stream())
+            stage, sbytes = self._ensure_stage(m4, self.size, a) if a != AR_NVLS else (0, 0)
+            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, self._scratch_off, self._scratch_off, stage, sbytes,
+                   m4, scale, int(wire_bf16), 0, self._stream())
             flat[lo:lo + m].copy_(scratch[:m])
         return t
 
@@ -367,6 +389,7 @@ class EmulatedPeerGroup(_HeapBase):
         self.desc.world, self.desc.rank, self.desc.emulate = world, 0, 1
         self.desc.timeout_ms = timeout_ms
         self.desc.flags_off, self.desc.seq_off = FLAGS_OFF, SEQ_OFF
+        self._init_ll_stage(world)                       # heaps are torch.zeros: already clean
         N.lib()
 
     def alloc(self, numel: int, dtype=torch.float32) -> Tuple[int, List[torch.Tensor]]:
@@ -378,9 +401,9 @@ class EmulatedPeerGroup(_HeapBase):
         return torch.cuda.current_stream(self.device).cuda_stream
 
     def allreduce(self, off: int, n: int, algo: int, scale: float = 1.0, wire_bf16: bool = False, blocks: int = 0):
-        stage = self._ensure_stage(n, self.world)
-        N.call('ddls_comm_allreduce', ctypes.byref(self.desc), algo, off, off, stage, n, scale, int(wire_bf16), blocks,
-               self._stream())
+        stage, sbytes = self._ensure_stage(n, self.world, algo)
+        N.call('ddls_comm_allreduce', ctypes.byref(self.desc), algo, off, off, stage, sbytes, n, scale, int(wire_bf16),
+               blocks, self._stream())
 
     def broadcast(self, off: int, nbytes: int, root: int, blocks: int = 0):
         N.call('ddls_comm_broadcast', ctypes.byref(self.desc), off, nbytes, root, 0, blocks, self._stream())

@@ -222,11 +222,14 @@ typedef struct {
   uint64_t flags_off;
   uint64_t seq_off;
 } DdlsCommDesc;
-enum { DDLS_AR_ONESHOT = 0, DDLS_AR_TWOSHOT = 1, DDLS_AR_NVLS = 2 };
-/* out = scale * sum_ranks(in) over fp32 [n].  stage_off: 2*world*n wire elements of scratch in each heap.
- * wire_bf16: values cross NVLink as bf16 (fp32 accumulate).  blocks = 0 picks by size. */
+enum { DDLS_AR_ONESHOT = 0, DDLS_AR_TWOSHOT = 1, DDLS_AR_NVLS = 2, DDLS_AR_ONESHOT_LL = 3 };
+/* DDLS_AR_ONESHOT_LL: flag-in-data packets (8 bytes = 4 payload + epoch), no flag round and no system fence; its staging
+ * region must be its own, zero-initialised, 2 * world * n * 8 bytes (fp32 wire) and never used by the other algorithms. */
+/* out = scale * sum_ranks(in) over fp32 [n].  stage_off / stage_bytes: a scratch region in each heap, used as two
+ * parity halves of stage_bytes/2 (each must hold world*n wire elements; the halves are fixed so that calls of different
+ * sizes never overlap).  wire_bf16: values cross NVLink as bf16 (fp32 accumulate).  blocks = 0 picks by size. */
 int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64_t out_off, uint64_t stage_off,
-                        uint64_t n, float scale, int wire_bf16, int blocks, void* stream);
+                        uint64_t stage_bytes, uint64_t n, float scale, int wire_bf16, int blocks, void* stream);
 int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast, int blocks,
                         void* stream);
 int ddls_comm_allgather(const DdlsCommDesc* d, uint64_t in_off, uint64_t out_off, uint64_t chunk_bytes, int blocks,

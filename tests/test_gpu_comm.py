@@ -5,7 +5,7 @@ import torch
 
 pytestmark = pytest.mark.gpu
 
-from distributeddeeplearningspark_b200.parallel.peer import AR_ONESHOT, AR_TWOSHOT, EmulatedPeerGroup
+from distributeddeeplearningspark_b200.parallel.peer import AR_ONESHOT, AR_ONESHOT_LL, AR_TWOSHOT, EmulatedPeerGroup
 
 
 @pytest.mark.parametrize('world', [2, 4, 8])
@@ -13,7 +13,7 @@ from distributeddeeplearningspark_b200.parallel.peer import AR_ONESHOT, AR_TWOSH
 @pytest.mark.parametrize('n,blocks', [(4, 1), (1000, 1), (66688, 0), (1048576 + 12, 0), (300000, 7)])
 def test_emulated_allreduce_matches_fp64_sum(world, algo, n, blocks):
     dev = torch.device('cuda', 0)
-    g = EmulatedPeerGroup(world, dev, heap_bytes=(2 * world + 2) * max(n, 1 << 20) * 4 + (1 << 20))
+    g = EmulatedPeerGroup(world, dev, heap_bytes=(2 * world + 2) * max(n, 1 << 20) * 4 + (16 << 20))
     off, bufs = g.alloc(n)
     torch.manual_seed(n + world)
     src = [torch.randn(n, device=dev) for _ in range(world)]
@@ -26,6 +26,46 @@ def test_emulated_allreduce_matches_fp64_sum(world, algo, n, blocks):
         torch.testing.assert_close(bufs[r], ref, rtol=1e-5, atol=1e-6)
     for r in range(1, world):                       # rank-ordered summation => bit-identical replicas
         assert torch.equal(bufs[0], bufs[r])
+
+
+@pytest.mark.parametrize('world', [2, 8])
+@pytest.mark.parametrize('n,blocks', [(4, 1), (1000, 0), (65536, 0), (50000, 3)])
+@pytest.mark.parametrize('wire_bf16', [False, True])
+def test_emulated_flag_in_data_allreduce(world, n, blocks, wire_bf16):
+    """One-shot with 8-byte {payload, epoch} packets: no flag round, no system fence."""
+    dev = torch.device('cuda', 0)
+    g = EmulatedPeerGroup(world, dev)
+    off, bufs = g.alloc(n)
+    for it in range(6):                             # both parities, increasing epochs over the same slots
+        torch.manual_seed(n + world + it)
+        src = [torch.randn(n, device=dev) for _ in range(world)]
+        for b, s in zip(bufs, src):
+            b.copy_(s)
+        g.allreduce(off, n, AR_ONESHOT_LL, scale=0.5, wire_bf16=wire_bf16, blocks=blocks)
+        torch.cuda.synchronize()
+        wire = [s.bfloat16().float() if wire_bf16 else s for s in src]
+        ref = (torch.stack(wire).double().sum(0) * 0.5).float()
+        torch.testing.assert_close(bufs[world - 1], ref, rtol=1e-5, atol=1e-5)
+        for r in range(1, world):
+            assert torch.equal(bufs[0], bufs[r])
+
+
+def test_emulated_allreduce_mixed_sizes_keep_parity_halves_apart():
+    """A small call followed by a larger one must not share staging bytes (a fast rank may already push the second
+    while a slow one still reads the first): the parity halves are fixed, not derived from the message size."""
+    dev = torch.device('cuda', 0)
+    world = 4
+    g = EmulatedPeerGroup(world, dev)
+    offs = [g.alloc(n) for n in (1024, 300000, 4096, 200000)]
+    for it in range(20):
+        for (off, bufs), n in zip(offs, (1024, 300000, 4096, 200000)):
+            for r, b in enumerate(bufs):
+                b.fill_(float(r + 1 + it))
+            g.allreduce(off, n, AR_ONESHOT if it % 2 else AR_TWOSHOT, scale=1.0)
+        torch.cuda.synchronize()
+        want = float(sum(r + 1 + it for r in range(world)))
+        for off, bufs in offs:
+            assert float(bufs[0].min()) == want and float(bufs[world - 1].max()) == want
 
 
 def test_emulated_allreduce_bf16_wire_and_back_to_back_calls():
@@ -88,7 +128,7 @@ def test_emulated_broadcast_every_root_and_allgather(world):
 # --------------------------------------------------------------------------------------------------------
 def _multi_rank_checks():
     import distributeddeeplearningspark_b200 as ddls
-    from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_TWOSHOT, PeerMemoryComm
+    from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_ONESHOT_LL, AR_TWOSHOT, PeerMemoryComm
     ddls.init()
     r, n = ddls.rank(), ddls.size()
     comm = ddls.runtime.communicator()
@@ -98,7 +138,7 @@ def _multi_rank_checks():
     algos = [AR_ONESHOT, AR_TWOSHOT] + ([AR_NVLS] if comm.mc_base else [])
     for numel in (4, 66688, 1048576, 12 * 1048576):
         t = comm.alloc(numel)
-        for algo in algos:
+        for algo in algos + ([AR_ONESHOT_LL] if numel * 4 <= 256 * 1024 else []):
             torch.manual_seed(100 + r)
             t.copy_(torch.randn(numel, device=dev))
             mine = t.clone()
