@@ -52,6 +52,7 @@ def parse():
     ap.add_argument('--batch-per-rank', type=int, default=None)
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-dataset', action='store_true', help='feed step(x, y) from the device pool instead of the in-graph gather')
     ap.add_argument('--comm', default=None, help='peer (default on GPUs) | nccl')
     return ap.parse_args()
 
@@ -137,15 +138,24 @@ def main():
     pool_n = max(8, min(4096, (160 << 20) // bytes_per_batch + 1))
     host = make_batches(args.model, B, pool_n, seed=rank, device=dev)
     from distributeddeeplearningspark_b200.ops.preprocess import mnist_preprocess
-    pool_x, pool_y = [], []
     if is_mnist:
         px = host['pixels'].to(dev); lab = host['labels'].to(dev)
         x_all, y_all = mnist_preprocess(px, lab)
-        pool_x = list(x_all.split(B)); pool_y = list(y_all.split(B))
         del px
     else:
-        pool_x = list(host['x'].to(dev).split(B)); pool_y = list(host['y'].to(dev).split(B))
-    pool_bytes = sum(t.numel() * t.element_size() for t in pool_x + pool_y)
+        x_all, y_all = host['x'].to(dev), host['y'].to(dev)
+    x_all, y_all = x_all[:pool_n * B].contiguous(), y_all[:pool_n * B].contiguous()
+    pool_bytes = x_all.numel() * x_all.element_size() + y_all.numel() * y_all.element_size()
+    # The training set stays on the device (the reference caches its DataFrame partitions in executor memory); every
+    # step gathers its minibatch from this pool INSIDE the captured graph (device-side cursor), so consecutive steps
+    # read different, L2-cold inputs and a step is one graph launch.
+    use_dataset = engine.use_cuda_graph and not args.no_dataset
+    if use_dataset:
+        engine.attach_dataset(x_all, y_all, B)
+    pool_x = list(x_all.split(B)); pool_y = list(y_all.split(B))
+
+    def train_step(i):
+        return engine.step_dataset() if use_dataset else engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
 
     def sync_all():
         torch.cuda.synchronize(dev)
@@ -154,14 +164,12 @@ def main():
             torch.cuda.synchronize(dev)
 
     # ---- launches per step (counted on one eager step; a graph replays exactly these) --------------------
-    for i in range(W):
-        engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
+    for i in range(max(W, 5)):                      # includes the three eager warm-ups and the graph capture
+        train_step(i)
     sync_all()
-    if engine.use_cuda_graph and engine._graph is None:
-        for i in range(4):
-            engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
-        sync_all()
     c0 = _native.launch_count()
+    if use_dataset:
+        engine._gather()
     engine._eager_step(pool_x[0], pool_y[0])
     per_step_launches = _native.launch_count() - c0
     sync_all()
@@ -172,7 +180,7 @@ def main():
     sync_all()
     ev0.record()
     for i in range(K):
-        engine.step(pool_x[i % pool_n], pool_y[i % pool_n])
+        train_step(i)
     ev1.record()
     sync_all()
     ms = ev0.elapsed_time(ev1)
@@ -192,14 +200,12 @@ def main():
             hl = host['labels'][:n_host * B].reshape(n_host, B).pin_memory()
             d_px = torch.empty((B, 784), dtype=torch.uint8, device=dev)
             d_lab = torch.empty((B,), dtype=torch.int64, device=dev)
-            d_x = torch.empty((B, 28, 28, 1), dtype=torch.float32, device=dev)
-            d_y = torch.empty((B, 10), dtype=torch.float32, device=dev)
+            d_x, d_y = engine.input_buffers(pool_x[0], pool_y[0])   # preprocess writes the step's static inputs
             h2d = B * 784 + B * 8
         else:
             hx = host['x'][:n_host * B].reshape(n_host, B, md['seq'], 1).pin_memory()
             hy = host['y'][:n_host * B].reshape(n_host, B, 1).pin_memory()
-            d_x = torch.empty((B, md['seq'], 1), dtype=torch.float32, device=dev)
-            d_y = torch.empty((B, 1), dtype=torch.float32, device=dev)
+            d_x, d_y = engine.input_buffers(pool_x[0], pool_y[0])   # H2D lands in the step's static inputs
             h2d = B * (md['seq'] + 1) * 4
         loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
 
@@ -215,7 +221,7 @@ def main():
             torch.cuda.current_stream(dev).synchronize()
             return float(loss_host[0])
 
-        for i in range(W):
+        for i in range(max(W, 5)):                  # three eager warm-ups + capture of the (x, y) graph
             e2e_step(i)
         sync_all()
         t0 = time.perf_counter()
@@ -241,9 +247,12 @@ def main():
         'data': 'synthetic', 'impl': 'ours',
         'config': {'model': args.model, 'global_batch': B * size, 'per_rank_batch': B, 'seq_len': md['seq'],
                    'parallelism': f'dp{size}', 'optimizer': opt_name, 'loss': loss_name,
-                   'comm': type(comm).__name__, 'cuda_graph': bool(engine.use_cuda_graph and engine._graph is not None),
-                   'l2': f'inputs rotate through a {pool_bytes >> 20} MB device pool (> 126 MB L2)'
-                         if pool_bytes > (126 << 20) else f'{pool_bytes >> 20} MB input pool (smaller than L2)'},
+                   'comm': type(comm).__name__, 'cuda_graph': bool(engine.use_cuda_graph and (engine._graph is not None or
+                                                                 getattr(engine, '_ds_graph', None) is not None)),
+                   'l2': (f'inputs rotate through a {pool_bytes >> 20} MB device pool (> 126 MB L2)'
+                          if pool_bytes > (126 << 20) else f'{pool_bytes >> 20} MB input pool (smaller than L2)'),
+                   'input_feed': ('minibatch gathered inside the step graph from the device-resident pool '
+                                  '(device-side cursor)') if use_dataset else 'step(x, y) from the device pool'},
         'e2e': e2e, 'gpu_launches': int(per_step_launches * K), 'gpu_launches_per_step': int(per_step_launches),
         'clocks': clocks, 'final_loss': last_loss,
     }

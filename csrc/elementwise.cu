@@ -206,6 +206,65 @@ extern "C" int ddls_sgd_step(float* params, float* grads, int* step, size_t n, f
   return check_cuda(cudaGetLastError(), "sgd_kernel launch");
 }
 
+namespace ddls {
+// Minibatch gather from a device-resident dataset (the B200 form of "the partition is cached in executor memory",
+// /root/reference/ddl_mnist_aztk.py:156-161): rows perm[(k*B + r) mod N] of X and Y are copied into the step's static
+// input buffers, k being a DEVICE-side batch cursor that the last block advances — so the gather is one node of the
+// captured training-step graph and a replay needs no host-side input copy at all.  Rows are copied in 4-byte words
+// (16-byte vectors when the row size allows).
+template <typename VecT>
+__global__ void __launch_bounds__(EW_THREADS) gather_batch_kernel(const VecT* __restrict__ X, const VecT* __restrict__ Y,
+                                                                  VecT* __restrict__ x, VecT* __restrict__ y,
+                                                                  const int* __restrict__ perm, unsigned* cursor,
+                                                                  int B, long long N, int xw, int yw) {
+  const unsigned long long k = cursor[0];
+  const size_t total_x = (size_t)B * xw, total = total_x + (size_t)B * yw;
+  for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+    const bool is_x = i < total_x;
+    const size_t j = is_x ? i : i - total_x;
+    const int w = is_x ? xw : yw;
+    const int r = (int)(j / w), c = (int)(j - (size_t)r * w);
+    long long row = (long long)((k * (unsigned long long)B + r) % (unsigned long long)N);
+    if (perm != nullptr) row = perm[row];
+    if (is_x) x[j] = X[(size_t)row * xw + c]; else y[j] = Y[(size_t)row * yw + c];
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(cursor + 1, 1u) == gridDim.x - 1) { cursor[1] = 0; cursor[0] = (unsigned)(k + 1); __threadfence(); }
+  }
+}
+}  // namespace ddls
+
+extern "C" int ddls_gather_batch(const void* X, const void* Y, void* x, void* y, const int* perm, unsigned* cursor, int B,
+                                 long long N, long long row_x_bytes, long long row_y_bytes, void* stream) {
+  using namespace ddls;
+  if (B <= 0 || N <= 0) { set_last_error("ddls_gather_batch: empty batch or dataset"); return 1; }
+  if (row_x_bytes % 4 != 0 || row_y_bytes % 4 != 0 || row_x_bytes <= 0 || row_y_bytes <= 0) {
+    set_last_error("ddls_gather_batch: row sizes must be positive multiples of 4 bytes (got %lld, %lld)", row_x_bytes, row_y_bytes);
+    return 1;
+  }
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool v16 = row_x_bytes % 16 == 0 && row_y_bytes % 16 == 0 &&
+                   ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(Y) | reinterpret_cast<uintptr_t>(x) |
+                     reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+  if (v16) {
+    const int xw = (int)(row_x_bytes / 16), yw = (int)(row_y_bytes / 16);
+    int blocks = ew_grid((size_t)B * (xw + yw));
+    if (blocks > 64) blocks = 64;
+    gather_batch_kernel<uint4><<<blocks, EW_THREADS, 0, st>>>(static_cast<const uint4*>(X), static_cast<const uint4*>(Y),
+                                                               static_cast<uint4*>(x), static_cast<uint4*>(y), perm, cursor, B, N, xw, yw);
+  } else {
+    const int xw = (int)(row_x_bytes / 4), yw = (int)(row_y_bytes / 4);
+    int blocks = ew_grid((size_t)B * (xw + yw));
+    if (blocks > 64) blocks = 64;
+    gather_batch_kernel<uint32_t><<<blocks, EW_THREADS, 0, st>>>(static_cast<const uint32_t*>(X), static_cast<const uint32_t*>(Y),
+                                                                  static_cast<uint32_t*>(x), static_cast<uint32_t*>(y), perm, cursor, B, N, xw, yw);
+  }
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "gather_batch_kernel launch");
+}
+
 extern "C" int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* labels, float* x, float* onehot, int n,
                                      int npix, int classes, float o_min, float scale, float n_min, void* stream) {
   if (n <= 0) return 0;

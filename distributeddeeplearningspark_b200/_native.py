@@ -8,7 +8,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_size_t, c_uint, c_ulonglong, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_uint, c_ulonglong, c_void_p
 from typing import Optional
 
 _LIB: Optional[ctypes.CDLL] = None

@@ -38,7 +38,8 @@ class _Bucket:
         self.launched = False
 
 
-def plan_buckets(segments: List[Tuple[int, int]], bucket_elems: int) -> List[Tuple[int, int, List[int]]]:
+def plan_buckets(segments: List[Tuple[int, int]], bucket_elems: int,
+                 total: Optional[int] = None) -> List[Tuple[int, int, List[int]]]:
     """Static plan: walk parameters in reverse registration order (≈ the order backward produces
     gradients) and cut a bucket whenever it reaches ``bucket_elems``.  Returns
     ``[(lo, hi, [param indices])]`` over the flat space, in launch order."""
@@ -63,6 +64,12 @@ def plan_buckets(segments: List[Tuple[int, int]], bucket_elems: int) -> List[Tup
     for a, b in zip(plan_sorted[:-1], plan_sorted[1:]):
         lo, _, idxs = plan[a]
         plan[a] = (lo, plan[b][0], idxs)
+    if total is not None and plan_sorted:
+        # the top bucket also owns the alignment padding after the last parameter, so every range is a multiple of
+        # the 16-byte vector the collectives move (an odd tail would bounce through the scratch region)
+        top = plan_sorted[-1]
+        lo, hi, idxs = plan[top]
+        plan[top] = (lo, max(hi, total), idxs)
     return plan
 
 
@@ -90,7 +97,7 @@ class DistributedOptimizer:
         self.device = self.flat.device
         bucket_bytes = bucket_bytes or env_int('DDLS_BUCKET_BYTES', 2 << 20)
         self.buckets = [_Bucket(lo, hi, idxs) for lo, hi, idxs in
-                        plan_buckets(self.flat.segments(), max(1, bucket_bytes // 4))]
+                        plan_buckets(self.flat.segments(), max(1, bucket_bytes // 4), self.flat.numel)]
         self._bucket_of: Dict[int, _Bucket] = {}
         for b in self.buckets:
             for i in b.params:

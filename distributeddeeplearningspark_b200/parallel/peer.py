@@ -42,7 +42,7 @@ SEQ_OFF = 2048
 ALIGN = 256
 
 AR_ONESHOT, AR_TWOSHOT, AR_NVLS, AR_ONESHOT_LL = 0, 1, 2, 3
-LL_MAX_BYTES_DEFAULT = 256 << 10     # flag-in-data one-shot up to this message size
+LL_MAX_BYTES_DEFAULT = 512 << 10     # flag-in-data one-shot up to this message size (NYISO LSTM: 267 KB of gradients)
 
 
 class CommDesc(ctypes.Structure):

@@ -122,8 +122,11 @@ class StepEngine:
 
     # -- graph capture -------------------------------------------------------
     def _capture(self, x: torch.Tensor, y: torch.Tensor) -> None:
-        self._static_x = x.clone()
-        self._static_y = y.clone()
+        if self._static_x is None or self._static_x.shape != x.shape:
+            self._static_x = x.clone()
+            self._static_y = y.clone()
+        elif x.data_ptr() != self._static_x.data_ptr():
+            self._static_x.copy_(x); self._static_y.copy_(y)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
             self._static_loss = self._eager_step(self._static_x, self._static_y)
@@ -153,10 +156,80 @@ class StepEngine:
             # the capture itself does not run the step: replay below with this batch
         if x.shape != self._static_x.shape:
             return self._eager_step(x, y)
-        self._static_x.copy_(x, non_blocking=True)
-        self._static_y.copy_(y, non_blocking=True)
+        if x.data_ptr() != self._static_x.data_ptr():      # callers may fill input_buffers() directly (no extra hop)
+            self._static_x.copy_(x, non_blocking=True)
+        if y.data_ptr() != self._static_y.data_ptr():
+            self._static_y.copy_(y, non_blocking=True)
         self._graph.replay()
         return self._static_loss
+
+    def input_buffers(self, x_like: torch.Tensor, y_like: torch.Tensor):
+        """The step's static input tensors (created from the given shapes/dtypes on first use).  A feeder that copies
+        its pinned host batch straight into them and then calls ``step(xb, yb)`` with these very tensors saves the
+        device-to-device hop a captured graph otherwise needs."""
+        if self._static_x is None:
+            self._static_x = torch.empty(x_like.shape, dtype=x_like.dtype, device=self.device)
+            self._static_y = torch.empty(y_like.shape, dtype=y_like.dtype, device=self.device)
+        return self._static_x, self._static_y
+
+    # -- device-resident dataset ------------------------------------------------------------------------------
+    def attach_dataset(self, X: torch.Tensor, Y: torch.Tensor, batch_size: int, perm: Optional[torch.Tensor] = None) -> None:
+        """Keep the (partition of the) training set on the device — the counterpart of the reference's cached
+        DataFrame partition (/root/reference/ddl_mnist_aztk.py:156-161).  ``step_dataset()`` then trains on
+        consecutive minibatches (positions wrap around the end like dist-keras' batching across epochs); the
+        minibatch gather is a kernel inside the captured step, driven by a device-side cursor, so a step is ONE graph
+        launch with no input copy.  ``perm`` (int32 [N]) gives a shuffled order."""
+        from .. import _native as N
+        assert self.cuda and X.is_cuda and Y.is_cuda and X.shape[0] == Y.shape[0]
+        X, Y = X.contiguous(), Y.contiguous()
+        rx, ry = X[0].numel() * X.element_size(), Y[0].numel() * Y.element_size()
+        if rx % 4 or ry % 4:
+            raise ValueError('dataset rows must be multiples of 4 bytes')
+        N.register('ddls_gather_batch', [N.c_void_p, N.c_void_p, N.c_void_p, N.c_void_p, N.c_void_p, N.c_void_p,
+                                         N.c_int, N.c_longlong, N.c_longlong, N.c_longlong, N.c_void_p])
+        self._ds = dict(X=X, Y=Y, B=int(batch_size), rx=rx, ry=ry,
+                        perm=None if perm is None else perm.to(self.device, torch.int32).contiguous(),
+                        cursor=torch.zeros(2, dtype=torch.int32, device=self.device))
+        self._ds_x = torch.empty((batch_size,) + tuple(X.shape[1:]), dtype=X.dtype, device=self.device)
+        self._ds_y = torch.empty((batch_size,) + tuple(Y.shape[1:]), dtype=Y.dtype, device=self.device)
+        self._ds_graph = None
+        self._ds_warm = 0
+
+    def _gather(self) -> None:
+        from .. import _native as N
+        d = self._ds
+        N.call('ddls_gather_batch', d['X'].data_ptr(), d['Y'].data_ptr(), self._ds_x.data_ptr(), self._ds_y.data_ptr(),
+               N.ptr(d['perm']), d['cursor'].data_ptr(), d['B'], d['X'].shape[0], d['rx'], d['ry'],
+               N.stream_ptr(self.device))
+
+    def step_dataset(self) -> torch.Tensor:
+        """One training step on the next minibatch of the attached dataset."""
+        self.steps += 1
+        if hasattr(self._inner, 'refresh_shadows_if_stale'):
+            self._inner.refresh_shadows_if_stale()
+        if self.use_cuda_graph and self._ds_graph is not None:
+            self._ds_graph.replay()
+            return self._ds_loss
+        if not self.use_cuda_graph or self._ds_warm < 3:
+            self._ds_warm += 1
+            s = torch.cuda.Stream(device=self.device)
+            s.wait_stream(torch.cuda.current_stream(self.device))
+            with torch.cuda.stream(s):
+                self._gather()
+                loss = self._eager_step(self._ds_x, self._ds_y)
+            torch.cuda.current_stream(self.device).wait_stream(s)
+            return loss
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._gather()
+            self._ds_loss = self._eager_step(self._ds_x, self._ds_y)
+        self._ds_graph = g
+        g.replay()
+        return self._ds_loss
+
+    def dataset_cursor(self) -> int:
+        """Number of minibatches consumed from the attached dataset (device -> host read)."""
+        return int(self._ds['cursor'][0].item())
 
     @torch.no_grad()
     def predict(self, x: torch.Tensor) -> torch.Tensor:

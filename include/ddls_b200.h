@@ -71,6 +71,12 @@ int ddls_refresh_shadows(const float* params, size_t n, const DdlsShadowSpec* sh
 int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* labels, float* x, float* onehot, int n, int npix,
                           int classes, float o_min, float scale, float n_min, void* stream);
 
+/* Minibatch gather from a device-resident dataset: rows perm[(k*B + r) mod N] (perm may be NULL) of X [N, row_x_bytes] and
+ * Y [N, row_y_bytes] -> x [B, ...], y [B, ...]; k = cursor[0] is a device-side batch counter the kernel advances
+ * (cursor: uint32[2], zero-initialised), so the gather can be the first node of a captured training-step graph. */
+int ddls_gather_batch(const void* X, const void* Y, void* x, void* y, const int* perm, unsigned* cursor, int B, long long N,
+                      long long row_x_bytes, long long row_y_bytes, void* stream);
+
 /* ---- persistent LSTM(128) recurrence, tcgen05 (Keras LSTM, /root/reference/ddl_nyiso_aztk.py:249-251) ---
  * x [B,T] fp32 (input dim 1), w_ih [4H], w_hh [H,4H], bias [4H] in Keras layout, gate order i,f,c,o.
  * out [B,H] (last step) or [B,T,H].  When save_for_backward: hs [T,B,H] bf16, gates [T,B,H,4] bf16
