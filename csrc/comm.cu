@@ -110,6 +110,52 @@ struct ArParams {
   float scale;
 };
 
+// Optional optimizer epilogue (K12/K13 "fused into the allreduce epilogue"): the thread that has just summed a
+// gradient vector applies the Keras update to the matching parameter / slot vectors, so a data-parallel step of a
+// single-bucket model is ONE kernel after backward instead of allreduce + optimizer.
+struct OptFuse {
+  int kind;                   // 0 none, 1 adam, 2 adagrad, 3 sgd
+  float* p; float* s1; float* s2;   // params, m|accumulator, v
+  int* step;                  // [completed steps, ticket] as in csrc/elementwise.cu
+  float lr, b1, b2, eps;
+  int zero_grads;
+};
+
+DDLS_DEVINL void opt_apply(const OptFuse& o, uint64_t i, float (&g)[4], float lr_t) {
+  float4* P = reinterpret_cast<float4*>(o.p) + i;
+  float4 pi = *P;
+  float pv[4] = {pi.x, pi.y, pi.z, pi.w};
+  if (o.kind == 1) {
+    float4* M = reinterpret_cast<float4*>(o.s1) + i;
+    float4* V = reinterpret_cast<float4*>(o.s2) + i;
+    const float4 m4 = *M, v4 = *V;
+    float mv[4] = {m4.x, m4.y, m4.z, m4.w}, vv[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      mv[j] = o.b1 * mv[j] + (1.0f - o.b1) * g[j];
+      vv[j] = o.b2 * vv[j] + (1.0f - o.b2) * g[j] * g[j];
+      pv[j] -= lr_t * mv[j] / (sqrtf(vv[j]) + o.eps);
+    }
+    *M = make_float4(mv[0], mv[1], mv[2], mv[3]);
+    *V = make_float4(vv[0], vv[1], vv[2], vv[3]);
+  } else if (o.kind == 2) {
+    float4* A = reinterpret_cast<float4*>(o.s1) + i;
+    const float4 a4 = *A;
+    float av[4] = {a4.x, a4.y, a4.z, a4.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      av[j] += g[j] * g[j];
+      pv[j] -= o.lr * g[j] / (sqrtf(av[j]) + o.eps);
+    }
+    *A = make_float4(av[0], av[1], av[2], av[3]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) pv[j] -= o.lr * g[j];
+  }
+  *P = make_float4(pv[0], pv[1], pv[2], pv[3]);
+  if (o.zero_grads) { g[0] = g[1] = g[2] = g[3] = 0.f; }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // one-shot push allreduce
 // ---------------------------------------------------------------------------------------------------------
@@ -194,8 +240,14 @@ DDLS_DEVINL uint4 ll_wait(const CommCtx& c, const uint4* p, uint32_t epoch, int 
 }
 
 template <typename Wire>
-__global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(CommCtx c, ArParams p) {
+__global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(CommCtx c, ArParams p, OptFuse opt) {
   constexpr bool F32 = sizeof(Wire) == 4;
+  int t_step = 0;
+  float lr_t = 0.f;
+  if (opt.kind != 0) {
+    t_step = *reinterpret_cast<volatile int*>(opt.step) + 1;
+    lr_t = (opt.kind == 1) ? opt.lr * sqrtf(1.0f - powf(opt.b2, (float)t_step)) / (1.0f - powf(opt.b1, (float)t_step)) : opt.lr;
+  }
   constexpr int Q = F32 ? 2 : 1;                          // 16-byte stores per 4 elements
   const int rank = c.rank_base + blockIdx.y;
   const uint32_t e0 = read_epoch(c, rank);
@@ -245,9 +297,22 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(Comm
       }
       acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3];
     }
-    out[i] = make_float4(acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale);
+    float g[4] = {acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale};
+    if (opt.kind != 0) opt_apply(opt, i, g, lr_t);
+    out[i] = make_float4(g[0], g[1], g[2], g[3]);
   }
-  advance_epoch(c, rank, e0 + 2);
+  // last block out: advance the collective epoch and, with a fused optimizer, its step counter
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* seq = reinterpret_cast<uint32_t*>(c.base[rank] + c.seq_off);
+    __threadfence();
+    const uint32_t ticket = atomicAdd(seq + 1, 1u);
+    if (ticket == gridDim.x - 1) {
+      seq[0] = e0 + 2; seq[1] = 0;
+      if (opt.kind != 0) opt.step[0] = t_step;
+      __threadfence();
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -509,8 +574,9 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
       int lb = blocks > 0 ? blocks : (int)((n / 4 + COMM_THREADS - 1) / COMM_THREADS);     // one 16-byte vector per thread
       if (lb > 64) lb = 64;
       if (lb < 1) lb = 1;
-      return wire_bf16 ? launch(d, allreduce_oneshot_ll_kernel<__nv_bfloat16>, lb, COMM_THREADS, st, c, p)
-                       : launch(d, allreduce_oneshot_ll_kernel<float>, lb, COMM_THREADS, st, c, p);
+      OptFuse none{};
+      return wire_bf16 ? launch(d, allreduce_oneshot_ll_kernel<__nv_bfloat16>, lb, COMM_THREADS, st, c, p, none)
+                       : launch(d, allreduce_oneshot_ll_kernel<float>, lb, COMM_THREADS, st, c, p, none);
     }
     case DDLS_AR_TWOSHOT:
       return wire_bf16 ? launch(d, allreduce_twoshot_kernel<__nv_bfloat16>, nb, COMM_THREADS, st, c, p)
@@ -521,6 +587,36 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
   }
   set_last_error("ddls_comm_allreduce: unknown algorithm %d", algo);
   return 1;
+}
+
+extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off, uint64_t stage_off, uint64_t stage_bytes,
+                                       uint64_t n, float scale, int wire_bf16, int kind, float* params, float* slot1,
+                                       float* slot2, int* step, float lr, float b1, float b2, float eps, int zero_grads,
+                                       void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  if (n == 0) return 0;
+  if (d->emulate) { set_last_error("ddls_comm_allreduce_opt: not available in emulation mode (one parameter set per rank)"); return 1; }
+  if (kind < 1 || kind > 3 || params == nullptr || step == nullptr || (kind <= 2 && slot1 == nullptr) || (kind == 1 && slot2 == nullptr)) {
+    set_last_error("ddls_comm_allreduce_opt: bad optimizer description (kind %d)", kind);
+    return 1;
+  }
+  if (n % 4 != 0 || (grad_off | stage_off) % 16 != 0 || (reinterpret_cast<uintptr_t>(params) & 15)) {
+    set_last_error("ddls_comm_allreduce_opt: n must be a multiple of 4 and buffers 16-byte aligned");
+    return 1;
+  }
+  const uint64_t parity_bytes = (stage_bytes / 2) & ~static_cast<uint64_t>(15);
+  if ((uint64_t)d->world * n * (wire_bf16 ? 4 : 8) > parity_bytes) {
+    set_last_error("ddls_comm_allreduce_opt: %llu elements do not fit the flag-in-data staging region", (unsigned long long)n);
+    return 1;
+  }
+  ArParams p{grad_off, grad_off, stage_off, parity_bytes, n, scale};
+  OptFuse o{kind, params, slot1, slot2, step, lr, b1, b2, eps, zero_grads};
+  int lb = (int)((n / 4 + COMM_THREADS - 1) / COMM_THREADS);
+  if (lb > 64) lb = 64;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  return wire_bf16 ? launch(d, allreduce_oneshot_ll_kernel<__nv_bfloat16>, lb, COMM_THREADS, st, c, p, o)
+                   : launch(d, allreduce_oneshot_ll_kernel<float>, lb, COMM_THREADS, st, c, p, o);
 }
 
 extern "C" int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast,

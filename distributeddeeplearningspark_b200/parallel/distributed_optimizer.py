@@ -113,6 +113,13 @@ class DistributedOptimizer:
         self._bf16 = None
         if self.compression is Compression.bf16 and self.size > 1:
             self._bf16 = self.comm.alloc(self.flat.numel, torch.bfloat16)
+        # Single-bucket models whose gradients fit the flag-in-data allreduce get allreduce + optimizer in ONE kernel
+        # (K12/K13 of SURVEY.md §2.5): the hook then has nothing to launch, step() issues the fused kernel.
+        self._fused = (self.size > 1 and not self._generic and len(self.buckets) == 1
+                       and self.backward_passes_per_step == 1 and env_int('DDLS_FUSED_OPT', 1) != 0
+                       and hasattr(self.comm, 'allreduce_opt_') and getattr(self.inner, 'kind', '') in ('adam', 'adagrad', 'sgd')
+                       and self.buckets[0].lo == 0 and self.buckets[0].hi == self.flat.numel
+                       and self.comm.can_fuse_optimizer(self.flat.flat_grads))
 
     # ------------------------------------------------------------------ hooks
     def _on_grad(self, p: torch.Tensor) -> None:
@@ -141,6 +148,8 @@ class DistributedOptimizer:
 
     def _launch(self, b: _Bucket) -> None:
         b.launched = True
+        if self._fused and not getattr(self.inner, '_nspecs', 0):
+            return                                   # reduced and applied by the fused kernel in step()
         if self.overlap:
             cur = torch.cuda.current_stream(self.device)
             ev = torch.cuda.Event()
@@ -181,6 +190,11 @@ class DistributedOptimizer:
             self.flat.gather_stray_grads()
             for b in self.buckets:  # hooks saw foreign tensors; reduce everything now
                 b.launched = False
+        if self._fused and closure is None and not getattr(self.inner, '_nspecs', 0):
+            for b in self.buckets:
+                b.pending = len(b.params); b.launched = False; b.done_event = None
+            self.comm.allreduce_opt_(self.flat.flat_grads, self.inner, self.op, wire_bf16=self._bf16 is not None)
+            return None
         self.synchronize()
         return self.inner.step() if closure is None else self.inner.step(closure)
 

@@ -63,6 +63,7 @@ N.register('ddls_mc_import', [I, ctypes.POINTER(ctypes.c_ulonglong)])
 N.register('ddls_mc_add_device', [ctypes.c_ulonglong, I])
 N.register('ddls_mc_bind_and_map', [ctypes.c_ulonglong, ctypes.c_ulonglong, N.c_size_t, I, ctypes.POINTER(P)])
 N.register('ddls_comm_allreduce', [DP, I, U64, U64, U64, U64, U64, F, I, I, P])
+N.register('ddls_comm_allreduce_opt', [DP, U64, U64, U64, U64, F, I, I, P, P, P, P, F, F, F, F, I, P])
 N.register('ddls_comm_broadcast', [DP, U64, U64, I, I, I, P])
 N.register('ddls_comm_allgather', [DP, U64, U64, U64, I, P])
 N.register('ddls_comm_barrier', [DP, P])
@@ -313,6 +314,25 @@ class PeerMemoryComm(Communicator, _HeapBase):
                    m4, scale, int(wire_bf16), 0, self._stream())
             flat[lo:lo + m].copy_(scratch[:m])
         return t
+
+    def can_fuse_optimizer(self, g: torch.Tensor) -> bool:
+        """Is ``g`` (a heap-resident fp32 gradient range) small enough for the fused allreduce + optimizer kernel?"""
+        n = g.numel()
+        return (g.dtype == torch.float32 and n % 4 == 0 and g.is_contiguous() and n <= self._ll_elems
+                and self.offset_of(g) is not None and self.offset_of(g) % 16 == 0)
+
+    def allreduce_opt_(self, g: torch.Tensor, opt, op: ReduceOp = Average, wire_bf16: bool = False) -> None:
+        """Allreduce the flat gradient ``g`` and apply ``opt``'s update (Keras Adam / Adagrad / SGD over the matching
+        flat parameter space) in ONE kernel: the thread that has summed a gradient vector updates its parameters."""
+        kind = {'adam': 1, 'adagrad': 2, 'sgd': 3}[opt.kind]
+        scale = opt.grad_scale * ((1.0 / self.size) if op is Average else 1.0)
+        s1 = opt.m if kind == 1 else (opt.acc if kind == 2 else None)
+        s2 = opt.v if kind == 1 else None
+        N.call('ddls_comm_allreduce_opt', ctypes.byref(self.desc), self.offset_of(g), self._ll_off, self._ll_bytes,
+               g.numel(), scale, int(wire_bf16), kind, opt.flat.flat_params.data_ptr(), N.ptr(s1), N.ptr(s2),
+               opt._step_buf.data_ptr(), opt.lr, getattr(opt, 'beta_1', 0.0), getattr(opt, 'beta_2', 0.0),
+               getattr(opt, 'epsilon', 0.0), int(opt.zero_grads_in_step), self._stream())
+        torch.autograd.graph.increment_version(g)
 
     def allreduce_bf16_wire_(self, g: torch.Tensor, _w: torch.Tensor, op: ReduceOp = Average) -> torch.Tensor:
         """fp32 gradients, bf16 on the wire, fp32 accumulate — the cast is fused into the collective."""

@@ -193,6 +193,31 @@ def _multi_rank_checks():
     dist.all_gather(ws, w)
     res['weights_equal'] = all(torch.equal(ws[0], v) for v in ws)
     res['graph'] = eng._graph is not None
+    res['fused'] = bool(dopt._fused)
+    # fused allreduce + optimizer kernel == allreduce kernel followed by the optimizer kernel (same gradients fed to both;
+    # end-to-end training runs are not compared because the recurrent kernels' atomics make tiny gradients differ
+    # from run to run and Adagrad's g/(sqrt(a)+eps) amplifies that)
+    import os
+    finals = {}
+    for fused in ('1', '0'):
+        os.environ['DDLS_FUSED_OPT'] = fused
+        for kind in ('adam', 'adagrad', 'sgd'):
+            torch.manual_seed(5)
+            ps = [torch.nn.Parameter(torch.randn(1000, device=dev)), torch.nn.Parameter(torch.randn(37, 5, device=dev))]
+            o2 = ddls.optim.get_optimizer(kind, ps, comm=comm)
+            o2.zero_grads_in_step = True
+            d2 = ddls.DistributedOptimizer(o2)
+            assert bool(d2._fused) == (fused == '1')
+            for k in range(5):
+                torch.manual_seed(1000 * k + r)
+                o2.flat.flat_grads.copy_(torch.randn(o2.flat.numel, device=dev))
+                d2.step()
+            torch.cuda.synchronize()
+            assert int(o2.step_count.item()) == 5 and float(o2.flat.flat_grads.abs().max()) == 0.0
+            finals[(fused, kind)] = o2.flat.flat_params.clone()
+    os.environ.pop('DDLS_FUSED_OPT')
+    res['fused_err'] = {k: float((finals[('1', k)] - finals[('0', k)]).abs().max()) for k in ('adam', 'adagrad', 'sgd')}
+    res['fused_matches'] = all(v < 1e-6 for v in res['fused_err'].values())
     torch.cuda.synchronize()
     return res
 
@@ -205,3 +230,4 @@ def test_peer_memory_comm_multi_gpu():
     out = spark.run(_multi_rank_checks, num_proc=n, backend=LocalBarrierBackend(timeout=600))
     assert [o['rank'] for o in out] == list(range(n))
     assert all(o['weights_equal'] for o in out) and all(o['graph'] for o in out)
+    assert all(o['fused'] for o in out) and all(o['fused_matches'] for o in out), [o.get('fused_err') for o in out]
