@@ -40,4 +40,25 @@ int tmap_bf16_sw128(CUtensorMap* out, const void* base, const uint64_t dims[3], 
   return 0;
 }
 
+
+// General form: rank 2..5, swizzle 0 = none, 1 = 32 B, 2 = 64 B, 3 = 128 B.
+int tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+              const uint32_t* box, int swizzle) {
+  uint64_t d3[3] = {1, 1, 1};
+  uint64_t s2[2] = {16, 16};
+  uint32_t b3[3] = {1, 1, 1};
+  if (tmap_bf16_sw128(out, base, d3, s2, b3) != 0 && g_encode == nullptr) return 1;   // resolves g_encode (error already set)
+  if (rank < 2 || rank > 5) { set_last_error("tmap_bf16: rank must be 2..5"); return 1; }
+  cuuint64_t d[5]; cuuint64_t s[4]; cuuint32_t b[5]; cuuint32_t e[5];
+  for (int i = 0; i < rank; ++i) { d[i] = dims[i]; b[i] = box[i]; e[i] = 1; }
+  for (int i = 0; i + 1 < rank; ++i) s[i] = strides_bytes[i];
+  const CUtensorMapSwizzle sw = swizzle == 3 ? CU_TENSOR_MAP_SWIZZLE_128B : swizzle == 2 ? CU_TENSOR_MAP_SWIZZLE_64B
+                              : swizzle == 1 ? CU_TENSOR_MAP_SWIZZLE_32B : CU_TENSOR_MAP_SWIZZLE_NONE;
+  const CUresult r = g_encode(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, (cuuint32_t)rank, const_cast<void*>(base), d, s, b, e,
+                              CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { set_last_error("cuTensorMapEncodeTiled failed (%d) for a rank-%d map", (int)r, rank); return 1; }
+  return 0;
+}
+
 }  // namespace ddls

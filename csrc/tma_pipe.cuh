@@ -25,6 +25,17 @@ namespace ddls {
 int tmap_bf16_sw128(CUtensorMap* out, const void* base, const uint64_t dims[3], const uint64_t strides_bytes[2],
                     const uint32_t box[3]);
 
+int tmap_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+              const uint32_t* box, int swizzle);
+
+DDLS_DEVINL void tma_load_4d(uint32_t smem_dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1, int c2, int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::"r"(
+          smem_dst),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
 DDLS_DEVINL void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");
 }
@@ -36,6 +47,7 @@ DDLS_DEVINL void tma_load_3d(uint32_t smem_dst, const CUtensorMap* m, uint64_t* 
       : "memory");
 }
 
+constexpr uint32_t SW64_DESC_HI = ((512u >> 4) & 0x3FFFu) | (1u << 14) | (4u << 29);     // SBO 512, version 1, SWIZZLE_64B
 constexpr uint32_t SW128_DESC_HI = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);   // SBO 1024, version 1, SWIZZLE_128B
 
 template <int BN_, bool A_MN_, bool B_MN_, int STAGES_>

@@ -9,11 +9,27 @@ from .gemm import gemm_bf16, workspace
 P, I, Z = N.c_void_p, N.c_int, N.c_size_t
 N.register('ddls_cnn_conv1_fwd', [P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_pool_fwd', [P, P, P, P, P, I, P])
+N.register('ddls_cnn_conv2_pool_fwd_tma', [P, P, P, P, P, I, P])
+N.register('ddls_cnn_conv2_dgrad_tma', [P, P, P, P, I, P])
 N.register('ddls_relu_bwd_bias', [P, P, P, P, I, I, I, P])
 N.register('ddls_cnn_unpool_bwd', [P, P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_wgrad', [P, P, P, P, Z, I, P])
 N.register('ddls_cnn_conv2_dgrad', [P, P, P, P, I, P])
 N.register('ddls_cnn_conv1_wgrad', [P, P, P, P, Z, I, P])
+
+
+def use_tma() -> bool:
+    """Persistent TMA-fed conv2 kernels (csrc/cnn_tma.cu) unless DDLS_CNN_TMA=0 (first generation, csrc/cnn.cu)."""
+    import os
+    return os.environ.get('DDLS_CNN_TMA', '1') != '0'
+
+
+def conv2_fwd_name() -> str:
+    return 'ddls_cnn_conv2_pool_fwd_tma' if use_tma() else 'ddls_cnn_conv2_pool_fwd'
+
+
+def conv2_dgrad_name() -> str:
+    return 'ddls_cnn_conv2_dgrad_tma' if use_tma() else 'ddls_cnn_conv2_dgrad'
 
 FWD_SPLIT_K = 18
 
@@ -40,7 +56,7 @@ class _CnnTrunk(torch.autograd.Function):
         pooled = torch.empty((B, 12, 12, 32), dtype=torch.bfloat16, device=dev)
         pidx = torch.empty((B, 12, 12, 32), dtype=torch.uint8, device=dev)
         N.call('ddls_cnn_conv1_fwd', x.data_ptr(), k1.data_ptr(), b1.data_ptr(), a1.data_ptr(), B, st)
-        N.call('ddls_cnn_conv2_pool_fwd', a1.data_ptr(), k2.data_ptr(), b2.data_ptr(), pooled.data_ptr(),
+        N.call(conv2_fwd_name(), a1.data_ptr(), k2.data_ptr(), b2.data_ptr(), pooled.data_ptr(),
                pidx.data_ptr(), B, st)
         a3 = gemm_bf16(pooled.view(B, 4608), kd1, bias=bd1, relu=True, b_mn_major=True, split_k=FWD_SPLIT_K)
         if any(ctx.needs_input_grad):
@@ -72,7 +88,7 @@ class _CnnTrunk(torch.autograd.Function):
         dk2 = torch.empty((3, 3, 32, 32), dtype=torch.float32, device=dev)
         N.call('ddls_cnn_conv2_wgrad', a1.data_ptr(), dz2.data_ptr(), dk2.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
         dz1 = torch.empty((B, 26, 26, 32), dtype=torch.bfloat16, device=dev)
-        N.call('ddls_cnn_conv2_dgrad', dz2.data_ptr(), k2.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
+        N.call(conv2_dgrad_name(), dz2.data_ptr(), k2.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
         g1 = torch.empty(320, dtype=torch.float32, device=dev)
         N.call('ddls_cnn_conv1_wgrad', x.data_ptr(), dz1.data_ptr(), g1.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
         return None, g1[:288].view(3, 3, 1, 32), g1[288:], dk2, db2, dkd1, dbd1

@@ -211,7 +211,7 @@ class DirectStep:
         dz1 = self._buf('dz1', (B, 26, 26, 32), bf)
         x = x.contiguous()
         N.call('ddls_cnn_conv1_fwd', x.data_ptr(), c1.kernel.data_ptr(), c1.bias.data_ptr(), a1.data_ptr(), B, st)
-        N.call('ddls_cnn_conv2_pool_fwd', a1.data_ptr(), c2.kernel.data_ptr(), c2.bias.data_ptr(), pooled.data_ptr(),
+        N.call(C.conv2_fwd_name(), a1.data_ptr(), c2.kernel.data_ptr(), c2.bias.data_ptr(), pooled.data_ptr(),
                pidx.data_ptr(), B, st)
         flat = pooled.view(B, 4608)
         w1s = self.w1s[:, :F]
@@ -230,7 +230,7 @@ class DirectStep:
         ws = workspace(self.dev, max(N.lib().ddls_cnn_conv2_wgrad_scratch_bytes(B), B * 320 * 4))
         N.call('ddls_cnn_conv2_wgrad', a1.data_ptr(), dz2.data_ptr(), c2.kernel.grad.data_ptr(), ws.data_ptr(),
                ws.numel(), B, st)
-        N.call('ddls_cnn_conv2_dgrad', dz2.data_ptr(), c2.kernel.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
+        N.call(C.conv2_dgrad_name(), dz2.data_ptr(), c2.kernel.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
         g1k, g1b = c1.kernel.grad, c1.bias.grad
         if g1b.data_ptr() == g1k.data_ptr() + 288 * 4:
             N.call('ddls_cnn_conv1_wgrad', x.data_ptr(), dz1.data_ptr(), g1k.data_ptr(), ws.data_ptr(), ws.numel(), B, st)

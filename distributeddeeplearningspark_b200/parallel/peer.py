@@ -197,6 +197,9 @@ class PeerMemoryComm(Communicator, _HeapBase):
         self._scratch_off = self._alloc_off(64 << 20)   # staging for tensors that are not heap-resident
         self._scratch_bytes = 64 << 20
         self._init_ll_stage(size)
+        # CTAs of the bandwidth algorithms (0 = by size, up to 64): fewer leave more SMs to the backward kernels the
+        # gradient allreduce overlaps with
+        self._ar_blocks = env_int('DDLS_AR_BLOCKS', 0)
         self._heap_u8[self._ll_off:self._ll_off + self._ll_bytes].zero_()
         torch.cuda.synchronize(device)
         dist.barrier(device_ids=[self.dev_index])
@@ -294,8 +297,9 @@ class PeerMemoryComm(Communicator, _HeapBase):
         if off is not None and off % 16 == 0:
             a = algo if algo is not None else self.select_algo(n * 4, True, bool(self.mc_base))
             stage, sbytes = self._ensure_stage(n, self.size, a) if a != AR_NVLS else (0, 0)
+            blocks = self._ar_blocks if a in (AR_NVLS, AR_TWOSHOT) else 0
             N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, sbytes, n, scale, int(wire_bf16),
-                   0, self._stream())
+                   blocks, self._stream())
             torch.autograd.graph.increment_version(t)     # raw-pointer kernels bypass torch's version counter
             return t
         # not heap-resident: bounce through the scratch region (chunked)

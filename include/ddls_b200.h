@@ -187,6 +187,11 @@ int ddls_cnn_conv2_wgrad(const void* a1, const void* dz2, float* dw2, void* scra
                          void* stream);
 /* conv2 data gradient fused with conv1's ReLU mask: dz1 [B,26,26,32] bf16. */
 int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream);
+/* Second-generation conv2 kernels (csrc/cnn_tma.cu): persistent CTAs, one 4-D TMA box per filter tap (64-byte swizzle)
+ * instead of a per-thread im2col gather; same arguments and results as the two functions above. */
+int ddls_cnn_conv2_pool_fwd_tma(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
+                                void* stream);
+int ddls_cnn_conv2_dgrad_tma(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream);
 /* conv1 gradients: dw1_db1 = [3*3*1*32 kernel gradient | 32 bias gradient] fp32; scratch B*320*4 bytes. */
 int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_db1, void* scratch, size_t scratch_bytes, int B,
                          void* stream);

@@ -36,15 +36,16 @@ def test_conv1_fwd(dev, B):
     assert _rel(a1, ref) < 6e-3
 
 
+@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_pool_fwd', 'ddls_cnn_conv2_pool_fwd_tma'])
 @pytest.mark.parametrize('B', [3, 128])
-def test_conv2_pool_fwd(dev, B):
+def test_conv2_pool_fwd(dev, B, entry):
     torch.manual_seed(1)
     a1 = torch.relu(torch.randn(B, 26, 26, 32, device=dev)).bfloat16()
     w = (torch.randn(3, 3, 32, 32, device=dev) * 0.08)
     b = torch.randn(32, device=dev) * 0.1
     pooled = torch.empty(B, 12, 12, 32, dtype=torch.bfloat16, device=dev)
     pidx = torch.empty(B, 12, 12, 32, dtype=torch.uint8, device=dev)
-    N.call('ddls_cnn_conv2_pool_fwd', a1.data_ptr(), w.data_ptr(), b.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), B,
+    N.call(entry, a1.data_ptr(), w.data_ptr(), b.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), B,
            N.stream_ptr(dev))
     z = _conv_ref(a1.float(), w.bfloat16().float(), b)                       # [B,24,24,32]
     zr = z.reshape(B, 12, 2, 12, 2, 32).permute(0, 1, 3, 2, 4, 5).reshape(B, 12, 12, 4, 32)
@@ -88,14 +89,15 @@ def test_conv2_wgrad(dev, B):
     assert _rel(dw, w.grad) < 5e-3
 
 
+@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_dgrad', 'ddls_cnn_conv2_dgrad_tma'])
 @pytest.mark.parametrize('B', [2, 128])
-def test_conv2_dgrad(dev, B):
+def test_conv2_dgrad(dev, B, entry):
     torch.manual_seed(4)
     a1 = torch.relu(torch.randn(B, 26, 26, 32, device=dev)).bfloat16()
     dz2 = torch.randn(B, 24, 24, 32, device=dev).bfloat16()
     w = torch.randn(3, 3, 32, 32, device=dev) * 0.1
     dz1 = torch.empty(B, 26, 26, 32, dtype=torch.bfloat16, device=dev)
-    N.call('ddls_cnn_conv2_dgrad', dz2.data_ptr(), w.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, N.stream_ptr(dev))
+    N.call(entry, dz2.data_ptr(), w.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, N.stream_ptr(dev))
     xin = a1.float().clone().requires_grad_(True)
     (_conv_ref(xin, w.bfloat16().float()) * dz2.float()).sum().backward()
     ref = xin.grad * (a1.float() > 0)
