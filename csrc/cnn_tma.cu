@@ -213,6 +213,115 @@ __global__ void __launch_bounds__(CV_THREADS, 1) conv2_tma_kernel(const __grid_c
   if (warp == 1) tmem_dealloc(tmem, 64);
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// conv2 weight gradient: dW[(tap, ci), co] = sum over pixels of a1[b, y+kh, x+kw, ci] * dz2[b, y, x, co].
+// K = pixels.  A band of 4 output rows (96 pixels = six K16 steps) needs the same nine shifted boxes of a1 as the
+// forward pass plus ONE box of dz2; here they are MN-major operands (K = pixel rows of 64 bytes, 32 channels each):
+// A tile j = taps 4j..4j+3 (M = 128, LBO = one tap block), B = the dz2 band (N = 32).  A persistent CTA accumulates
+// all its bands into three TMEM accumulators (M = 288 padded to 384) and writes ONE partial dW at the end; the existing
+// sum_partials kernel adds the per-CTA partials (no atomics).
+constexpr int WG_TAPS = 12;                              // 9 real tap blocks + 3 zero blocks so that M tiles are whole
+constexpr int WG_STAGE_BYTES = (WG_TAPS + 1) * TAP_BYTES;   // + the dz2 band
+constexpr int WG_SMEM = 2 * WG_STAGE_BYTES + 1024;
+
+__global__ void __launch_bounds__(CV_THREADS, 1)
+conv2_wgrad_tma_kernel(const __grid_constant__ CUtensorMap ta, const __grid_constant__ CUtensorMap tz, float* partial,
+                       int tiles) {
+  constexpr uint32_t BOX_BYTES = 96 * 64;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = align1024(smem_raw);
+  __shared__ uint64_t full[2], empty[2], done;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(&done, 1);
+    mbar_fence_init();
+    tma_prefetch_desc(&ta); tma_prefetch_desc(&tz);
+  }
+  if (warp == 1) tmem_alloc(&tmem_slot, 128);
+  // tap blocks 9..11 (and pixel rows 96..127 of every block, never read: K = 96) — zero the padding taps once
+  for (int i = threadIdx.x; i < 2 * 3 * (TAP_BYTES / 16); i += blockDim.x) {
+    const int s = i / (3 * (TAP_BYTES / 16)), r = i - s * 3 * (TAP_BYTES / 16);
+    *reinterpret_cast<uint4*>(smem + s * WG_STAGE_BYTES + 9 * TAP_BYTES + r * 16) = make_uint4(0u, 0u, 0u, 0u);
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  const int my_tiles = (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+        const int b = tile / 6, y0 = (tile - b * 6) * 4;
+        const int s = it & 1, ph = (it >> 1) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        mbar_expect_tx(&full[s], 10 * BOX_BYTES);
+        const uint32_t base = smem_u32(smem + s * WG_STAGE_BYTES);
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) {
+          const int kh = tap / 3, kw = tap - kh * 3;
+          tma_load_4d(base + tap * TAP_BYTES, &ta, &full[s], 0, kw, y0 + kh, b);
+        }
+        tma_load_4d(base + WG_TAPS * TAP_BYTES, &tz, &full[s], 0, 0, y0, b);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 32, true, true);
+      int it = 0;
+      for (int tile = blockIdx.x; tile < tiles; tile += gridDim.x, ++it) {
+        const int s = it & 1, ph = (it >> 1) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t base = smem_u32(smem + s * WG_STAGE_BYTES);
+        const uint32_t b_base = base + WG_TAPS * TAP_BYTES;
+#pragma unroll
+        for (int mt = 0; mt < 3; ++mt)
+#pragma unroll
+          for (int k16 = 0; k16 < 6; ++k16) {
+            const uint32_t a_lo = umma_desc_lo(base + mt * 4 * TAP_BYTES + k16 * 1024, TAP_BYTES);
+            const uint32_t b_lo = umma_desc_lo(b_base + k16 * 1024, TAP_BYTES);
+            umma_bf16_lohi(tmem + mt * 32, a_lo, SW64_DESC_HI, b_lo, SW64_DESC_HI, idesc, it > 0 || k16 > 0);
+          }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(&done);
+    }
+  } else {
+    const int quad = warp & 3;
+    float* dst = partial + (size_t)blockIdx.x * K2 * CH;
+    if (my_tiles > 0) {
+      mbar_wait(&done, 0);
+      tc_fence_after();
+    }
+#pragma unroll
+    for (int mt = 0; mt < 3; ++mt) {
+      uint32_t v[32];
+      if (my_tiles > 0) {
+        tmem_ld32(tmem + (static_cast<uint32_t>(quad * 32) << 16) + mt * 32, v);
+        tmem_ld_wait();
+      }
+      const int m = mt * 128 + quad * 32 + lane;          // = tap*32 + ci
+      if (m < K2) {
+        float4* o = reinterpret_cast<float4*>(dst + (size_t)m * CH);
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          o[c] = my_tiles > 0 ? make_float4(__uint_as_float(v[4 * c]), __uint_as_float(v[4 * c + 1]),
+                                            __uint_as_float(v[4 * c + 2]), __uint_as_float(v[4 * c + 3]))
+                              : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 128);
+}
+
 }  // namespace ddls
 
 using namespace ddls;
@@ -259,4 +368,30 @@ extern "C" int ddls_cnn_conv2_dgrad_tma(const void* dz2, const float* w2, const 
   conv2_tma_kernel<true><<<grid, CV_THREADS, CV_SMEM, static_cast<cudaStream_t>(stream)>>>(tm, p);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "conv2_tma_kernel<dgrad> launch");
+}
+
+namespace ddls {
+__global__ void sum_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int n, int splits);
+}
+
+extern "C" int ddls_cnn_conv2_wgrad_tma(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
+                                        void* stream) {
+  if (B <= 0) return 0;
+  const int tiles = B * 6;
+  const size_t per = (size_t)K2 * CH * sizeof(float);
+  int grid = tiles < conv_sm_count() ? tiles : conv_sm_count();
+  if (scratch == nullptr || scratch_bytes < per) {
+    set_last_error("ddls_cnn_conv2_wgrad_tma: needs at least %zu bytes of scratch (got %zu)", per, scratch_bytes);
+    return 1;
+  }
+  if ((size_t)grid * per > scratch_bytes) grid = (int)(scratch_bytes / per);
+  CUtensorMap ta, tz;
+  if (nhwc_map(&ta, a1, B, C1, C2) || nhwc_map(&tz, dz2, B, C2, C2)) return 1;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  DDLS_CUDA_OK(cudaFuncSetAttribute(conv2_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
+  conv2_wgrad_tma_kernel<<<grid, CV_THREADS, WG_SMEM, st>>>(ta, tz, static_cast<float*>(scratch), tiles);
+  const int n = K2 * CH;
+  sum_partials_kernel<<<(n * 8 + 255) / 256, 256, 0, st>>>(static_cast<const float*>(scratch), dw2, n, grid);
+  count_launch(2);
+  return check_cuda(cudaGetLastError(), "conv2_wgrad_tma launch");
 }

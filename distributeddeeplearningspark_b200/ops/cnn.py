@@ -11,6 +11,7 @@ N.register('ddls_cnn_conv1_fwd', [P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_pool_fwd', [P, P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_pool_fwd_tma', [P, P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_dgrad_tma', [P, P, P, P, I, P])
+N.register('ddls_cnn_conv2_wgrad_tma', [P, P, P, P, N.c_size_t, I, P])
 N.register('ddls_relu_bwd_bias', [P, P, P, P, I, I, I, P])
 N.register('ddls_cnn_unpool_bwd', [P, P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_wgrad', [P, P, P, P, Z, I, P])
@@ -26,6 +27,10 @@ def use_tma() -> bool:
 
 def conv2_fwd_name() -> str:
     return 'ddls_cnn_conv2_pool_fwd_tma' if use_tma() else 'ddls_cnn_conv2_pool_fwd'
+
+
+def conv2_wgrad_name() -> str:
+    return 'ddls_cnn_conv2_wgrad_tma' if use_tma() else 'ddls_cnn_conv2_wgrad'
 
 
 def conv2_dgrad_name() -> str:
@@ -86,7 +91,7 @@ class _CnnTrunk(torch.autograd.Function):
                db2.data_ptr(), B, st)
         ws = workspace(dev, max(N.lib().ddls_cnn_conv2_wgrad_scratch_bytes(B), B * 320 * 4))
         dk2 = torch.empty((3, 3, 32, 32), dtype=torch.float32, device=dev)
-        N.call('ddls_cnn_conv2_wgrad', a1.data_ptr(), dz2.data_ptr(), dk2.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
+        N.call(conv2_wgrad_name(), a1.data_ptr(), dz2.data_ptr(), dk2.data_ptr(), ws.data_ptr(), ws.numel(), B, st)
         dz1 = torch.empty((B, 26, 26, 32), dtype=torch.bfloat16, device=dev)
         N.call(conv2_dgrad_name(), dz2.data_ptr(), k2.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
         g1 = torch.empty(320, dtype=torch.float32, device=dev)

@@ -228,7 +228,7 @@ class DirectStep:
         N.call('ddls_cnn_unpool_bwd', dflat.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), dz2.data_ptr(),
                c2.bias.grad.data_ptr(), B, st)
         ws = workspace(self.dev, max(N.lib().ddls_cnn_conv2_wgrad_scratch_bytes(B), B * 320 * 4))
-        N.call('ddls_cnn_conv2_wgrad', a1.data_ptr(), dz2.data_ptr(), c2.kernel.grad.data_ptr(), ws.data_ptr(),
+        N.call(C.conv2_wgrad_name(), a1.data_ptr(), dz2.data_ptr(), c2.kernel.grad.data_ptr(), ws.data_ptr(),
                ws.numel(), B, st)
         N.call(C.conv2_dgrad_name(), dz2.data_ptr(), c2.kernel.data_ptr(), a1.data_ptr(), dz1.data_ptr(), B, st)
         g1k, g1b = c1.kernel.grad, c1.bias.grad

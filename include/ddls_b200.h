@@ -192,6 +192,10 @@ int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void*
 int ddls_cnn_conv2_pool_fwd_tma(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
                                 void* stream);
 int ddls_cnn_conv2_dgrad_tma(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream);
+/* Weight gradient on the same boxes (MN-major operands, K = pixels); one partial dW per persistent CTA in `scratch`
+ * (at least 36,864 bytes; more lets more CTAs run), summed by a second kernel. */
+int ddls_cnn_conv2_wgrad_tma(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
+                             void* stream);
 /* conv1 gradients: dw1_db1 = [3*3*1*32 kernel gradient | 32 bias gradient] fp32; scratch B*320*4 bytes. */
 int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_db1, void* scratch, size_t scratch_bytes, int B,
                          void* stream);

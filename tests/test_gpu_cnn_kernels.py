@@ -75,14 +75,15 @@ def test_unpool_bwd(dev):
     torch.testing.assert_close(db2, g.sum(dim=(0, 1, 2)), rtol=1e-4, atol=1e-3)
 
 
+@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_wgrad', 'ddls_cnn_conv2_wgrad_tma'])
 @pytest.mark.parametrize('B', [2, 128])
-def test_conv2_wgrad(dev, B):
+def test_conv2_wgrad(dev, B, entry):
     torch.manual_seed(3)
     a1 = torch.relu(torch.randn(B, 26, 26, 32, device=dev)).bfloat16()
     dz2 = (torch.randn(B, 24, 24, 32, device=dev) * (torch.rand(B, 24, 24, 32, device=dev) < 0.25)).bfloat16()
     dw = torch.empty(3, 3, 32, 32, device=dev)
     ws = workspace(dev, N.lib().ddls_cnn_conv2_wgrad_scratch_bytes(B))
-    N.call('ddls_cnn_conv2_wgrad', a1.data_ptr(), dz2.data_ptr(), dw.data_ptr(), ws.data_ptr(), ws.numel(), B,
+    N.call(entry, a1.data_ptr(), dz2.data_ptr(), dw.data_ptr(), ws.data_ptr(), ws.numel(), B,
            N.stream_ptr(dev))
     w = torch.zeros(3, 3, 32, 32, device=dev, requires_grad=True)
     (_conv_ref(a1.float(), w) * dz2.float()).sum().backward()
