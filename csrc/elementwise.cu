@@ -103,7 +103,10 @@ __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p
                                                           size_t n4, float lr, float b1, float b2, float eps,
                                                           float gs, int zero_grads, ShadowSet sh) {
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
-  const float lr_t = lr * sqrtf(1.0f - powf(b2, (float)t)) / (1.0f - powf(b1, (float)t));
+  __shared__ float s_lr_t;                 // two powf per thread cost more than the update itself: one thread computes
+  if (threadIdx.x == 0) s_lr_t = lr * sqrtf(1.0f - powf(b2, (float)t)) / (1.0f - powf(b1, (float)t));
+  __syncthreads();
+  const float lr_t = s_lr_t;
   const float ob1 = 1.0f - b1, ob2 = 1.0f - b2;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     float4 gi = g[i], mi = m[i], vi = v[i], pi = p[i];

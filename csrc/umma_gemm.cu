@@ -310,8 +310,13 @@ template <bool A_MN, bool B_MN>
 static int dispatch_bn_v2(const GemmParams& p, int splits, cudaStream_t st) {
   if (p.N <= 32) return launch_gemm_v2<32, A_MN, B_MN>(p, splits, st);
   if (p.N <= 64) return launch_gemm_v2<64, A_MN, B_MN>(p, splits, st);
-  if (p.N <= 128 || (p.N >= 1024 && p.M < 4096)) return launch_gemm_v2<128, A_MN, B_MN>(p, splits, st);   // wide N, few rows: more CTAs
-  return launch_gemm_v2<256, A_MN, B_MN>(p, splits, st);
+  // These problems are small (the MNIST Dense(225) layer: 0.27 GFLOP per GEMM) and latency-bound: the widest tile that
+  // still spreads the work over ~100 CTAs wins, not the one with the best operand reuse.
+  const int tm = (p.M + GEMM_BM - 1) / GEMM_BM;
+  auto ctas = [&](int bn) { return tm * ((p.N + bn - 1) / bn) * splits; };
+  if (p.N > 128 && ctas(256) >= 96) return launch_gemm_v2<256, A_MN, B_MN>(p, splits, st);
+  if (p.N > 64 && ctas(128) >= 96) return launch_gemm_v2<128, A_MN, B_MN>(p, splits, st);
+  return launch_gemm_v2<64, A_MN, B_MN>(p, splits, st);
 }
 
 template <int BN, bool A_MN, bool B_MN>
