@@ -499,7 +499,7 @@ __global__ void __launch_bounds__(CT, 2) conv2_dgrad_relu_kernel(const __nv_bflo
 // One CTA per image; thread = (tap or bias slot, co); per-image partials written to scratch
 // [B][10][32] and reduced by sum_partials_kernel (no atomics).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(320) conv1_wgrad_kernel(const float* __restrict__ x,
+__global__ void __launch_bounds__(640) conv1_wgrad_kernel(const float* __restrict__ x,
                                                           const __nv_bfloat16* __restrict__ dz1,
                                                           float* __restrict__ partial, int B) {
   extern __shared__ __align__(16) uint8_t smem[];
@@ -510,18 +510,42 @@ __global__ void __launch_bounds__(320) conv1_wgrad_kernel(const float* __restric
   for (int i = threadIdx.x; i < C1 * C1 * CH / 8; i += blockDim.x) reinterpret_cast<uint4*>(sdz)[i] = src[i];
   for (int i = threadIdx.x; i < IMG * IMG; i += blockDim.x) sx[i] = x[(size_t)b * IMG * IMG + i];
   __syncthreads();
-  const int slot = threadIdx.x >> 5, co = threadIdx.x & 31;    // slot 0..8 = tap, 9 = bias
+  // 640 threads: two groups of 320 = (slot, co) split the 26 output rows; four independent accumulators per thread
+  // break the 676-long dependent FMA chain of the first version (13.5 us -> see profiles/kernel_times_mnist_cnn.json)
+  __shared__ float red[320];
+  const int grp = threadIdx.x / 320, t = threadIdx.x - grp * 320;
+  const int slot = t >> 5, co = t & 31;                          // slot 0..8 = tap, 9 = bias
   const int kh = slot / 3, kw = slot - kh * 3;
-  float acc = 0.f;
+  const int ngrp = blockDim.x / 320;
+  const int oh0 = grp * (C1 / 2 + (ngrp == 1 ? C1 / 2 : 0)), oh1 = (ngrp == 1 || grp == 1) ? C1 : C1 / 2;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
   if (slot < 9) {
-    for (int oh = 0; oh < C1; ++oh)
-#pragma unroll 2
-      for (int ow = 0; ow < C1; ++ow)
-        acc = fmaf(sx[(oh + kh) * IMG + ow + kw], __bfloat162float(sdz[(oh * C1 + ow) * CH + co]), acc);
+    for (int oh = oh0; oh < oh1; ++oh) {
+      const float* xr = sx + (oh + kh) * IMG + kw;
+      const __nv_bfloat16* zr = sdz + (size_t)oh * C1 * CH + co;
+#pragma unroll
+      for (int ow = 0; ow < 24; ow += 4) {
+        a0 = fmaf(xr[ow], __bfloat162float(zr[ow * CH]), a0);
+        a1 = fmaf(xr[ow + 1], __bfloat162float(zr[(ow + 1) * CH]), a1);
+        a2 = fmaf(xr[ow + 2], __bfloat162float(zr[(ow + 2) * CH]), a2);
+        a3 = fmaf(xr[ow + 3], __bfloat162float(zr[(ow + 3) * CH]), a3);
+      }
+      a0 = fmaf(xr[24], __bfloat162float(zr[24 * CH]), a0);
+      a1 = fmaf(xr[25], __bfloat162float(zr[25 * CH]), a1);
+    }
   } else {
-    for (int i = 0; i < C1 * C1; ++i) acc += __bfloat162float(sdz[i * CH + co]);
+    for (int i = oh0 * C1; i < oh1 * C1; i += 2) {
+      a0 += __bfloat162float(sdz[i * CH + co]);
+      a1 += __bfloat162float(sdz[(i + 1) * CH + co]);
+    }
   }
-  partial[((size_t)b * 10 + slot) * CH + co] = acc;
+  float acc = (a0 + a1) + (a2 + a3);
+  if (grp == 1) red[t] = acc;
+  __syncthreads();
+  if (grp == 0) {
+    if (ngrp == 2) acc += red[t];
+    partial[((size_t)b * 10 + slot) * CH + co] = acc;
+  }
 }
 
 }  // namespace ddls
@@ -625,7 +649,7 @@ extern "C" int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_
   const int smem = C1 * C1 * CH * 2 + IMG * IMG * 4;
   DDLS_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   float* part = static_cast<float*>(scratch);
-  conv1_wgrad_kernel<<<B, 320, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
+  conv1_wgrad_kernel<<<B, 640, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
   // per-image partial rows are [9*32 dW1 | 32 db1]; the output buffer has the same 320-float layout
   sum_partials_kernel<<<(320 * 8 + 255) / 256, 256, 0, ST(stream)>>>(part, dw1_db1, 320, B);
   count_launch(2);
@@ -683,7 +707,7 @@ extern "C" int ddls_cnn_conv1_wgrad_noalloc(const float* x, const void* dz1, flo
   }
   float* part = g_conv1_scratch_addr[dev];
   const int smem = C1 * C1 * CH * 2 + IMG * IMG * 4;
-  conv1_wgrad_kernel<<<B, 320, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
+  conv1_wgrad_kernel<<<B, 640, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
   sum_partials_kernel<<<(320 * 8 + 255) / 256, 256, 0, ST(stream)>>>(part, dw1_db1, 320, B);
   count_launch(2);
   return check_cuda(cudaGetLastError(), "conv1_wgrad (no-alloc) launch");
