@@ -200,34 +200,32 @@ def main():
             hl = host['labels'][:n_host * B].reshape(n_host, B).pin_memory()
             d_px = torch.empty((B, 784), dtype=torch.uint8, device=dev)
             d_lab = torch.empty((B,), dtype=torch.int64, device=dev)
-            d_x, d_y = engine.input_buffers(pool_x[0], pool_y[0])   # preprocess writes the step's static inputs
             h2d = B * 784 + B * 8
         else:
             hx = host['x'][:n_host * B].reshape(n_host, B, md['seq'], 1).pin_memory()
             hy = host['y'][:n_host * B].reshape(n_host, B, 1).pin_memory()
-            d_x, d_y = engine.input_buffers(pool_x[0], pool_y[0])   # H2D lands in the step's static inputs
             h2d = B * (md['seq'] + 1) * 4
-        loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+        # Public API under test: StepEngine.run_stream — pinned host batches -> copy stream (H2D + on-device
+        # preprocessing) -> captured step graph; the loss of every step is read back (one step behind the launches).
+        if is_mnist:
+            def stage(hb, xs, ys):
+                d_px.copy_(hb[0], non_blocking=True); d_lab.copy_(hb[1], non_blocking=True)
+                mnist_preprocess(d_px, d_lab, out_x=xs, out_y=ys)
 
-        def e2e_step(i):
-            j = i % n_host
-            if is_mnist:
-                d_px.copy_(hp[j], non_blocking=True); d_lab.copy_(hl[j], non_blocking=True)
-                mnist_preprocess(d_px, d_lab, out_x=d_x, out_y=d_y)
-            else:
-                d_x.copy_(hx[j], non_blocking=True); d_y.copy_(hy[j], non_blocking=True)
-            loss = engine.step(d_x, d_y)
-            loss_host.copy_(loss.reshape(1), non_blocking=True)
-            torch.cuda.current_stream(dev).synchronize()
-            return float(loss_host[0])
+            def host_batches(n):
+                return ((hp[i % n_host], hl[i % n_host]) for i in range(n))
+        else:
+            stage = None
 
-        for i in range(max(W, 5)):                  # three eager warm-ups + capture of the (x, y) graph
-            e2e_step(i)
+            def host_batches(n):
+                return ((hx[i % n_host], hy[i % n_host]) for i in range(n))
+
+        engine.run_stream(host_batches(max(W, 6)), pool_x[0], pool_y[0], stage=stage)   # eager warm-ups + both captures
         sync_all()
         t0 = time.perf_counter()
-        for i in range(K):
-            e2e_step(i)
+        e2e_losses = engine.run_stream(host_batches(K), pool_x[0], pool_y[0], stage=stage)
         sync_all()
+        assert len(e2e_losses) == K
         e2e_s = time.perf_counter() - t0
         te = torch.tensor([e2e_s], device=dev)
         if size > 1:

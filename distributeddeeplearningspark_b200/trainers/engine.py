@@ -172,6 +172,78 @@ class StepEngine:
             self._static_y = torch.empty(y_like.shape, dtype=y_like.dtype, device=self.device)
         return self._static_x, self._static_y
 
+    # -- pipelined host feed ------------------------------------------------------------------------------------
+    def run_stream(self, batches, x_like: torch.Tensor, y_like: torch.Tensor, stage=None):
+        """Train on an iterable of pinned HOST batches with the copies pipelined against the compute:
+
+        * two input slots, each with its own captured step graph; the host->device copy (and any on-device
+          preprocessing done by ``stage``) of batch i+1 runs on a copy stream while the graph of batch i executes,
+        * the loss of every step is copied back to pinned host memory, but the host only waits for the loss of step
+          i-1 after it has launched step i — the launch latencies of one step hide behind the execution of another.
+
+        ``stage(host_batch, x_slot, y_slot)`` fills the slot's device tensors (default: ``x_slot.copy_(hb[0]);
+        y_slot.copy_(hb[1])``); it runs with the copy stream current.  ``x_like``/``y_like`` give the shape and dtype
+        of the model inputs.  Host batches must stay alive until their step has run.  Returns the per-step losses."""
+        if not self.cuda:
+            out = []
+            for hb in batches:
+                out.append(float(self._eager_step(hb[0], hb[1])))
+            return out
+        if getattr(self, '_slots', None) is None:
+            self._slots = [dict(x=torch.empty(x_like.shape, dtype=x_like.dtype, device=self.device),
+                                y=torch.empty(y_like.shape, dtype=y_like.dtype, device=self.device),
+                                graph=None, loss=None, ready=torch.cuda.Event(), free=torch.cuda.Event(),
+                                done=torch.cuda.Event(), loss_host=torch.empty(1, dtype=torch.float32).pin_memory())
+                           for _ in range(2)]
+            self._copy_stream = torch.cuda.Stream(device=self.device)
+        if stage is None:
+            def stage(hb, xs, ys):
+                xs.copy_(hb[0], non_blocking=True); ys.copy_(hb[1], non_blocking=True)
+        cur = torch.cuda.current_stream(self.device)
+        losses, prev = [], None
+        for i, hb in enumerate(batches):
+            sl = self._slots[i & 1]
+            with torch.cuda.stream(self._copy_stream):
+                if i >= 2:
+                    self._copy_stream.wait_event(sl['free'])     # the step two batches ago has consumed this slot
+                stage(hb, sl['x'], sl['y'])
+                sl['ready'].record(self._copy_stream)
+            cur.wait_event(sl['ready'])
+            loss = self._slot_step(sl)
+            sl['free'].record(cur)
+            sl['loss_host'].copy_(loss.reshape(1), non_blocking=True)
+            sl['done'].record(cur)
+            if prev is not None:
+                prev['done'].synchronize()
+                losses.append(float(prev['loss_host'][0]))
+            prev = sl
+        if prev is not None:
+            prev['done'].synchronize()
+            losses.append(float(prev['loss_host'][0]))
+        return losses
+
+    def _slot_step(self, sl) -> torch.Tensor:
+        self.steps += 1
+        if hasattr(self._inner, 'refresh_shadows_if_stale'):
+            self._inner.refresh_shadows_if_stale()
+        if not self.use_cuda_graph:
+            return self._eager_step(sl['x'], sl['y'])
+        if sl['graph'] is None:
+            if self._warm < 3:
+                self._warm += 1
+                s = torch.cuda.Stream(device=self.device)
+                s.wait_stream(torch.cuda.current_stream(self.device))
+                with torch.cuda.stream(s):
+                    loss = self._eager_step(sl['x'], sl['y'])
+                torch.cuda.current_stream(self.device).wait_stream(s)
+                return loss
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                sl['loss'] = self._eager_step(sl['x'], sl['y'])
+            sl['graph'] = g
+        sl['graph'].replay()
+        return sl['loss']
+
     # -- device-resident dataset ------------------------------------------------------------------------------
     def attach_dataset(self, X: torch.Tensor, Y: torch.Tensor, batch_size: int, perm: Optional[torch.Tensor] = None) -> None:
         """Keep the (partition of the) training set on the device — the counterpart of the reference's cached

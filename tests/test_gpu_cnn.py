@@ -183,3 +183,27 @@ def test_step_engine_device_dataset_matches_explicit_batches():
     assert ea.dataset_cursor() == 9
     for pa, pb in zip(ma.parameters(), mb.parameters()):
         torch.testing.assert_close(pa, pb, rtol=1e-4, atol=1e-5)
+
+
+def test_step_engine_run_stream_matches_step_by_step():
+    """Pipelined host feed (two input slots / graphs, copy stream, losses read one step behind) == step(x, y)."""
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    dev = torch.device('cuda', 0)
+    torch.manual_seed(1)
+    n, B, T = 11, 32, 25
+    hx = [torch.rand(B, T, 1).pin_memory() for _ in range(n)]
+    hy = [torch.rand(B, 1).pin_memory() for _ in range(n)]
+    ma = ddls.models.nyiso_gru(seed=4).to(dev); mb = ddls.models.nyiso_gru(seed=4).to(dev)
+    ea = StepEngine(ma, optimizer='sgd', loss='mean_squared_error', device=dev, use_cuda_graph=True)
+    eb = StepEngine(mb, optimizer='sgd', loss='mean_squared_error', device=dev, use_cuda_graph=True)
+    la = ea.run_stream(zip(hx, hy), hx[0], hy[0])
+    lb = []
+    for x, y in zip(hx, hy):
+        lb.append(float(eb.step(x.to(dev), y.to(dev))))
+    torch.cuda.synchronize()
+    assert len(la) == n and all(s['graph'] is not None for s in ea._slots)
+    for k, (a, b) in enumerate(zip(la, lb)):
+        assert abs(a - b) <= 1e-4 * max(1.0, abs(b)), (k, a, b)
+    for pa, pb in zip(ma.parameters(), mb.parameters()):
+        torch.testing.assert_close(pa, pb, rtol=1e-4, atol=1e-5)

@@ -18,7 +18,7 @@ for m in $MODELS; do
   grep '^{' gpurun_out/bench_n${N}_$m.log > gpurun_out/bench_n${N}_$m.json
   cut -c1-330 gpurun_out/bench_n${N}_$m.json
 done
-if [ "$N" != 1 ]; then
+if [ "$N" != 1 ] && [ -z "$SKIP_SWEEP" ]; then
   PORT=$((PORT+1))
   launch 400 -m distributeddeeplearningspark_b200.bench.allreduce_sweep --max-mb $SWEEP_MB --graph --out gpurun_out/sweep${TAG}_n$N.json > gpurun_out/sweep${TAG}_n$N.log 2>&1
   tail -12 gpurun_out/sweep${TAG}_n$N.log | cut -c1-400
