@@ -99,3 +99,19 @@ def test_allreduce_trainer_mnist_two_ranks_and_accuracy_eval():
 def test_accuracy_evaluator_counts():
     df = DataFrame({'prediction_index': np.array([1.0, 2, 3, 4]), 'label': np.array([1, 2, 0, 4])})
     assert AccuracyEvaluator('prediction_index', 'label').evaluate(df) == 0.75
+
+
+def test_step_engine_run_stream_cpu_path():
+    """run_stream on CPU degrades to a plain loop over the host batches (same losses as step())."""
+    import torch
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    torch.manual_seed(0)
+    xs = [torch.rand(8, 25, 1) for _ in range(4)]
+    ys = [torch.rand(8, 1) for _ in range(4)]
+    ma, mb = ddls.models.nyiso_gru(seed=2), ddls.models.nyiso_gru(seed=2)
+    ea = StepEngine(ma, optimizer='adagrad', loss='mean_squared_error', device='cpu')
+    eb = StepEngine(mb, optimizer='adagrad', loss='mean_squared_error', device='cpu')
+    la = ea.run_stream(zip(xs, ys), xs[0], ys[0])
+    lb = [float(eb.step(x, y)) for x, y in zip(xs, ys)]
+    assert la == lb and la[-1] < la[0] * 1.5
