@@ -56,6 +56,21 @@ class CollectiveCenter:
         flat_params.copy_(self.center)
         self.rounds += 1
 
+    def elastic_round(self, flat_params: torch.Tensor, alpha: float, active: bool = True) -> None:
+        """Elastic averaging (AEASGD): every worker computes ``E_r = alpha * (W_r - center)``, moves itself towards the
+        center (``W_r -= E_r``) and the center towards the workers (``center += sum_r E_r``).  Unlike a commit/pull
+        round the worker keeps its own weights."""
+        if active:
+            torch.sub(flat_params, self.center, out=self._delta)
+            self._delta.mul_(alpha)
+            flat_params.sub_(self._delta)
+            self.local_commits += 1
+        else:
+            self._delta.zero_()
+        self.comm.allreduce_(self._delta, Sum)
+        self.center.add_(self._delta)
+        self.rounds += 1
+
     def total_updates(self) -> int:
         t = torch.tensor([self.local_commits], dtype=torch.float64, device=self.center.device)
         if self.comm.size > 1:

@@ -82,19 +82,25 @@ def _worker(spec: Dict) -> Dict:
     window = int(spec.get('communication_window', 1))
     center = None
     async_center = False
-    if mode in ('adag', 'dynsgd'):
+    if mode in ('adag', 'dynsgd', 'downpour', 'aeasgd'):
         # GPUs with a peer-memory communicator: asynchronous center in multicast memory (DDLS_ADAG=sync forces
         # the lock-step collective emulation, which is also what CPU/gloo and single-rank runs use)
-        async_center = (type(comm).__name__ == 'PeerMemoryComm' and os.environ.get('DDLS_ADAG', 'async') != 'sync')
+        async_center = (type(comm).__name__ == 'PeerMemoryComm' and os.environ.get('DDLS_ADAG', 'async') != 'sync'
+                        and mode != 'aeasgd')       # the elastic exchange is a lock-step collective
         cls = MulticastCenter if async_center else CollectiveCenter
         center = cls(comm, flat.flat_params, staleness_aware=(mode == 'dynsgd'))
     n_batches = len(feeder)
-    if mode in ('adag', 'dynsgd'):
+    center_modes = ('adag', 'dynsgd', 'downpour', 'aeasgd')
+    avg_every = 0
+    if mode in center_modes:
         my_rounds = n_batches // window
         max_rounds = max(comm.allgather_object(my_rounds))
-    elif mode == 'allreduce':
+    elif mode in ('allreduce', 'averaging'):
         # lock-step collectives: every rank must run the same number of steps
         n_batches = min(comm.allgather_object(n_batches))
+        if mode == 'averaging':                        # weights are averaged at every epoch boundary
+            avg_every = max(1, n_batches // max(1, int(spec['num_epoch'])))
+    alpha = float(spec.get('rho', 5.0)) * float(spec.get('learning_rate', 0.1))
     losses: List[torch.Tensor] = []
     t0 = time.perf_counter()
     it = 0
@@ -107,13 +113,24 @@ def _worker(spec: Dict) -> Dict:
         losses.append(engine.step(xb, batch['y']))
         it += 1
         if center is not None and it % window == 0:
-            center.commit_pull(flat.flat_params, 1.0 / window if mode == 'adag' else 1.0, active=True)
+            if mode == 'aeasgd':
+                center.elastic_round(flat.flat_params, alpha, active=True)
+                engine.notify_params_changed()
+            else:
+                center.commit_pull(flat.flat_params, 1.0 / window if mode == 'adag' else 1.0, active=True)
+        if avg_every and it % avg_every == 0 and size > 1:
+            from ..parallel.comm import Average
+            comm.allreduce_(flat.flat_params, Average)
+            engine.notify_params_changed()
     if center is not None:
         if async_center:
             center.finalize()
         else:
             for _ in range(max_rounds - my_rounds):  # keep peers' collectives matched
-                center.commit_pull(flat.flat_params, 0.0, active=False)
+                if mode == 'aeasgd':
+                    center.elastic_round(flat.flat_params, alpha, active=False)
+                else:
+                    center.commit_pull(flat.flat_params, 0.0, active=False)
         flat.flat_params.copy_(center.center)
         num_updates = center.total_updates()
     else:
@@ -123,7 +140,7 @@ def _worker(spec: Dict) -> Dict:
     elapsed = time.perf_counter() - t0
     hist = torch.stack(losses).float().cpu().tolist() if losses else []
     out = {'rank': rank, 'history': hist, 'num_updates': num_updates, 'elapsed': elapsed, 'steps': it}
-    if rank == 0:
+    if rank == 0 or mode == 'ensemble':
         out['weights'] = model.get_weights()
         if spec.get('checkpoint'):
             from ..ckpt import save_checkpoint
@@ -272,6 +289,74 @@ class DynSGD(ADAG):
                  features_col='features', label_col='label', num_epoch=1, communication_window=5, **kw):
         super().__init__(keras_model, worker_optimizer, loss, metrics, num_workers, batch_size, features_col,
                          label_col, num_epoch, communication_window, **kw)
+
+
+class DOWNPOUR(ADAG):
+    """dist-keras ``DOWNPOUR``: every ``communication_window`` steps a worker commits its accumulated weight change
+    un-normalised (``center += W - W_pulled``) and pulls the center."""
+
+    mode = 'downpour'
+
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), num_workers=2, batch_size=32,
+                 features_col='features', label_col='label', num_epoch=1, communication_window=5, **kw):
+        super().__init__(keras_model, worker_optimizer, loss, metrics, num_workers, batch_size, features_col,
+                         label_col, num_epoch, communication_window, **kw)
+
+
+class AEASGD(ADAG):
+    """dist-keras ``AEASGD`` (asynchronous elastic averaging SGD, run here as lock-step rounds): every
+    ``communication_window`` steps worker and center are pulled towards each other by ``rho * learning_rate`` times
+    their difference."""
+
+    mode = 'aeasgd'
+
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), num_workers=2, batch_size=32,
+                 features_col='features', label_col='label', num_epoch=1, communication_window=32, rho=5.0,
+                 learning_rate=0.1, **kw):
+        super().__init__(keras_model, worker_optimizer, loss, metrics, num_workers, batch_size, features_col,
+                         label_col, num_epoch, communication_window, **kw)
+        self.rho, self.learning_rate = float(rho), float(learning_rate)
+
+    def _spec(self, parts_dir):
+        s = super()._spec(parts_dir)
+        s['rho'], s['learning_rate'] = self.rho, self.learning_rate
+        return s
+
+
+class AveragingTrainer(DistributedTrainer):
+    """dist-keras ``AveragingTrainer``: workers train independently on their partitions and the weights are averaged
+    at every epoch boundary (one allreduce of the flat parameter buffer per epoch)."""
+
+    mode = 'averaging'
+
+    def _count_updates(self, results) -> int:
+        return int(self.num_epoch)
+
+
+class EnsembleTrainer(DistributedTrainer):
+    """dist-keras ``EnsembleTrainer``: ``num_models`` copies of the model are trained independently, one per
+    partition, with no communication; ``train`` returns the list of trained models."""
+
+    mode = 'ensemble'
+
+    def __init__(self, keras_model, worker_optimizer, loss, metrics=('accuracy',), num_models=2, batch_size=32,
+                 features_col='features', label_col='label', num_epoch=1, **kw):
+        kw.pop('num_workers', None)
+        super().__init__(keras_model, worker_optimizer, loss, metrics, num_models, batch_size, features_col,
+                         label_col, num_epoch, **kw)
+        self.num_models = int(num_models)
+
+    def train(self, dataframe: DataFrame, shuffle: bool = False):
+        super().train(dataframe, shuffle)
+        models = []
+        for r in self.worker_results:
+            m = deserialize_model(self.master_model)
+            m.set_weights(r['weights'])
+            models.append(m)
+        return models
+
+    def _count_updates(self, results) -> int:
+        return int(sum(r['steps'] for r in results))
 
 
 class AllreduceTrainer(DistributedTrainer):

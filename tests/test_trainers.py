@@ -75,6 +75,43 @@ def test_adag_two_workers_gloo_update_counter_and_center(cls):
     assert all(np.isfinite(a).all() for a in w1)
 
 
+@pytest.mark.parametrize('name', ['DOWNPOUR', 'AEASGD', 'AveragingTrainer', 'EnsembleTrainer'])
+def test_other_distkeras_trainers_two_workers_gloo(name):
+    """The rest of dist-keras' trainer family on two gloo ranks: the model moves, stays finite, and the bookkeeping
+    (update counter / returned models) has the documented shape."""
+    import os
+    from distributeddeeplearningspark_b200 import trainers as T
+    tr, te, lo, hi = _nyiso_frames(400)
+    model = nyiso_lstm(units=8, seed=0)
+    kw = dict(keras_model=model, worker_optimizer='adagrad', loss='mean_squared_error', batch_size=16, num_epoch=2,
+              features_col='feature_matrix', label_col='labels', backend=LocalBarrierBackend(**ENV_BACKEND), seed=0)
+    if name == 'EnsembleTrainer':
+        t = T.EnsembleTrainer(num_models=2, **kw)
+    elif name == 'AveragingTrainer':
+        t = T.AveragingTrainer(num_workers=2, **kw)
+    else:
+        t = getattr(T, name)(num_workers=2, communication_window=4, **kw)
+    os.environ['DDLS_FORCE_CPU'] = '1'
+    try:
+        out = t.train(tr)
+    finally:
+        os.environ.pop('DDLS_FORCE_CPU', None)
+    w0 = model.get_weights()
+    models = out if name == 'EnsembleTrainer' else [out]
+    assert len(models) == (2 if name == 'EnsembleTrainer' else 1)
+    for m in models:
+        w1 = m.get_weights()
+        assert any(np.abs(a - b).max() > 1e-4 for a, b in zip(w0, w1)) and all(np.isfinite(a).all() for a in w1)
+    if name == 'EnsembleTrainer':
+        assert any(np.abs(a - b).max() > 1e-6 for a, b in zip(models[0].get_weights(), models[1].get_weights()))
+    rows = [len(tr.partition_indices(i, 2)) for i in range(2)]
+    if name in ('DOWNPOUR', 'AEASGD'):
+        assert t.parameter_server.num_updates == _update_count(rows, 2, 16, 4)
+    if name == 'AveragingTrainer':
+        assert t.parameter_server.num_updates == 2
+    assert len(t.get_history()) == 2 and all(len(h) > 0 for h in t.get_history())
+
+
 def test_allreduce_trainer_mnist_two_ranks_and_accuracy_eval():
     df = mnist_like_frame(640, seed=0)
     df = OneHotTransformer(10, 'label', 'label_encoded').transform(df)
