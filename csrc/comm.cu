@@ -119,6 +119,7 @@ struct OptFuse {
   int* step;                  // [completed steps, ticket] as in csrc/elementwise.cu
   float lr, b1, b2, eps;
   int zero_grads;
+  uint64_t nvec;              // vectors the optimizer owns; the message may be longer (metric tail: reduced only)
 };
 
 DDLS_DEVINL void opt_apply(const OptFuse& o, uint64_t i, float (&g)[4], float lr_t) {
@@ -298,7 +299,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(Comm
       acc[0] += v[0]; acc[1] += v[1]; acc[2] += v[2]; acc[3] += v[3];
     }
     float g[4] = {acc[0] * p.scale, acc[1] * p.scale, acc[2] * p.scale, acc[3] * p.scale};
-    if (opt.kind != 0) opt_apply(opt, i, g, lr_t);
+    if (opt.kind != 0 && i < opt.nvec) opt_apply(opt, i, g, lr_t);
     out[i] = make_float4(g[0], g[1], g[2], g[3]);
   }
   // last block out: advance the collective epoch and, with a fused optimizer, its step counter
@@ -590,7 +591,7 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
 }
 
 extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off, uint64_t stage_off, uint64_t stage_bytes,
-                                       uint64_t n, float scale, int wire_bf16, int kind, float* params, float* slot1,
+                                       uint64_t n, uint64_t n_opt, float scale, int wire_bf16, int kind, float* params, float* slot1,
                                        float* slot2, int* step, float lr, float b1, float b2, float eps, int zero_grads,
                                        void* stream) {
   CommCtx c;
@@ -601,8 +602,8 @@ extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off,
     set_last_error("ddls_comm_allreduce_opt: bad optimizer description (kind %d)", kind);
     return 1;
   }
-  if (n % 4 != 0 || (grad_off | stage_off) % 16 != 0 || (reinterpret_cast<uintptr_t>(params) & 15)) {
-    set_last_error("ddls_comm_allreduce_opt: n must be a multiple of 4 and buffers 16-byte aligned");
+  if (n % 4 != 0 || n_opt % 4 != 0 || n_opt > n || (grad_off | stage_off) % 16 != 0 || (reinterpret_cast<uintptr_t>(params) & 15)) {
+    set_last_error("ddls_comm_allreduce_opt: n and n_opt (<= n) must be multiples of 4 and buffers 16-byte aligned");
     return 1;
   }
   const uint64_t parity_bytes = (stage_bytes / 2) & ~static_cast<uint64_t>(15);
@@ -611,7 +612,7 @@ extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off,
     return 1;
   }
   ArParams p{grad_off, grad_off, stage_off, parity_bytes, n, scale};
-  OptFuse o{kind, params, slot1, slot2, step, lr, b1, b2, eps, zero_grads};
+  OptFuse o{kind, params, slot1, slot2, step, lr, b1, b2, eps, zero_grads, n_opt / 4};
   int lb = (int)((n / 4 + COMM_THREADS - 1) / COMM_THREADS);
   if (lb > 64) lb = 64;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

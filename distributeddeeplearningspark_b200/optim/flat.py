@@ -17,7 +17,7 @@ ALIGN_ELEMS = 4  # 16 B of fp32
 
 
 class FlatSpace:
-    def __init__(self, params: Iterable[torch.nn.Parameter], comm=None, with_grads: bool = True):
+    def __init__(self, params: Iterable[torch.nn.Parameter], comm=None, with_grads: bool = True, metric_slots: int = 0):
         self.params: List[torch.nn.Parameter] = [p for p in params if p.requires_grad]
         if not self.params:
             raise ValueError('no trainable parameters')
@@ -36,8 +36,15 @@ class FlatSpace:
         self.numel = off
         alloc = (lambda n: comm.alloc(n, torch.float32)) if (comm is not None and dev.type == 'cuda') \
             else (lambda n: torch.zeros(n, dtype=torch.float32, device=dev))
+        # Optional tail of the GRADIENT buffer (K20 of SURVEY.md §2.5): a few extra fp32 slots that ride along with the
+        # last gradient bucket through the allreduce (so they come back averaged / summed like the gradients) but are
+        # outside the range the optimizer updates and clears.  The parameter buffer has no tail.
+        self.metric_slots = (int(metric_slots) + ALIGN_ELEMS - 1) // ALIGN_ELEMS * ALIGN_ELEMS
+        self.grad_numel = self.numel + self.metric_slots
         self.flat_params = alloc(self.numel)
-        self.flat_grads = alloc(self.numel) if with_grads else None
+        self.flat_grads = alloc(self.grad_numel) if with_grads else None
+        if with_grads and self.metric_slots:
+            self.flat_grads[self.numel:].zero_()
         with torch.no_grad():
             for p, o in zip(self.params, self.offsets):
                 view = self.flat_params[o:o + p.numel()].view(p.shape)
@@ -67,7 +74,12 @@ class FlatSpace:
             p.grad = view
 
     def zero_grads(self) -> None:
-        self.flat_grads.zero_()
+        self.flat_grads[:self.numel].zero_()
+
+    @property
+    def metrics(self) -> Optional[torch.Tensor]:
+        """The metric tail of the gradient buffer (None when ``metric_slots == 0``)."""
+        return self.flat_grads[self.numel:] if (self.flat_grads is not None and self.metric_slots) else None
 
     def segments(self) -> List[Tuple[int, int]]:
         return [(o, p.numel()) for p, o in zip(self.params, self.offsets)]

@@ -24,8 +24,9 @@ from .flat import FlatSpace
 class _FlatOptimizer:
     kind = 'base'
 
-    def __init__(self, params: Iterable[torch.nn.Parameter], comm=None, flat: Optional[FlatSpace] = None):
-        self.flat = flat if flat is not None else FlatSpace(list(params), comm=comm)
+    def __init__(self, params: Iterable[torch.nn.Parameter], comm=None, flat: Optional[FlatSpace] = None,
+                 metric_slots: int = 0):
+        self.flat = flat if flat is not None else FlatSpace(list(params), comm=comm, metric_slots=metric_slots)
         self.device = self.flat.device
         self._step_buf = torch.zeros(2, dtype=torch.int32, device=self.device)  # [steps, kernel ticket]
         self.step_count = self._step_buf[:1]
@@ -108,8 +109,8 @@ class _FlatOptimizer:
 class KerasAdam(_FlatOptimizer):
     kind = 'adam'
 
-    def __init__(self, params, lr=1e-3, beta_1=0.9, beta_2=0.999, epsilon=1e-7, comm=None, flat=None):
-        super().__init__(params, comm=comm, flat=flat)
+    def __init__(self, params, lr=1e-3, beta_1=0.9, beta_2=0.999, epsilon=1e-7, comm=None, flat=None, metric_slots=0):
+        super().__init__(params, comm=comm, flat=flat, metric_slots=metric_slots)
         self.lr, self.beta_1, self.beta_2, self.epsilon = lr, beta_1, beta_2, epsilon
         self.m = torch.zeros_like(self.flat.flat_params)
         self.v = torch.zeros_like(self.flat.flat_params)
@@ -130,7 +131,8 @@ class KerasAdam(_FlatOptimizer):
         self.step_count += 1
         t = int(self.step_count.item())
         lr_t = self.lr * math.sqrt(1.0 - self.beta_2 ** t) / (1.0 - self.beta_1 ** t)
-        g = f.flat_grads * self.grad_scale if self.grad_scale != 1.0 else f.flat_grads
+        fg = f.flat_grads[:f.numel]
+        g = fg * self.grad_scale if self.grad_scale != 1.0 else fg
         self.m.mul_(self.beta_1).add_(g, alpha=1 - self.beta_1)
         self.v.mul_(self.beta_2).addcmul_(g, g, value=1 - self.beta_2)
         f.flat_params.addcdiv_(self.m, self.v.sqrt().add_(self.epsilon), value=-lr_t)
@@ -139,8 +141,8 @@ class KerasAdam(_FlatOptimizer):
 class KerasAdagrad(_FlatOptimizer):
     kind = 'adagrad'
 
-    def __init__(self, params, lr=0.01, epsilon=1e-7, comm=None, flat=None):
-        super().__init__(params, comm=comm, flat=flat)
+    def __init__(self, params, lr=0.01, epsilon=1e-7, comm=None, flat=None, metric_slots=0):
+        super().__init__(params, comm=comm, flat=flat, metric_slots=metric_slots)
         self.lr, self.epsilon = lr, epsilon
         self.acc = torch.zeros_like(self.flat.flat_params)
 
@@ -158,7 +160,8 @@ class KerasAdagrad(_FlatOptimizer):
                                       self._specs, self._nspecs)
             return
         self.step_count += 1
-        g = f.flat_grads * self.grad_scale if self.grad_scale != 1.0 else f.flat_grads
+        fg = f.flat_grads[:f.numel]
+        g = fg * self.grad_scale if self.grad_scale != 1.0 else fg
         self.acc.addcmul_(g, g)
         f.flat_params.addcdiv_(g, self.acc.sqrt().add_(self.epsilon), value=-self.lr)
 
@@ -166,8 +169,8 @@ class KerasAdagrad(_FlatOptimizer):
 class KerasSGD(_FlatOptimizer):
     kind = 'sgd'
 
-    def __init__(self, params, lr=0.01, comm=None, flat=None):
-        super().__init__(params, comm=comm, flat=flat)
+    def __init__(self, params, lr=0.01, comm=None, flat=None, metric_slots=0):
+        super().__init__(params, comm=comm, flat=flat, metric_slots=metric_slots)
         self.lr = lr
 
     def hyper(self):
@@ -180,7 +183,7 @@ class KerasSGD(_FlatOptimizer):
                                   self.zero_grads_in_step, self._specs, self._nspecs)
             return
         self.step_count += 1
-        f.flat_params.add_(f.flat_grads, alpha=-self.lr * self.grad_scale)
+        f.flat_params.add_(f.flat_grads[:f.numel], alpha=-self.lr * self.grad_scale)
 
 
 _BY_NAME = {'adam': KerasAdam, 'adagrad': KerasAdagrad, 'sgd': KerasSGD}

@@ -95,9 +95,11 @@ class DistributedOptimizer:
             self.flat = _GradOnlyFlat(params, self.comm)
             self._generic = True
         self.device = self.flat.device
+        # the gradient buffer may carry a metric tail (FlatSpace.metric_slots) that rides in the top bucket
+        self._grad_numel = getattr(self.flat, 'grad_numel', self.flat.numel)
         bucket_bytes = bucket_bytes or env_int('DDLS_BUCKET_BYTES', 2 << 20)
         self.buckets = [_Bucket(lo, hi, idxs) for lo, hi, idxs in
-                        plan_buckets(self.flat.segments(), max(1, bucket_bytes // 4), self.flat.numel)]
+                        plan_buckets(self.flat.segments(), max(1, bucket_bytes // 4), self._grad_numel)]
         self._bucket_of: Dict[int, _Bucket] = {}
         for b in self.buckets:
             for i in b.params:
@@ -112,13 +114,13 @@ class DistributedOptimizer:
             self.inner.grad_scale = 1.0 / self.backward_passes_per_step
         self._bf16 = None
         if self.compression is Compression.bf16 and self.size > 1:
-            self._bf16 = self.comm.alloc(self.flat.numel, torch.bfloat16)
+            self._bf16 = self.comm.alloc(self._grad_numel, torch.bfloat16)
         # Single-bucket models whose gradients fit the flag-in-data allreduce get allreduce + optimizer in ONE kernel
         # (K12/K13 of SURVEY.md §2.5): the hook then has nothing to launch, step() issues the fused kernel.
         self._fused = (self.size > 1 and not self._generic and len(self.buckets) == 1
                        and self.backward_passes_per_step == 1 and env_int('DDLS_FUSED_OPT', 1) != 0
                        and hasattr(self.comm, 'allreduce_opt_') and getattr(self.inner, 'kind', '') in ('adam', 'adagrad', 'sgd')
-                       and self.buckets[0].lo == 0 and self.buckets[0].hi == self.flat.numel
+                       and self.buckets[0].lo == 0 and self.buckets[0].hi == self._grad_numel
                        and self.comm.can_fuse_optimizer(self.flat.flat_grads))
 
     # ------------------------------------------------------------------ hooks
@@ -197,6 +199,13 @@ class DistributedOptimizer:
             return None
         self.synchronize()
         return self.inner.step() if closure is None else self.inner.step(closure)
+
+    @property
+    def metrics(self) -> Optional[torch.Tensor]:
+        """Metric slots piggy-backed on the top gradient bucket (K20): write local values before ``step()``, read the
+        reduced values (same reduction as the gradients: average by default) after it.  ``None`` unless the wrapped
+        optimizer was built with ``metric_slots=k``."""
+        return getattr(self.flat, 'metrics', None)
 
     def zero_grad(self, set_to_none: bool = False) -> None:
         if self._generic:

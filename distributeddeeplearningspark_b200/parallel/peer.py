@@ -63,7 +63,7 @@ N.register('ddls_mc_import', [I, ctypes.POINTER(ctypes.c_ulonglong)])
 N.register('ddls_mc_add_device', [ctypes.c_ulonglong, I])
 N.register('ddls_mc_bind_and_map', [ctypes.c_ulonglong, ctypes.c_ulonglong, N.c_size_t, I, ctypes.POINTER(P)])
 N.register('ddls_comm_allreduce', [DP, I, U64, U64, U64, U64, U64, F, I, I, P])
-N.register('ddls_comm_allreduce_opt', [DP, U64, U64, U64, U64, F, I, I, P, P, P, P, F, F, F, F, I, P])
+N.register('ddls_comm_allreduce_opt', [DP, U64, U64, U64, U64, U64, F, I, I, P, P, P, P, F, F, F, F, I, P])
 N.register('ddls_comm_broadcast', [DP, U64, U64, I, I, I, P])
 N.register('ddls_comm_allgather', [DP, U64, U64, U64, I, P])
 N.register('ddls_comm_barrier', [DP, P])
@@ -333,7 +333,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
         s1 = opt.m if kind == 1 else (opt.acc if kind == 2 else None)
         s2 = opt.v if kind == 1 else None
         N.call('ddls_comm_allreduce_opt', ctypes.byref(self.desc), self.offset_of(g), self._ll_off, self._ll_bytes,
-               g.numel(), scale, int(wire_bf16), kind, opt.flat.flat_params.data_ptr(), N.ptr(s1), N.ptr(s2),
+               g.numel(), opt.flat.numel, scale, int(wire_bf16), kind, opt.flat.flat_params.data_ptr(), N.ptr(s1), N.ptr(s2),
                opt._step_buf.data_ptr(), opt.lr, getattr(opt, 'beta_1', 0.0), getattr(opt, 'beta_2', 0.0),
                getattr(opt, 'epsilon', 0.0), int(opt.zero_grads_in_step), self._stream())
         torch.autograd.graph.increment_version(g)

@@ -248,9 +248,10 @@ int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64
 /* Flag-in-data allreduce of the gradient range at grad_off FUSED with the optimizer update (kind 1 Keras Adam: slot1 = m,
  * slot2 = v; 2 Adagrad: slot1 = accumulator; 3 SGD): the thread that finishes summing a gradient vector updates the
  * matching parameter vector; `scale` already contains 1/N and the optimizer's gradient scale; step = the optimizer's
- * device counter {steps, ticket}.  With zero_grads the gradient range is cleared, else it holds the reduced gradient. */
+ * device counter {steps, ticket}.  With zero_grads the gradient range is cleared, else it holds the reduced gradient.
+ * n_opt <= n: the optimizer owns the first n_opt elements; the rest of the message (metric slots) is only reduced. */
 int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off, uint64_t stage_off, uint64_t stage_bytes, uint64_t n,
-                            float scale, int wire_bf16, int kind, float* params, float* slot1, float* slot2, int* step,
+                            uint64_t n_opt, float scale, int wire_bf16, int kind, float* params, float* slot1, float* slot2, int* step,
                             float lr, float b1, float b2, float eps, int zero_grads, void* stream);
 int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast, int blocks,
                         void* stream);

@@ -52,6 +52,41 @@ def test_mnist_cnn_two_ranks_gloo(compression, passes):
     assert all(np.isfinite(o['losses']).all() for o in out)
 
 
+def _metric_slots_job():
+    import distributeddeeplearningspark_b200 as ddls
+    ddls.init()
+    r, n = ddls.rank(), ddls.size()
+    outs = {}
+    for slots in (0, 3):
+        torch.manual_seed(11)
+        ps = [torch.nn.Parameter(torch.randn(50)), torch.nn.Parameter(torch.randn(7, 3))]   # 50 -> padded to 52
+        opt = ddls.optim.KerasAdagrad(ps, metric_slots=slots)
+        dopt = ddls.DistributedOptimizer(opt)
+        assert (dopt.metrics is None) == (slots == 0)
+        for k in range(3):
+            torch.manual_seed(100 * k + r)
+            opt.flat.flat_grads[:opt.flat.numel].copy_(torch.randn(opt.flat.numel))
+            if slots:
+                dopt.metrics[0] = float(r + 1 + k)
+                dopt.metrics[1] = 10.0 * (r + 1)
+            dopt.step()
+            if slots:   # averaged like the gradients, not consumed or cleared by the optimizer
+                assert abs(float(dopt.metrics[0]) - (k + (n + 1) / 2.0)) < 1e-6, float(dopt.metrics[0])
+                assert abs(float(dopt.metrics[1]) - 10.0 * (n + 1) / 2.0) < 1e-5
+            opt.zero_grad()
+        outs[slots] = opt.flat.flat_params.clone()
+        assert opt.flat.flat_params.numel() == 76 and opt.flat.flat_grads.numel() == 76 + (4 if slots else 0)
+    return {'rank': r, 'same': bool(torch.equal(outs[0], outs[3])), 'buckets_hi': dopt.buckets[-1].hi}
+
+
+def test_metric_slots_ride_in_the_top_gradient_bucket():
+    """K20: metric slots in the tail of the gradient buffer are reduced with the last bucket and do not disturb the
+    parameter update."""
+    out = spark.run(_metric_slots_job, num_proc=2, backend=LocalBarrierBackend(timeout=300), env=ENV)
+    assert all(o['same'] for o in out)
+    assert max(o['buckets_hi'] for o in out) == 80
+
+
 def test_bucket_plan_is_static_and_tiles_the_flat_space():
     segs, off = [], 0
     for n in (288, 32, 9216, 32, 1036800, 228, 2250, 12):   # MNIST CNN tensors, 4-aligned

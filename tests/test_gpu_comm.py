@@ -204,16 +204,21 @@ def _multi_rank_checks():
         for kind in ('adam', 'adagrad', 'sgd'):
             torch.manual_seed(5)
             ps = [torch.nn.Parameter(torch.randn(1000, device=dev)), torch.nn.Parameter(torch.randn(37, 5, device=dev))]
-            o2 = ddls.optim.get_optimizer(kind, ps, comm=comm)
+            slots = 4 if kind == 'adam' else 0            # K20: metric slots ride in the (single) bucket
+            o2 = ddls.optim.get_optimizer(kind, ps, comm=comm, metric_slots=slots)
             o2.zero_grads_in_step = True
             d2 = ddls.DistributedOptimizer(o2)
             assert bool(d2._fused) == (fused == '1')
             for k in range(5):
                 torch.manual_seed(1000 * k + r)
-                o2.flat.flat_grads.copy_(torch.randn(o2.flat.numel, device=dev))
+                o2.flat.flat_grads[:o2.flat.numel].copy_(torch.randn(o2.flat.numel, device=dev))
+                if slots:
+                    d2.metrics[0] = float(r + k)
                 d2.step()
+                if slots:
+                    assert abs(float(d2.metrics[0]) - (k + (n - 1) / 2.0)) < 1e-5, (fused, float(d2.metrics[0]))
             torch.cuda.synchronize()
-            assert int(o2.step_count.item()) == 5 and float(o2.flat.flat_grads.abs().max()) == 0.0
+            assert int(o2.step_count.item()) == 5 and float(o2.flat.flat_grads[:o2.flat.numel].abs().max()) == 0.0
             finals[(fused, kind)] = o2.flat.flat_params.clone()
     os.environ.pop('DDLS_FUSED_OPT')
     res['fused_err'] = {k: float((finals[('1', k)] - finals[('0', k)]).abs().max()) for k in ('adam', 'adagrad', 'sgd')}
