@@ -167,23 +167,41 @@ class KerasAdagrad(_FlatOptimizer):
 
 
 class KerasSGD(_FlatOptimizer):
+    """Keras SGD: ``v = momentum*v - lr*g; p += v`` (``nesterov``: ``p += momentum*v - lr*g``).  Without momentum the
+    update is one fused kernel; with momentum (dist-keras' EAMSGD workers) it is three torch ops over the flat buffers."""
     kind = 'sgd'
 
-    def __init__(self, params, lr=0.01, comm=None, flat=None, metric_slots=0):
+    def __init__(self, params, lr=0.01, momentum=0.0, nesterov=False, comm=None, flat=None, metric_slots=0):
         super().__init__(params, comm=comm, flat=flat, metric_slots=metric_slots)
-        self.lr = lr
+        self.lr, self.momentum, self.nesterov = lr, float(momentum), bool(nesterov)
+        self.velocity = torch.zeros_like(self.flat.flat_params) if self.momentum else None
 
     def hyper(self):
-        return {'lr': self.lr}
+        return {'lr': self.lr, 'momentum': self.momentum, 'nesterov': self.nesterov}
+
+    def slots(self):
+        return {'velocity': self.velocity} if self.velocity is not None else {}
 
     def _update(self):
         f = self.flat
-        if self._native is not None:
+        if self._native is not None and not self.momentum:
             self._native.sgd_step(f.flat_params, f.flat_grads, self.step_count, self.lr, self.grad_scale,
                                   self.zero_grads_in_step, self._specs, self._nspecs)
             return
         self.step_count += 1
-        f.flat_params.add_(f.flat_grads[:f.numel], alpha=-self.lr * self.grad_scale)
+        g = f.flat_grads[:f.numel]
+        if not self.momentum:
+            f.flat_params.add_(g, alpha=-self.lr * self.grad_scale)
+        else:
+            self.velocity.mul_(self.momentum).add_(g, alpha=-self.lr * self.grad_scale)
+            if self.nesterov:
+                f.flat_params.add_(self.velocity, alpha=self.momentum).add_(g, alpha=-self.lr * self.grad_scale)
+            else:
+                f.flat_params.add_(self.velocity)
+        if self._native is not None:                  # CUDA without the fused kernel: honour the fused contracts
+            if self.zero_grads_in_step:
+                g.zero_()
+            self.refresh_shadows()
 
 
 _BY_NAME = {'adam': KerasAdam, 'adagrad': KerasAdagrad, 'sgd': KerasSGD}

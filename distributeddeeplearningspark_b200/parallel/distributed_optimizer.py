@@ -120,6 +120,7 @@ class DistributedOptimizer:
         self._fused = (self.size > 1 and not self._generic and len(self.buckets) == 1
                        and self.backward_passes_per_step == 1 and env_int('DDLS_FUSED_OPT', 1) != 0
                        and hasattr(self.comm, 'allreduce_opt_') and getattr(self.inner, 'kind', '') in ('adam', 'adagrad', 'sgd')
+                       and not getattr(self.inner, 'momentum', 0.0)
                        and self.buckets[0].lo == 0 and self.buckets[0].hi == self._grad_numel
                        and self.comm.can_fuse_optimizer(self.flat.flat_grads))
 

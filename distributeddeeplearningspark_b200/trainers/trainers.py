@@ -323,6 +323,21 @@ class AEASGD(ADAG):
         return s
 
 
+class EAMSGD(AEASGD):
+    """dist-keras ``EAMSGD``: elastic averaging with momentum SGD workers (``worker_optimizer='sgd'`` with
+    ``momentum``, Nesterov by default as in the paper)."""
+
+    def __init__(self, keras_model, worker_optimizer='sgd', loss='mean_squared_error', metrics=('accuracy',),
+                 num_workers=2, batch_size=32, features_col='features', label_col='label', num_epoch=1,
+                 communication_window=32, rho=5.0, learning_rate=0.1, momentum=0.9, **kw):
+        okw = dict(kw.pop('optimizer_kwargs', None) or {})
+        okw.setdefault('momentum', momentum)
+        okw.setdefault('nesterov', True)
+        super().__init__(keras_model, 'sgd', loss, metrics, num_workers, batch_size, features_col, label_col, num_epoch,
+                         communication_window, rho, learning_rate, optimizer_kwargs=okw, **kw)
+        self.momentum = float(momentum)
+
+
 class AveragingTrainer(DistributedTrainer):
     """dist-keras ``AveragingTrainer``: workers train independently on their partitions and the weights are averaged
     at every epoch boundary (one allreduce of the flat parameter buffer per epoch)."""

@@ -64,3 +64,24 @@ def test_cnn_output_is_softmax_and_flatten_order_hwc():
     out = m(torch.rand(3, 28, 28, 1))
     assert out.shape == (3, 10)
     torch.testing.assert_close(out.sum(-1), torch.ones(3))
+
+
+def test_keras_sgd_momentum_matches_torch_sgd():
+    """KerasSGD with (Nesterov) momentum == torch.optim.SGD for a constant learning rate."""
+    import torch
+    import distributeddeeplearningspark_b200 as ddls
+    for nesterov in (False, True):
+        torch.manual_seed(0)
+        p1 = [torch.nn.Parameter(torch.randn(10)), torch.nn.Parameter(torch.randn(3, 4))]
+        p2 = [torch.nn.Parameter(p.detach().clone()) for p in p1]
+        o1 = ddls.optim.KerasSGD(p1, lr=0.05, momentum=0.9, nesterov=nesterov)
+        o2 = torch.optim.SGD(p2, lr=0.05, momentum=0.9, nesterov=nesterov)
+        for _ in range(5):
+            gs = [torch.randn_like(p) for p in p1]
+            for p, g in zip(p1, gs):
+                p.grad.copy_(g)
+            for p, g in zip(p2, gs):
+                p.grad = g.clone()
+            o1.step(); o2.step()
+        for a, b in zip(p1, p2):
+            torch.testing.assert_close(a.detach(), b.detach(), rtol=1e-5, atol=1e-6)

@@ -75,7 +75,7 @@ def test_adag_two_workers_gloo_update_counter_and_center(cls):
     assert all(np.isfinite(a).all() for a in w1)
 
 
-@pytest.mark.parametrize('name', ['DOWNPOUR', 'AEASGD', 'AveragingTrainer', 'EnsembleTrainer'])
+@pytest.mark.parametrize('name', ['DOWNPOUR', 'AEASGD', 'EAMSGD', 'AveragingTrainer', 'EnsembleTrainer'])
 def test_other_distkeras_trainers_two_workers_gloo(name):
     """The rest of dist-keras' trainer family on two gloo ranks: the model moves, stays finite, and the bookkeeping
     (update counter / returned models) has the documented shape."""
@@ -105,7 +105,7 @@ def test_other_distkeras_trainers_two_workers_gloo(name):
     if name == 'EnsembleTrainer':
         assert any(np.abs(a - b).max() > 1e-6 for a, b in zip(models[0].get_weights(), models[1].get_weights()))
     rows = [len(tr.partition_indices(i, 2)) for i in range(2)]
-    if name in ('DOWNPOUR', 'AEASGD'):
+    if name in ('DOWNPOUR', 'AEASGD', 'EAMSGD'):
         assert t.parameter_server.num_updates == _update_count(rows, 2, 16, 4)
     if name == 'AveragingTrainer':
         assert t.parameter_server.num_updates == 2
