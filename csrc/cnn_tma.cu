@@ -345,7 +345,7 @@ int nhwc_map(CUtensorMap* out, const void* base, int B, int HW, int box_w) {
 }
 }  // namespace
 
-extern "C" int ddls_cnn_conv2_pool_fwd_tma(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
+extern "C" int ddls_cnn_conv2_pool_fwd(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
                                            void* stream) {
   if (B <= 0) return 0;
   CUtensorMap tm;
@@ -358,7 +358,7 @@ extern "C" int ddls_cnn_conv2_pool_fwd_tma(const void* a1, const float* w2, cons
   return check_cuda(cudaGetLastError(), "conv2_tma_kernel<fwd> launch");
 }
 
-extern "C" int ddls_cnn_conv2_dgrad_tma(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream) {
+extern "C" int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream) {
   if (B <= 0) return 0;
   CUtensorMap tm;
   if (nhwc_map(&tm, dz2, B, C2, C1)) return 1;
@@ -374,14 +374,21 @@ namespace ddls {
 __global__ void sum_partials_kernel(const float* __restrict__ partial, float* __restrict__ out, int n, int splits);
 }
 
-extern "C" int ddls_cnn_conv2_wgrad_tma(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
+extern "C" size_t ddls_cnn_conv2_wgrad_scratch_bytes(int B) {
+  // one partial dW (36,864 bytes) per persistent CTA; fewer bytes are accepted and simply run fewer CTAs
+  const int tiles = B * 6;
+  const int grid = tiles < conv_sm_count() ? tiles : conv_sm_count();
+  return (size_t)(grid < 1 ? 1 : grid) * K2 * CH * sizeof(float);
+}
+
+extern "C" int ddls_cnn_conv2_wgrad(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
                                         void* stream) {
   if (B <= 0) return 0;
   const int tiles = B * 6;
   const size_t per = (size_t)K2 * CH * sizeof(float);
   int grid = tiles < conv_sm_count() ? tiles : conv_sm_count();
   if (scratch == nullptr || scratch_bytes < per) {
-    set_last_error("ddls_cnn_conv2_wgrad_tma: needs at least %zu bytes of scratch (got %zu)", per, scratch_bytes);
+    set_last_error("ddls_cnn_conv2_wgrad: needs at least %zu bytes of scratch (got %zu)", per, scratch_bytes);
     return 1;
   }
   if ((size_t)grid * per > scratch_bytes) grid = (int)(scratch_bytes / per);

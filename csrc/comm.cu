@@ -21,6 +21,7 @@
 #include <cstdio>
 
 #include "common.cuh"
+#include "shadow.cuh"
 #include "../include/ddls_b200.h"
 
 namespace ddls {
@@ -108,6 +109,7 @@ struct ArParams {
                               // push call k+1 (other parity, possibly larger n) while a slow one still reads call k
   uint64_t n;                 // elements, multiple of 4
   float scale;
+  int mc_push;                // flag-in-data: push each packet with ONE store through the multicast mapping (all peers at once)
 };
 
 // Optional optimizer epilogue (K12/K13 "fused into the allreduce epilogue"): the thread that has just summed a
@@ -120,6 +122,7 @@ struct OptFuse {
   float lr, b1, b2, eps;
   int zero_grads;
   uint64_t nvec;              // vectors the optimizer owns; the message may be longer (metric tail: reduced only)
+  int advance_step;           // the LAST bucket kernel of a training step publishes step+1 (multi-bucket models)
 };
 
 DDLS_DEVINL void opt_apply(const OptFuse& o, uint64_t i, float (&g)[4], float lr_t) {
@@ -265,18 +268,40 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(Comm
     uint32_t w[4];
     if (F32) { w[0] = __float_as_uint(x.x); w[1] = __float_as_uint(x.y); w[2] = __float_as_uint(x.z); w[3] = __float_as_uint(x.w); }
     else { w[0] = pack_bf16x2(x.x, x.y); w[1] = pack_bf16x2(x.z, x.w); w[2] = 0; w[3] = 0; }
-    for (int d = 1; d < c.world; ++d) {
-      const int r = (rank + d) % c.world;
-      uint4* dst = reinterpret_cast<uint4*>(c.base[r] + p.stage_off) + par * parity_q + (uint64_t)rank * slot_q + i * Q;
+    if (p.mc_push) {
+      // a store to the multicast mapping is replicated by the switch into the same offset of every heap: one 16-byte
+      // store per packet pair instead of N-1 (my own replica of my slot is written too and never read)
+      uint4* dst = reinterpret_cast<uint4*>(c.mc_base + p.stage_off) + par * parity_q + (uint64_t)rank * slot_q + i * Q;
       st_volatile_v4(dst, w[0], epoch, w[1], epoch);
       if (F32) st_volatile_v4(dst + 1, w[2], epoch, w[3], epoch);
+    } else {
+      for (int d = 1; d < c.world; ++d) {
+        const int r = (rank + d) % c.world;
+        uint4* dst = reinterpret_cast<uint4*>(c.base[r] + p.stage_off) + par * parity_q + (uint64_t)rank * slot_q + i * Q;
+        st_volatile_v4(dst, w[0], epoch, w[1], epoch);
+        if (F32) st_volatile_v4(dst + 1, w[2], epoch, w[3], epoch);
+      }
     }
   }
   const uint4* stage = reinterpret_cast<const uint4*>(c.base[rank] + p.stage_off) + par * parity_q;
   for (uint64_t i = first; i < nvec; i += stride) {
     float acc[4] = {0.f, 0.f, 0.f, 0.f};
     const float4 mine = in[i];
-    for (int r = 0; r < c.world; ++r) {                   // fixed rank order => identical bits on every rank
+    // Issue the loads of EVERY peer's packet(s) before testing any flag: up to 14 independent 16-byte loads are in flight
+    // instead of seven dependent poll loops (8 GPUs: 256 KB took 21 us with the serial form).  Packets that have not
+    // landed yet are then re-polled one by one.
+    uint4 pa[MAXR], pb[MAXR];
+#pragma unroll
+    for (int r = 0; r < MAXR; ++r) {
+      if (r < c.world && r != rank) {
+        const uint4* src = stage + (uint64_t)r * slot_q + i * Q;
+        pa[r] = ld_volatile_v4(src);
+        if (F32) pb[r] = ld_volatile_v4(src + 1);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < MAXR; ++r) {                      // fixed rank order => identical bits on every rank
+      if (r >= c.world) break;
       float v[4];
       if (r == rank) {
         if (F32) { v[0] = mine.x; v[1] = mine.y; v[2] = mine.z; v[3] = mine.w; }
@@ -287,9 +312,11 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(Comm
         }
       } else {
         const uint4* src = stage + (uint64_t)r * slot_q + i * Q;
-        const uint4 a = ll_wait(c, src, epoch, rank, r);
+        uint4 a = pa[r];
+        if (a.y != epoch || a.w != epoch) a = ll_wait(c, src, epoch, rank, r);
         if (F32) {
-          const uint4 b = ll_wait(c, src + 1, epoch, rank, r);
+          uint4 b = pb[r];
+          if (b.y != epoch || b.w != epoch) b = ll_wait(c, src + 1, epoch, rank, r);
           v[0] = __uint_as_float(a.x); v[1] = __uint_as_float(a.z); v[2] = __uint_as_float(b.x); v[3] = __uint_as_float(b.z);
         } else {
           v[0] = __uint_as_float(a.x << 16); v[1] = __uint_as_float(a.x & 0xFFFF0000u);
@@ -310,7 +337,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(Comm
     const uint32_t ticket = atomicAdd(seq + 1, 1u);
     if (ticket == gridDim.x - 1) {
       seq[0] = e0 + 2; seq[1] = 0;
-      if (opt.kind != 0) opt.step[0] = t_step;
+      if (opt.kind != 0 && opt.advance_step) opt.step[0] = t_step;
       __threadfence();
     }
   }
@@ -395,6 +422,146 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c,
   }
   peer_barrier(c, rank, blockIdx.x, epoch + 1);
   advance_epoch(c, rank, epoch + 1);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Sharded data-parallel step: reduce-scatter -> Keras optimizer on my 1/N slice -> parameter all-gather, ONE kernel per
+// gradient bucket (the training loop of /root/reference/ddl_mnist_aztk.py:216-219 does commit + pull + optimizer as three
+// host-side phases).
+//
+//   barrier A   every rank's gradients of this bucket are final (and nobody reads this bucket's parameters any more)
+//   my slice    g = scale * sum_ranks(grad)   `multimem.ld_reduce` through the switch (or N peer loads in rank order)
+//               m, v, p update on the slice only: the optimizer pass costs 1/N and its slots are sharded by rank
+//               new parameters -> every replica with ONE `multimem.st` (or N peer stores); the reduced gradient itself
+//               never crosses NVLink again
+//   barrier B   every slice of this block index has landed everywhere
+//   local pass  clear my gradient buffer and refresh my bf16 shadow weights for the slices other ranks own
+//
+// Rank r owns vectors [r*per_rank, (r+1)*per_rank) of the bucket (per_rank = ceil(nvec/world)), independent of the grid,
+// so the host knows which part of the optimizer slots is valid on which rank (checkpoints gather them).  Block b of every
+// rank works on sub-slice b of its rank's slice; barriers pair same-index blocks.
+// ---------------------------------------------------------------------------------------------------------
+struct DpStep {
+  uint64_t grad_off, param_off;   // symmetric offsets of the bucket's first element (fp32) in every heap
+  uint64_t s1_off, s2_off;        // optimizer slots (m | accumulator, v) of the bucket, offsets in MY heap
+  uint64_t n, n_opt;              // elements in the bucket / elements the optimizer owns (rest: metric tail, reduced only)
+  uint64_t elem0;                 // flat parameter index of the bucket's first element (shadow specs use flat indices)
+  int* step;                      // optimizer step counter {steps, ticket}
+  float scale, lr, b1, b2, eps;
+  int kind;                       // 1 adam, 2 adagrad, 3 sgd
+  int zero_grads, advance_step;
+};
+
+DDLS_DEVINL float4 ldcg4(const float4* p) { return __ldcg(p); }
+
+template <bool MC>
+__global__ void __launch_bounds__(COMM_THREADS) dp_step_kernel(CommCtx c, DpStep p, ShadowSet sh) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t e0 = read_epoch(c, rank);
+  const int t_step = *reinterpret_cast<volatile int*>(p.step) + 1;
+  __shared__ float s_lr_t;
+  if (threadIdx.x == 0)
+    s_lr_t = (p.kind == 1) ? p.lr * sqrtf(1.0f - powf(p.b2, (float)t_step)) / (1.0f - powf(p.b1, (float)t_step)) : p.lr;
+  const uint64_t nvec = p.n / 4, nopt = p.n_opt / 4;
+  const uint64_t per_rank = (nvec + c.world - 1) / c.world;
+  const uint64_t per_blk = (per_rank + gridDim.x - 1) / gridDim.x;
+  const uint64_t rlo = min(nvec, (uint64_t)rank * per_rank), rhi = min(nvec, rlo + per_rank);
+  const uint64_t lo = min(rhi, rlo + blockIdx.x * per_blk), hi = min(rhi, lo + per_blk);
+  float4* P = reinterpret_cast<float4*>(c.base[rank] + p.param_off);
+  float4* G = reinterpret_cast<float4*>(c.base[rank] + p.grad_off);
+  float4* S1 = reinterpret_cast<float4*>(c.base[rank] + p.s1_off);
+  float4* S2 = reinterpret_cast<float4*>(c.base[rank] + p.s2_off);
+  peer_barrier(c, rank, blockIdx.x, e0 + 1);
+  const float lr_t = s_lr_t;
+  const float ob1 = 1.0f - p.b1, ob2 = 1.0f - p.b2;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    float4 g;
+    if (MC) {
+      g = multimem_ld_reduce_f32x4(reinterpret_cast<const float*>(c.mc_base + p.grad_off) + 4 * i);
+    } else {
+      g = zero4;
+#pragma unroll
+      for (int r = 0; r < MAXR; ++r) {                      // fixed rank order => every rank would compute the same bits
+        if (r >= c.world) break;
+        const float4 x = ldcg4(reinterpret_cast<const float4*>(c.base[r] + p.grad_off) + i);
+        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
+      }
+    }
+    g.x *= p.scale; g.y *= p.scale; g.z *= p.scale; g.w *= p.scale;
+    if (i < nopt) {
+      float4 pi = P[i];
+      if (p.kind == 1) {
+        float4 mi = S1[i], vi = S2[i];
+        mi.x = p.b1 * mi.x + ob1 * g.x; mi.y = p.b1 * mi.y + ob1 * g.y; mi.z = p.b1 * mi.z + ob1 * g.z; mi.w = p.b1 * mi.w + ob1 * g.w;
+        vi.x = p.b2 * vi.x + ob2 * g.x * g.x; vi.y = p.b2 * vi.y + ob2 * g.y * g.y;
+        vi.z = p.b2 * vi.z + ob2 * g.z * g.z; vi.w = p.b2 * vi.w + ob2 * g.w * g.w;
+        pi.x -= lr_t * mi.x / (sqrtf(vi.x) + p.eps); pi.y -= lr_t * mi.y / (sqrtf(vi.y) + p.eps);
+        pi.z -= lr_t * mi.z / (sqrtf(vi.z) + p.eps); pi.w -= lr_t * mi.w / (sqrtf(vi.w) + p.eps);
+        S1[i] = mi; S2[i] = vi;
+      } else if (p.kind == 2) {
+        float4 ai = S1[i];
+        ai.x += g.x * g.x; ai.y += g.y * g.y; ai.z += g.z * g.z; ai.w += g.w * g.w;
+        pi.x -= p.lr * g.x / (sqrtf(ai.x) + p.eps); pi.y -= p.lr * g.y / (sqrtf(ai.y) + p.eps);
+        pi.z -= p.lr * g.z / (sqrtf(ai.z) + p.eps); pi.w -= p.lr * g.w / (sqrtf(ai.w) + p.eps);
+        S1[i] = ai;
+      } else {
+        pi.x -= p.lr * g.x; pi.y -= p.lr * g.y; pi.z -= p.lr * g.z; pi.w -= p.lr * g.w;
+      }
+      if (MC) {
+        multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.param_off) + 4 * i, pi);
+        if (!p.zero_grads) multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.grad_off) + 4 * i, g);
+      } else {
+#pragma unroll
+        for (int d = 0; d < MAXR; ++d) {
+          if (d >= c.world) break;
+          const int r = (rank + d) % c.world;
+          reinterpret_cast<float4*>(c.base[r] + p.param_off)[i] = pi;
+          if (!p.zero_grads) reinterpret_cast<float4*>(c.base[r] + p.grad_off)[i] = g;
+        }
+      }
+      if (p.zero_grads) G[i] = zero4;           // my replica of MY slice: nobody else reads it
+      const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
+      write_shadows(sh, p.elem0 + 4 * i, pv);
+    } else {                                    // metric tail: the reduced value goes to every replica, nothing is cleared
+      if (MC) {
+        multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.grad_off) + 4 * i, g);
+      } else {
+        for (int r = 0; r < c.world; ++r) reinterpret_cast<float4*>(c.base[r] + p.grad_off)[i] = g;
+      }
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, e0 + 2);
+  // local pass over the sub-slices the OTHER ranks' same-index blocks have just finished
+  if (p.zero_grads || sh.n != 0) {
+    for (int d = 1; d < c.world; ++d) {
+      const int r = (rank + d) % c.world;
+      const uint64_t qlo = min(nvec, (uint64_t)r * per_rank), qhi = min(nvec, qlo + per_rank);
+      const uint64_t l2 = min(qhi, qlo + blockIdx.x * per_blk), h2 = min(min(qhi, l2 + per_blk), nopt);
+#pragma unroll 2
+      for (uint64_t i = l2 + threadIdx.x; i < h2; i += blockDim.x) {
+        if (p.zero_grads) G[i] = zero4;
+        const uint64_t e = p.elem0 + 4 * i;
+        if (sh.n != 0 && e + 4 > sh.lo && e < sh.hi) {
+          const float4 pi = ldcg4(P + i);       // written by a peer through NVLink: read it from L2, not a stale L1 line
+          const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
+          write_shadows(sh, e, pv);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    uint32_t* seq = reinterpret_cast<uint32_t*>(c.base[rank] + c.seq_off);
+    __threadfence();
+    const uint32_t ticket = atomicAdd(seq + 1, 1u);
+    if (ticket == gridDim.x - 1) {
+      seq[0] = e0 + 2; seq[1] = 0;
+      if (p.advance_step) p.step[0] = t_step;
+      __threadfence();
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -546,11 +713,13 @@ static int pick_blocks(uint64_t n, int requested) {
 using namespace ddls;
 
 extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64_t out_off,
-                                   uint64_t stage_off, uint64_t stage_bytes, uint64_t n, float scale, int wire_bf16,
+                                   uint64_t stage_off, uint64_t stage_bytes, uint64_t n, float scale, int wire_flags,
                                    int blocks, void* stream) {
   CommCtx c;
   if (make_ctx(d, &c)) return 1;
   if (n == 0) return 0;
+  const int wire_bf16 = wire_flags & DDLS_WIRE_BF16;
+  const int mc_push = (wire_flags & DDLS_LL_MC_PUSH) && c.mc_base != nullptr && !d->emulate;
   if (n % 4 != 0 || (in_off | out_off | stage_off) % 16 != 0) {
     set_last_error("ddls_comm_allreduce: n must be a multiple of 4 and offsets 16-byte aligned");
     return 1;
@@ -564,7 +733,7 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
       return 1;
     }
   }
-  ArParams p{in_off, out_off, stage_off, parity_bytes, n, scale};
+  ArParams p{in_off, out_off, stage_off, parity_bytes, n, scale, mc_push};
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int nb = pick_blocks(n, blocks);
   switch (algo) {
@@ -591,12 +760,14 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
 }
 
 extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off, uint64_t stage_off, uint64_t stage_bytes,
-                                       uint64_t n, uint64_t n_opt, float scale, int wire_bf16, int kind, float* params, float* slot1,
+                                       uint64_t n, uint64_t n_opt, float scale, int wire_flags, int kind, float* params, float* slot1,
                                        float* slot2, int* step, float lr, float b1, float b2, float eps, int zero_grads,
-                                       void* stream) {
+                                       int advance_step, void* stream) {
   CommCtx c;
   if (make_ctx(d, &c)) return 1;
   if (n == 0) return 0;
+  const int wire_bf16 = wire_flags & DDLS_WIRE_BF16;
+  const int mc_push = (wire_flags & DDLS_LL_MC_PUSH) && c.mc_base != nullptr && !d->emulate;
   if (d->emulate) { set_last_error("ddls_comm_allreduce_opt: not available in emulation mode (one parameter set per rank)"); return 1; }
   if (kind < 1 || kind > 3 || params == nullptr || step == nullptr || (kind <= 2 && slot1 == nullptr) || (kind == 1 && slot2 == nullptr)) {
     set_last_error("ddls_comm_allreduce_opt: bad optimizer description (kind %d)", kind);
@@ -611,13 +782,40 @@ extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off,
     set_last_error("ddls_comm_allreduce_opt: %llu elements do not fit the flag-in-data staging region", (unsigned long long)n);
     return 1;
   }
-  ArParams p{grad_off, grad_off, stage_off, parity_bytes, n, scale};
-  OptFuse o{kind, params, slot1, slot2, step, lr, b1, b2, eps, zero_grads, n_opt / 4};
+  ArParams p{grad_off, grad_off, stage_off, parity_bytes, n, scale, mc_push};
+  OptFuse o{kind, params, slot1, slot2, step, lr, b1, b2, eps, zero_grads, n_opt / 4, advance_step};
   int lb = (int)((n / 4 + COMM_THREADS - 1) / COMM_THREADS);
   if (lb > 64) lb = 64;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   return wire_bf16 ? launch(d, allreduce_oneshot_ll_kernel<__nv_bfloat16>, lb, COMM_THREADS, st, c, p, o)
                    : launch(d, allreduce_oneshot_ll_kernel<float>, lb, COMM_THREADS, st, c, p, o);
+}
+
+extern "C" int ddls_comm_dp_step(const DdlsCommDesc* d, uint64_t grad_off, uint64_t param_off, uint64_t slot1_off,
+                                 uint64_t slot2_off, uint64_t n, uint64_t n_opt, uint64_t elem0, float scale, int kind,
+                                 int* step, float lr, float b1, float b2, float eps, int zero_grads, int advance_step,
+                                 const DdlsShadowSpec* shadows, int n_shadows, int blocks, void* stream) {
+  CommCtx c;
+  if (make_ctx(d, &c)) return 1;
+  if (n == 0) return 0;
+  if (kind < 1 || kind > 3 || step == nullptr) { set_last_error("ddls_comm_dp_step: bad optimizer description (kind %d)", kind); return 1; }
+  if (n % 4 != 0 || n_opt % 4 != 0 || n_opt > n || elem0 % 4 != 0 ||
+      (grad_off | param_off | slot1_off | slot2_off) % 16 != 0) {
+    set_last_error("ddls_comm_dp_step: n, n_opt (<= n), elem0 must be multiples of 4 and offsets 16-byte aligned");
+    return 1;
+  }
+  DpStep p{grad_off, param_off, slot1_off, slot2_off, n, n_opt, elem0, step, scale, lr, b1, b2, eps, kind, zero_grads, advance_step};
+  const ShadowSet sh = make_shadows(shadows, n_shadows);
+  // ~16 KB of my slice per block: the kernel is latency-bound (two flag rounds + one switch round trip), so many blocks
+  // with few vectors each; `blocks` > 0 caps the SMs taken from the backward kernels this overlaps with
+  const uint64_t slice_bytes = (n * 4 + d->world - 1) / d->world;
+  int nb = (int)((slice_bytes + (16 << 10) - 1) / (16 << 10));
+  if (nb < 1) nb = 1;
+  if (nb > MAX_CHANNELS) nb = MAX_CHANNELS;
+  if (blocks > 0 && blocks < nb) nb = blocks;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (c.mc_base != nullptr && !d->emulate) return launch(d, dp_step_kernel<true>, nb, COMM_THREADS, st, c, p, sh);
+  return launch(d, dp_step_kernel<false>, nb, COMM_THREADS, st, c, p, sh);
 }
 
 extern "C" int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast,

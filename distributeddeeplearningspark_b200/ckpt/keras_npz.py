@@ -59,6 +59,9 @@ def save_checkpoint(path: str, model: Sequential, optimizer=None, step: Optional
     if rank is None:
         from .. import runtime
         rank = runtime.rank() if runtime.is_initialized() else 0
+    inner0 = getattr(optimizer, 'inner', optimizer)
+    if inner0 is not None and hasattr(inner0, 'gather_slots'):
+        inner0.gather_slots()           # collective: slots sharded by the data-parallel step kernel are exchanged first
     if rank != 0:
         return None
     npz, js = _paths(path)

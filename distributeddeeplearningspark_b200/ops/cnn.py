@@ -1,4 +1,4 @@
-"""Autograd wrapper for the MNIST CNN trunk kernels (``csrc/cnn.cu`` + the tcgen05 GEMM)."""
+"""Autograd wrapper for the MNIST CNN trunk kernels (``csrc/cnn.cu``, ``csrc/cnn_tma.cu`` + the tcgen05 GEMM)."""
 from __future__ import annotations
 
 import torch
@@ -9,9 +9,6 @@ from .gemm import gemm_bf16, workspace
 P, I, Z = N.c_void_p, N.c_int, N.c_size_t
 N.register('ddls_cnn_conv1_fwd', [P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_pool_fwd', [P, P, P, P, P, I, P])
-N.register('ddls_cnn_conv2_pool_fwd_tma', [P, P, P, P, P, I, P])
-N.register('ddls_cnn_conv2_dgrad_tma', [P, P, P, P, I, P])
-N.register('ddls_cnn_conv2_wgrad_tma', [P, P, P, P, N.c_size_t, I, P])
 N.register('ddls_relu_bwd_bias', [P, P, P, P, I, I, I, P])
 N.register('ddls_cnn_unpool_bwd', [P, P, P, P, P, I, P])
 N.register('ddls_cnn_conv2_wgrad', [P, P, P, P, Z, I, P])
@@ -19,22 +16,17 @@ N.register('ddls_cnn_conv2_dgrad', [P, P, P, P, I, P])
 N.register('ddls_cnn_conv1_wgrad', [P, P, P, P, Z, I, P])
 
 
-def use_tma() -> bool:
-    """Persistent TMA-fed conv2 kernels (csrc/cnn_tma.cu) unless DDLS_CNN_TMA=0 (first generation, csrc/cnn.cu)."""
-    import os
-    return os.environ.get('DDLS_CNN_TMA', '1') != '0'
-
-
 def conv2_fwd_name() -> str:
-    return 'ddls_cnn_conv2_pool_fwd_tma' if use_tma() else 'ddls_cnn_conv2_pool_fwd'
+    return 'ddls_cnn_conv2_pool_fwd'
 
 
 def conv2_wgrad_name() -> str:
-    return 'ddls_cnn_conv2_wgrad_tma' if use_tma() else 'ddls_cnn_conv2_wgrad'
+    return 'ddls_cnn_conv2_wgrad'
 
 
 def conv2_dgrad_name() -> str:
-    return 'ddls_cnn_conv2_dgrad_tma' if use_tma() else 'ddls_cnn_conv2_dgrad'
+    return 'ddls_cnn_conv2_dgrad'
+
 
 FWD_SPLIT_K = 18
 

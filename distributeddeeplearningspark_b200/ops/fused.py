@@ -222,9 +222,11 @@ class DirectStep:
         heads.softmax_xent_raw(a3, d2.kernel, d2.bias, y.contiguous(), None, loss, None, dz3, ld, d2.kernel.grad,
                                d2.bias.grad, d1.bias.grad, True, scr)
         self._ready(d2.bias, d2.kernel, d1.bias)
-        gemm_bf16(flat, dz3[:, :F], a_mn_major=True, b_mn_major=True, out=d1.kernel.grad)
-        self._ready(d1.kernel)                    # 99 % of the gradient bytes: its allreduce overlaps the conv backward
+        # data gradient first: it is the last reader of the bf16 shadow of dense1's kernel, and the bucket kernel launched
+        # by _ready() below may rewrite that shadow (sharded step: reduce-scatter + optimizer + all-gather) on any rank
         gemm_bf16(dz3[:, :F], w1s, out=dflat)
+        gemm_bf16(flat, dz3[:, :F], a_mn_major=True, b_mn_major=True, out=d1.kernel.grad)
+        self._ready(d1.kernel)                    # 99 % of the gradient bytes: its bucket overlaps the conv backward
         N.call('ddls_cnn_unpool_bwd', dflat.data_ptr(), pooled.data_ptr(), pidx.data_ptr(), dz2.data_ptr(),
                c2.bias.grad.data_ptr(), B, st)
         ws = workspace(self.dev, max(N.lib().ddls_cnn_conv2_wgrad_scratch_bytes(B), B * 320 * 4))
@@ -246,25 +248,20 @@ class DirectStep:
         from .. import _native as N
         from . import heads
         from . import recurrent as R
-        from .gemm import gemm_bf16
         p = self.plan
         rnn, dense = p['rnn'], p['dense']
         is_lstm = rnn.keras_class == 'LSTM'
-        G = 4 if is_lstm else 3
         H = R.H
         B, T, _ = x.shape
-        st = N.stream_ptr(self.dev)
         bf, f32 = torch.bfloat16, torch.float32
         x2 = x.reshape(B, T).contiguous()
         O = dense.kernel.shape[1]
         h = self._buf('h', (B, H), f32)
-        hs = self._buf('hs', (T, B, H), bf)
         pred = self._buf('pred', (B, O), f32)
         loss = self._buf('loss', (1,), f32)
         dh = self._buf('dh', (B, H), f32)
-        dz = self._buf('dz', (T, B, G * H), bf)
         k, r, b = rnn.kernel, rnn.recurrent_kernel, rnn.bias
-        if is_lstm and R.use_v2():
+        if is_lstm:
             key = ('lstm_v2', B, T)
             bufs = self._bufs.get(key)
             if bufs is None:
@@ -276,9 +273,7 @@ class DirectStep:
             heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh,
                                 dense.kernel.grad, dense.bias.grad)
             R.lstm_v2_backward(dh, x2, img, gates2, cs2, dz2, k.grad, b.grad, r.grad, B, T, False, hs2)
-            self._ready(dense.bias, dense.kernel, b, r, k)
-            return loss
-        if (not is_lstm) and R.use_v2():
+        else:
             key = ('gru_v2', B, T)
             bufs = self._bufs.get(key)
             if bufs is None:
@@ -290,35 +285,5 @@ class DirectStep:
             heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh,
                                 dense.kernel.grad, dense.bias.grad)
             R.gru_v2_backward(dh, x2, img, zrh2, hprev2, da2, k.grad, b.grad, r.grad, B, T, False, hs2, rh2)
-            self._ready(dense.bias, dense.kernel, b, r, k)
-            return loss
-        if is_lstm:
-            gates = self._buf('gates', (T, B, H, 4), bf)
-            cs = self._buf('cs', (T, B, H), f32)
-            N.call('ddls_lstm128_forward', x2.data_ptr(), k.data_ptr(), r.data_ptr(), b.data_ptr(), h.data_ptr(),
-                   hs.data_ptr(), gates.data_ptr(), cs.data_ptr(), B, T, 0, 1, 0, st)
-        else:
-            rh = self._buf('rh', (T, B, H), bf)
-            gates = self._buf('gates', (T, B, H, 4), f32)
-            N.call('ddls_gru128_forward', x2.data_ptr(), k.data_ptr(), r.data_ptr(), b.data_ptr(), h.data_ptr(),
-                   hs.data_ptr(), rh.data_ptr(), gates.data_ptr(), B, T, 0, 1, 0, st)
-        heads.dense_mse_raw(h, dense.kernel, dense.bias, y.reshape(B, O).contiguous(), pred, loss, dh, dense.kernel.grad,
-                            dense.bias.grad)
-        if is_lstm:
-            N.call('ddls_lstm128_backward', dh.data_ptr(), x2.data_ptr(), r.data_ptr(), gates.data_ptr(), cs.data_ptr(),
-                   dz.data_ptr(), k.grad.data_ptr(), b.grad.data_ptr(), B, T, 0, 0, st)
-        else:
-            N.call('ddls_gru128_backward', dh.data_ptr(), x2.data_ptr(), r.data_ptr(), gates.data_ptr(), dz.data_ptr(),
-                   k.grad.data_ptr(), b.grad.data_ptr(), B, T, 0, 0, st)
-        if T > 1:
-            kk = (T - 1) * B
-            sk = R._wgrad_split(kk)
-            dz2 = dz[1:].reshape(kk, G * H)
-            if is_lstm:
-                gemm_bf16(hs[:T - 1].reshape(kk, H), dz2, a_mn_major=True, b_mn_major=True, split_k=sk, out=r.grad)
-            else:
-                gemm_bf16(hs[:T - 1].reshape(kk, H), dz2[:, :2 * H], a_mn_major=True, b_mn_major=True, split_k=sk,
-                          out=r.grad[:, :2 * H])
-                gemm_bf16(rh[1:].reshape(kk, H), dz2[:, 2 * H:], a_mn_major=True, b_mn_major=True, split_k=sk,
-                          out=r.grad[:, 2 * H:])
+        self._ready(dense.bias, dense.kernel, b, r, k)
         return loss

@@ -1,18 +1,12 @@
-"""Autograd wrappers for the persistent tcgen05 recurrent kernels (``csrc/lstm.cu``, ``csrc/gru.cu``)."""
+"""Autograd wrappers for the persistent tcgen05 recurrent kernels (``csrc/rnn128.cu``)."""
 from __future__ import annotations
 
 import torch
 
 from .. import _native as N
-from .gemm import gemm_bf16
 
 P = N.c_void_p
 I = N.c_int
-N.register('ddls_lstm128_forward', [P, P, P, P, P, P, P, P, I, I, I, I, I, P])
-N.register('ddls_lstm128_backward', [P, P, P, P, P, P, P, P, I, I, I, I, P])
-N.register('ddls_gru128_forward', [P, P, P, P, P, P, P, P, I, I, I, I, I, P])
-N.register('ddls_gru128_backward', [P, P, P, P, P, P, P, I, I, I, I, P])
-
 N.register('ddls_rnn128_pack', [P, P, P, P, I, P])
 N.register('ddls_lstm128_forward_v2', [P, P, P, P, P, P, I, I, I, I, I, P])
 N.register('ddls_lstm128_backward_v2', [P, P, P, P, P, P, P, P, I, I, I, I, P])
@@ -28,11 +22,6 @@ def _tile() -> int:
     """Batch rows per CTA for the v2 kernels (0 = pick by batch size; DDLS_RNN_TILE forces 16/32/64)."""
     import os
     return int(os.environ.get('DDLS_RNN_TILE', '0'))
-
-
-def use_v2() -> bool:
-    import os
-    return os.environ.get('DDLS_RNN_V1', '0') != '1'
 
 
 def pack_image(recurrent, kernel, bias, gates: int, out=None):
@@ -87,10 +76,6 @@ def native_available(x: torch.Tensor, units: int) -> bool:
         return False
     N.lib()  # raises NativeError if the .so is missing
     return True
-
-
-def _wgrad_split(k: int) -> int:
-    return max(1, min(32, k // 64))
 
 
 def gru_v2_buffers(B: int, T: int, dev):
@@ -199,106 +184,9 @@ class _LSTM128v2(torch.autograd.Function):
         return dx, d_wih.view(1, 4 * H), d_rec, d_bias, None
 
 
-class _LSTM128(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, x, kernel, recurrent, bias, return_sequences):
-        B, T, _ = x.shape
-        dev = x.device
-        x2 = x.reshape(B, T).contiguous()
-        need_bwd = any(ctx.needs_input_grad)
-        out = torch.empty((B, T, H) if return_sequences else (B, H), dtype=torch.float32, device=dev)
-        if need_bwd:
-            hs = torch.empty((T, B, H), dtype=torch.bfloat16, device=dev)
-            gates = torch.empty((T, B, H, 4), dtype=torch.bfloat16, device=dev)
-            cs = torch.empty((T, B, H), dtype=torch.float32, device=dev)
-        else:
-            hs = gates = cs = None
-        N.call('ddls_lstm128_forward', x2.data_ptr(), kernel.data_ptr(), recurrent.data_ptr(), bias.data_ptr(),
-               out.data_ptr(), N.ptr(hs), N.ptr(gates), N.ptr(cs), B, T, int(return_sequences), int(need_bwd), 0,
-               N.stream_ptr(dev))
-        if need_bwd:
-            ctx.save_for_backward(x2, kernel, recurrent, hs, gates, cs)
-            ctx.return_sequences = return_sequences
-        return out
-
-    @staticmethod
-    def backward(ctx, dout):
-        x2, kernel, recurrent, hs, gates, cs = ctx.saved_tensors
-        T, B, _ = hs.shape
-        dev = x2.device
-        dout = dout.contiguous()
-        dz = torch.empty((T, B, 4 * H), dtype=torch.bfloat16, device=dev)
-        small = torch.zeros(8 * H, dtype=torch.float32, device=dev)
-        d_wih, d_bias = small[:4 * H], small[4 * H:]
-        N.call('ddls_lstm128_backward', dout.data_ptr(), x2.data_ptr(), recurrent.data_ptr(), gates.data_ptr(),
-               cs.data_ptr(), dz.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(ctx.return_sequences), 0,
-               N.stream_ptr(dev))
-        if T > 1:   # dU[k', col] = sum_{t>=1,b} h_{t-1}[b,k'] * dz_t[b,col]
-            k = (T - 1) * B
-            d_rec = gemm_bf16(hs[:T - 1].reshape(k, H), dz[1:].reshape(k, 4 * H), a_mn_major=True, b_mn_major=True,
-                              split_k=_wgrad_split(k))
-        else:
-            d_rec = torch.zeros_like(recurrent)
-        dx = None
-        if ctx.needs_input_grad[0]:
-            dx = (dz.float() @ kernel.t()).permute(1, 0, 2).contiguous()
-        return dx, d_wih.view(1, 4 * H), d_rec, d_bias, None
-
-
 def lstm_layer(x, kernel, recurrent, bias, return_sequences=False):
-    fn = _LSTM128v2 if use_v2() else _LSTM128
-    return fn.apply(x, kernel, recurrent, bias, bool(return_sequences))
-
-
-class _GRU128(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, x, kernel, recurrent, bias, return_sequences):
-        B, T, _ = x.shape
-        dev = x.device
-        x2 = x.reshape(B, T).contiguous()
-        need_bwd = any(ctx.needs_input_grad)
-        out = torch.empty((B, T, H) if return_sequences else (B, H), dtype=torch.float32, device=dev)
-        if need_bwd:
-            hs = torch.empty((T, B, H), dtype=torch.bfloat16, device=dev)       # h_t
-            rh = torch.empty((T, B, H), dtype=torch.bfloat16, device=dev)       # r_t * h_{t-1}
-            gates = torch.empty((T, B, H, 4), dtype=torch.float32, device=dev)  # z, r, hh, h_{t-1}
-        else:
-            hs = rh = gates = None
-        N.call('ddls_gru128_forward', x2.data_ptr(), kernel.data_ptr(), recurrent.data_ptr(), bias.data_ptr(),
-               out.data_ptr(), N.ptr(hs), N.ptr(rh), N.ptr(gates), B, T, int(return_sequences), int(need_bwd), 0,
-               N.stream_ptr(dev))
-        if need_bwd:
-            ctx.save_for_backward(x2, kernel, recurrent, hs, rh, gates)
-            ctx.return_sequences = return_sequences
-        return out
-
-    @staticmethod
-    def backward(ctx, dout):
-        x2, kernel, recurrent, hs, rh, gates = ctx.saved_tensors
-        T, B, _ = hs.shape
-        dev = x2.device
-        dout = dout.contiguous()
-        da = torch.empty((T, B, 3 * H), dtype=torch.bfloat16, device=dev)    # d(az), d(ar), d(ah)
-        small = torch.zeros(6 * H, dtype=torch.float32, device=dev)
-        d_wih, d_bias = small[:3 * H], small[3 * H:]
-        N.call('ddls_gru128_backward', dout.data_ptr(), x2.data_ptr(), recurrent.data_ptr(), gates.data_ptr(),
-               da.data_ptr(), d_wih.data_ptr(), d_bias.data_ptr(), B, T, int(ctx.return_sequences), 0,
-               N.stream_ptr(dev))
-        d_rec = torch.zeros_like(recurrent)
-        if T > 1:
-            k = (T - 1) * B
-            da2 = da[1:].reshape(k, 3 * H)
-            # dU_z, dU_r: h_{t-1}^T · [daz | dar];  dU_h: (r ⊙ h_{t-1})^T · dah
-            gemm_bf16(hs[:T - 1].reshape(k, H), da2[:, :2 * H], a_mn_major=True, b_mn_major=True,
-                      split_k=_wgrad_split(k), out=d_rec[:, :2 * H])
-            gemm_bf16(rh[1:].reshape(k, H), da2[:, 2 * H:], a_mn_major=True, b_mn_major=True,
-                      split_k=_wgrad_split(k), out=d_rec[:, 2 * H:])
-        dx = None
-        if ctx.needs_input_grad[0]:
-            dx = (da.float() @ kernel.t()).permute(1, 0, 2).contiguous()
-        return dx, d_wih.view(1, 3 * H), d_rec, d_bias, None
+    return _LSTM128v2.apply(x, kernel, recurrent, bias, bool(return_sequences))
 
 
 def gru_layer(x, kernel, recurrent, bias, return_sequences=False):
-    fn = _GRU128v2 if use_v2() else _GRU128
-    return fn.apply(x, kernel, recurrent, bias, bool(return_sequences))
+    return _GRU128v2.apply(x, kernel, recurrent, bias, bool(return_sequences))

@@ -36,6 +36,7 @@ class FlatSpace:
         self.numel = off
         alloc = (lambda n: comm.alloc(n, torch.float32)) if (comm is not None and dev.type == 'cuda') \
             else (lambda n: torch.zeros(n, dtype=torch.float32, device=dev))
+        self._alloc = alloc
         # Optional tail of the GRADIENT buffer (K20 of SURVEY.md §2.5): a few extra fp32 slots that ride along with the
         # last gradient bucket through the allreduce (so they come back averaged / summed like the gradients) but are
         # outside the range the optimizer updates and clears.  The parameter buffer has no tail.
@@ -52,6 +53,11 @@ class FlatSpace:
                 p.data = view
         if with_grads:
             self.attach_grads()
+
+    def new_slot(self) -> torch.Tensor:
+        """A zeroed fp32 buffer shaped like the flat parameters, in the same memory (the symmetric heap when a peer
+        communicator is active: the sharded data-parallel step addresses optimizer slots by heap offset)."""
+        return self._alloc(self.numel)
 
     def attach_grads(self) -> None:
         for p, o in zip(self.params, self.offsets):

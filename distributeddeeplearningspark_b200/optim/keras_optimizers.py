@@ -39,7 +39,14 @@ class _FlatOptimizer:
         self._shadows = []          # [(begin, rows, cols, ld, bf16 tensor)]
         self._shadow_by_param = {}
         self._specs, self._nspecs = None, 0
-        self._seen_param_version = self.flat.flat_params._version
+        self._seen_param_version = self._param_version()
+        self._shard_gather = None   # set by DistributedOptimizer when the sharded step kernel owns the slots
+
+    def gather_slots(self) -> None:
+        """Collective no-op unless a ``DistributedOptimizer`` shards the slots by rank (then: exchange the slices so
+        every rank holds complete m / v / accumulator buffers, e.g. before a checkpoint)."""
+        if self._shard_gather is not None:
+            self._shard_gather()
 
     # bf16 shadow copies of weight matrices, refreshed inside the fused update kernel -------------------
     def add_shadow(self, param: torch.nn.Parameter, ld: Optional[int] = None) -> torch.Tensor:
@@ -61,14 +68,19 @@ class _FlatOptimizer:
         self.refresh_shadows()
         return t
 
+    def _param_version(self) -> int:
+        # FlatSpace re-points every parameter with `p.data = view`, which gives each parameter its OWN version counter:
+        # `p.copy_()` (Sequential.set_weights, load_checkpoint) does not bump the flat buffer's.  Track both.
+        return self.flat.flat_params._version + sum(p._version for p in self.flat.params)
+
     def refresh_shadows(self) -> None:
         if self._nspecs:
             self._native.refresh_shadows(self.flat.flat_params, self._specs, self._nspecs)
-        self._seen_param_version = self.flat.flat_params._version
+        self._seen_param_version = self._param_version()
 
     def refresh_shadows_if_stale(self) -> None:
         """Parameters changed through torch ops since the last refresh (broadcast, set_weights, ADAG pull)?"""
-        if self._nspecs and self.flat.flat_params._version != self._seen_param_version:
+        if self._nspecs and self._param_version() != self._seen_param_version:
             self.refresh_shadows()
 
     # torch.optim-like surface ----------------------------------------------
@@ -112,8 +124,8 @@ class KerasAdam(_FlatOptimizer):
     def __init__(self, params, lr=1e-3, beta_1=0.9, beta_2=0.999, epsilon=1e-7, comm=None, flat=None, metric_slots=0):
         super().__init__(params, comm=comm, flat=flat, metric_slots=metric_slots)
         self.lr, self.beta_1, self.beta_2, self.epsilon = lr, beta_1, beta_2, epsilon
-        self.m = torch.zeros_like(self.flat.flat_params)
-        self.v = torch.zeros_like(self.flat.flat_params)
+        self.m = self.flat.new_slot()
+        self.v = self.flat.new_slot()
 
     def hyper(self):
         return {'lr': self.lr, 'beta_1': self.beta_1, 'beta_2': self.beta_2, 'epsilon': self.epsilon}
@@ -144,7 +156,7 @@ class KerasAdagrad(_FlatOptimizer):
     def __init__(self, params, lr=0.01, epsilon=1e-7, comm=None, flat=None, metric_slots=0):
         super().__init__(params, comm=comm, flat=flat, metric_slots=metric_slots)
         self.lr, self.epsilon = lr, epsilon
-        self.acc = torch.zeros_like(self.flat.flat_params)
+        self.acc = self.flat.new_slot()
 
     def hyper(self):
         return {'lr': self.lr, 'epsilon': self.epsilon}

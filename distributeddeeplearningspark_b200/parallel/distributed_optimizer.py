@@ -29,13 +29,15 @@ class Compression(Enum):
 
 
 class _Bucket:
-    __slots__ = ('lo', 'hi', 'params', 'pending', 'done_event', 'launched')
+    __slots__ = ('lo', 'hi', 'params', 'pending', 'done_event', 'launched', 'll_ok', 'sharded')
 
     def __init__(self, lo, hi, params):
         self.lo, self.hi, self.params = lo, hi, params
         self.pending = len(params)
         self.done_event = None
         self.launched = False
+        self.ll_ok = False
+        self.sharded = False
 
 
 def plan_buckets(segments: List[Tuple[int, int]], bucket_elems: int,
@@ -115,14 +117,75 @@ class DistributedOptimizer:
         self._bf16 = None
         if self.compression is Compression.bf16 and self.size > 1:
             self._bf16 = self.comm.alloc(self._grad_numel, torch.bfloat16)
-        # Single-bucket models whose gradients fit the flag-in-data allreduce get allreduce + optimizer in ONE kernel
-        # (K12/K13 of SURVEY.md §2.5): the hook then has nothing to launch, step() issues the fused kernel.
-        self._fused = (self.size > 1 and not self._generic and len(self.buckets) == 1
-                       and self.backward_passes_per_step == 1 and env_int('DDLS_FUSED_OPT', 1) != 0
+        # Fused data-parallel step (K12/K13/K17 of SURVEY.md §2.5): every bucket's allreduce AND optimizer update is ONE
+        # kernel, launched the moment the bucket's last gradient lands —
+        #   'll'  small buckets: flag-in-data one-shot allreduce, every rank applies the (replicated) update;
+        #   'dp'  large buckets or buckets holding bf16 shadow weights: in-switch reduce-scatter, optimizer on this rank's
+        #         1/N slice (slots sharded by rank), multicast all-gather of the new parameters.
+        # step() then only waits for the buckets; the wrapped optimizer's own kernel never runs.
+        self._fused = (self.size > 1 and not self._generic and env_int('DDLS_FUSED_OPT', 1) != 0
                        and hasattr(self.comm, 'allreduce_opt_') and getattr(self.inner, 'kind', '') in ('adam', 'adagrad', 'sgd')
-                       and not getattr(self.inner, 'momentum', 0.0)
-                       and self.buckets[0].lo == 0 and self.buckets[0].hi == self._grad_numel
-                       and self.comm.can_fuse_optimizer(self.flat.flat_grads))
+                       and not getattr(self.inner, 'momentum', 0.0) and self._plan_fused())
+        self._n_launched = 0
+        if self._fused:
+            self.inner._shard_gather = self.gather_slots
+        # one bucket: nothing to overlap with, the kernel runs on the caller's stream
+        if len(self.buckets) == 1:
+            self.overlap = False
+
+    def _plan_fused(self) -> bool:
+        """Can every bucket run as a fused kernel?  Sets ``_dp_ok`` (sharded kernel usable) and ``_ll_ok`` per bucket."""
+        comm = self.comm
+        self._dp_ok = hasattr(comm, 'dp_step_') and comm.can_shard_step(self.inner) and self._bf16 is None
+        self._dp_min_bytes = env_int('DDLS_DP_STEP_MIN_BYTES', 512 << 10)
+        for b in self.buckets:
+            b.ll_ok = comm.can_fuse_optimizer(self.flat.flat_grads[b.lo:b.hi])
+            if not (b.ll_ok or self._dp_ok):
+                return False
+        return True
+
+    def _bucket_mode(self, b) -> str:
+        """'ll' or 'dp' for bucket ``b`` (decided at launch time: bf16 shadows are registered after construction)."""
+        shadowed = any(beg < b.hi and beg + rows * cols > b.lo for beg, rows, cols, _, _ in getattr(self.inner, '_shadows', ()))
+        if b.ll_ok and not shadowed and ((b.hi - b.lo) * 4 < self._dp_min_bytes or not self._dp_ok):
+            return 'll'
+        if not self._dp_ok:
+            raise RuntimeError('bucket holds bf16 shadow weights but the sharded step kernel is unavailable '
+                               '(parameters, gradients and slots must live in the symmetric heap; bf16 wire unsupported)')
+        return 'dp'
+
+    def _fused_bucket(self, b) -> None:
+        advance = self._n_launched == len(self.buckets)      # the last bucket of the step publishes step+1
+        if self._bucket_mode(b) == 'll':
+            n_opt = max(0, min(b.hi, self.flat.numel) - b.lo)
+            self.comm.allreduce_opt_(self.flat.flat_grads[b.lo:b.hi], self.inner, self.op, wire_bf16=self._bf16 is not None,
+                                     lo=b.lo, n_opt=n_opt, advance=advance)
+        else:
+            self.comm.dp_step_(self.inner, b.lo, b.hi, self.op, advance=advance)
+            b.sharded = True
+
+    def shard_bounds(self, b, rank: Optional[int] = None):
+        """[lo, hi) flat element range of bucket ``b`` whose optimizer slots ``rank`` owns under the sharded kernel."""
+        rank = self.comm.rank if rank is None else rank
+        nvec = (b.hi - b.lo) // 4
+        per = (nvec + self.size - 1) // self.size
+        lo = min(nvec, rank * per); hi = min(nvec, lo + per)
+        return b.lo + 4 * lo, min(b.lo + 4 * hi, self.flat.numel)
+
+    def gather_slots(self) -> None:
+        """Collective: make every rank's optimizer slots complete.  Buckets that ran through the sharded kernel keep
+        m / v / accumulator up to date only on the owner of each slice; before a checkpoint or a state broadcast the
+        slices are exchanged (non-owned parts are zeroed and the ranges summed over the ranks)."""
+        if not self._fused or self.size == 1:
+            return
+        for b in self.buckets:
+            if not getattr(b, 'sharded', False):
+                continue
+            lo, hi = self.shard_bounds(b)
+            top = min(b.hi, self.flat.numel)
+            for t in self.inner.slots().values():
+                t[b.lo:lo].zero_(); t[hi:top].zero_()
+                self.comm.allreduce_(t[b.lo:top], Sum)
 
     # ------------------------------------------------------------------ hooks
     def _on_grad(self, p: torch.Tensor) -> None:
@@ -151,19 +214,19 @@ class DistributedOptimizer:
 
     def _launch(self, b: _Bucket) -> None:
         b.launched = True
-        if self._fused and not getattr(self.inner, '_nspecs', 0):
-            return                                   # reduced and applied by the fused kernel in step()
+        self._n_launched += 1
+        run = self._fused_bucket if self._fused else (lambda bb: self._reduce_range(bb.lo, bb.hi))
         if self.overlap:
             cur = torch.cuda.current_stream(self.device)
             ev = torch.cuda.Event()
             ev.record(cur)
             self._comm_stream.wait_event(ev)
             with torch.cuda.stream(self._comm_stream):
-                self._reduce_range(b.lo, b.hi)
+                run(b)
                 b.done_event = torch.cuda.Event()
                 b.done_event.record(self._comm_stream)
         else:
-            self._reduce_range(b.lo, b.hi)
+            run(b)
 
     # -------------------------------------------------------------- public API
     def synchronize(self) -> None:
@@ -183,6 +246,7 @@ class DistributedOptimizer:
                 self.flat.unpack()
         for b in self.buckets:
             b.pending = len(b.params); b.launched = False; b.done_event = None
+        self._n_launched = 0
 
     def step(self, closure=None):
         self._passes += 1
@@ -193,19 +257,18 @@ class DistributedOptimizer:
             self.flat.gather_stray_grads()
             for b in self.buckets:  # hooks saw foreign tensors; reduce everything now
                 b.launched = False
-        if self._fused and closure is None and not getattr(self.inner, '_nspecs', 0):
-            for b in self.buckets:
-                b.pending = len(b.params); b.launched = False; b.done_event = None
-            self.comm.allreduce_opt_(self.flat.flat_grads, self.inner, self.op, wire_bf16=self._bf16 is not None)
-            return None
         self.synchronize()
+        if self._fused:                      # every bucket kernel has reduced AND applied its range
+            return None if closure is None else closure()
         return self.inner.step() if closure is None else self.inner.step(closure)
 
     @property
     def metrics(self) -> Optional[torch.Tensor]:
-        """Metric slots piggy-backed on the top gradient bucket (K20): write local values before ``step()``, read the
-        reduced values (same reduction as the gradients: average by default) after it.  ``None`` unless the wrapped
-        optimizer was built with ``metric_slots=k``."""
+        """Metric slots piggy-backed on the top gradient bucket (K20): write local values BEFORE ``backward()`` — on a
+        multi-bucket model the bucket that carries the tail is launched from the gradient hook during backward, so a value
+        written between ``backward()`` and ``step()`` (this step's loss, say) misses the collective or races with it; report
+        it one step late instead.  Read the reduced values (same reduction as the gradients: average by default) after
+        ``step()``.  ``None`` unless the wrapped optimizer was built with ``metric_slots=k``."""
         return getattr(self.flat, 'metrics', None)
 
     def zero_grad(self, set_to_none: bool = False) -> None:
@@ -215,6 +278,8 @@ class DistributedOptimizer:
             self.flat.zero_grads()
 
     def state_dict(self):
+        """Collective when slots are sharded (every rank must call it): gathers them first."""
+        self.gather_slots()
         return self.inner.state_dict()
 
     def load_state_dict(self, sd):

@@ -95,6 +95,7 @@ def broadcast_optimizer_state(optimizer, root_rank: int = 0) -> None:
     comm = _comm()
     inner = getattr(optimizer, 'inner', optimizer)
     if isinstance(inner, _FlatOptimizer):
+        inner.gather_slots()            # slots sharded by the data-parallel step kernel: complete them on every rank first
         comm.broadcast_(inner.step_count, root_rank)
         for t in inner.slots().values():
             comm.broadcast_(t, root_rank)

@@ -42,6 +42,7 @@ SEQ_OFF = 2048
 ALIGN = 256
 
 AR_ONESHOT, AR_TWOSHOT, AR_NVLS, AR_ONESHOT_LL = 0, 1, 2, 3
+WIRE_BF16, LL_MC_PUSH = 1, 2                # wire_flags of ddls_comm_allreduce / ddls_comm_allreduce_opt
 LL_MAX_BYTES_DEFAULT = 512 << 10     # flag-in-data one-shot up to this message size (NYISO LSTM: 267 KB of gradients)
 
 
@@ -63,7 +64,8 @@ N.register('ddls_mc_import', [I, ctypes.POINTER(ctypes.c_ulonglong)])
 N.register('ddls_mc_add_device', [ctypes.c_ulonglong, I])
 N.register('ddls_mc_bind_and_map', [ctypes.c_ulonglong, ctypes.c_ulonglong, N.c_size_t, I, ctypes.POINTER(P)])
 N.register('ddls_comm_allreduce', [DP, I, U64, U64, U64, U64, U64, F, I, I, P])
-N.register('ddls_comm_allreduce_opt', [DP, U64, U64, U64, U64, U64, F, I, I, P, P, P, P, F, F, F, F, I, P])
+N.register('ddls_comm_allreduce_opt', [DP, U64, U64, U64, U64, U64, F, I, I, P, P, P, P, F, F, F, F, I, I, P])
+N.register('ddls_comm_dp_step', [DP, U64, U64, U64, U64, U64, U64, U64, F, I, P, F, F, F, F, I, I, P, I, I, P])
 N.register('ddls_comm_broadcast', [DP, U64, U64, I, I, I, P])
 N.register('ddls_comm_allgather', [DP, U64, U64, U64, I, P])
 N.register('ddls_comm_barrier', [DP, P])
@@ -200,6 +202,8 @@ class PeerMemoryComm(Communicator, _HeapBase):
         # CTAs of the bandwidth algorithms (0 = by size, up to 64): fewer leave more SMs to the backward kernels the
         # gradient allreduce overlaps with
         self._ar_blocks = env_int('DDLS_AR_BLOCKS', 0)
+        # flag-in-data packets pushed with one store through the multicast mapping instead of one store per peer
+        self._ll_mc_push = env_int('DDLS_LL_MC_PUSH', 0) != 0
         self._heap_u8[self._ll_off:self._ll_off + self._ll_bytes].zero_()
         torch.cuda.synchronize(device)
         dist.barrier(device_ids=[self.dev_index])
@@ -298,8 +302,8 @@ class PeerMemoryComm(Communicator, _HeapBase):
             a = algo if algo is not None else self.select_algo(n * 4, True, bool(self.mc_base))
             stage, sbytes = self._ensure_stage(n, self.size, a) if a != AR_NVLS else (0, 0)
             blocks = self._ar_blocks if a in (AR_NVLS, AR_TWOSHOT) else 0
-            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, sbytes, n, scale, int(wire_bf16),
-                   blocks, self._stream())
+            N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, sbytes, n, scale,
+                   self._wire_flags(wire_bf16), blocks, self._stream())
             torch.autograd.graph.increment_version(t)     # raw-pointer kernels bypass torch's version counter
             return t
         # not heap-resident: bounce through the scratch region (chunked)
@@ -315,7 +319,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
             a = algo if algo is not None else self.select_algo(m4 * 4, True, bool(self.mc_base))
             stage, sbytes = self._ensure_stage(m4, self.size, a) if a != AR_NVLS else (0, 0)
             N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, self._scratch_off, self._scratch_off, stage, sbytes,
-                   m4, scale, int(wire_bf16), 0, self._stream())
+                   m4, scale, self._wire_flags(wire_bf16), 0, self._stream())
             flat[lo:lo + m].copy_(scratch[:m])
         return t
 
@@ -325,18 +329,51 @@ class PeerMemoryComm(Communicator, _HeapBase):
         return (g.dtype == torch.float32 and n % 4 == 0 and g.is_contiguous() and n <= self._ll_elems
                 and self.offset_of(g) is not None and self.offset_of(g) % 16 == 0)
 
-    def allreduce_opt_(self, g: torch.Tensor, opt, op: ReduceOp = Average, wire_bf16: bool = False) -> None:
-        """Allreduce the flat gradient ``g`` and apply ``opt``'s update (Keras Adam / Adagrad / SGD over the matching
-        flat parameter space) in ONE kernel: the thread that has summed a gradient vector updates its parameters."""
+    def _wire_flags(self, wire_bf16: bool) -> int:
+        return (WIRE_BF16 if wire_bf16 else 0) | (LL_MC_PUSH if (self._ll_mc_push and self.mc_base) else 0)
+
+    def allreduce_opt_(self, g: torch.Tensor, opt, op: ReduceOp = Average, wire_bf16: bool = False,
+                       lo: int = 0, n_opt: Optional[int] = None, advance: bool = True) -> None:
+        """Allreduce the gradient range ``g`` (= flat_grads[lo:lo+len(g)]) and apply ``opt``'s update (Keras Adam /
+        Adagrad / SGD over the matching range of the flat parameter space) in ONE kernel: the thread that has summed a
+        gradient vector updates its parameters.  ``n_opt`` elements of the range belong to the optimizer (the rest is a
+        metric tail that is only reduced); ``advance``: publish step+1 (the last bucket of a step)."""
         kind = {'adam': 1, 'adagrad': 2, 'sgd': 3}[opt.kind]
         scale = opt.grad_scale * ((1.0 / self.size) if op is Average else 1.0)
         s1 = opt.m if kind == 1 else (opt.acc if kind == 2 else None)
         s2 = opt.v if kind == 1 else None
+        n_opt = (opt.flat.numel - lo) if n_opt is None else n_opt
+        sl = lambda t: None if t is None else t[lo:]
         N.call('ddls_comm_allreduce_opt', ctypes.byref(self.desc), self.offset_of(g), self._ll_off, self._ll_bytes,
-               g.numel(), opt.flat.numel, scale, int(wire_bf16), kind, opt.flat.flat_params.data_ptr(), N.ptr(s1), N.ptr(s2),
-               opt._step_buf.data_ptr(), opt.lr, getattr(opt, 'beta_1', 0.0), getattr(opt, 'beta_2', 0.0),
-               getattr(opt, 'epsilon', 0.0), int(opt.zero_grads_in_step), self._stream())
+               g.numel(), n_opt, scale, self._wire_flags(wire_bf16), kind, opt.flat.flat_params[lo:].data_ptr(),
+               N.ptr(sl(s1)), N.ptr(sl(s2)), opt._step_buf.data_ptr(), opt.lr, getattr(opt, 'beta_1', 0.0),
+               getattr(opt, 'beta_2', 0.0), getattr(opt, 'epsilon', 0.0), int(opt.zero_grads_in_step), int(advance),
+               self._stream())
         torch.autograd.graph.increment_version(g)
+
+    def can_shard_step(self, opt) -> bool:
+        """Do ``opt``'s parameters, gradients and slots all live in the symmetric heap (what ``dp_step_`` needs)?"""
+        ts = [opt.flat.flat_params, opt.flat.flat_grads] + list(opt.slots().values())
+        return all(t is not None and t.dtype == torch.float32 and self.offset_of(t) is not None
+                   and self.offset_of(t) % 16 == 0 for t in ts)
+
+    def dp_step_(self, opt, lo: int, hi: int, op: ReduceOp = Average, advance: bool = True, blocks: int = 0) -> None:
+        """Sharded data-parallel step of the gradient bucket ``flat_grads[lo:hi]`` (``ddls_comm_dp_step``): in-switch
+        reduce-scatter, Keras update of this rank's 1/size slice, multicast all-gather of the new parameters, local
+        gradient clearing and bf16 shadow refresh — one kernel.  The slots of the bucket are valid only on the owner
+        of each slice afterwards (``shard_bounds``)."""
+        kind = {'adam': 1, 'adagrad': 2, 'sgd': 3}[opt.kind]
+        f = opt.flat
+        scale = opt.grad_scale * ((1.0 / self.size) if op is Average else 1.0)
+        s1 = opt.m if kind == 1 else (opt.acc if kind == 2 else None)
+        s2 = opt.v if kind == 1 else None
+        n_opt = max(0, min(hi, f.numel) - lo)
+        off = lambda t: 0 if t is None else self.offset_of(t) + 4 * lo
+        N.call('ddls_comm_dp_step', ctypes.byref(self.desc), off(f.flat_grads), off(f.flat_params), off(s1), off(s2),
+               hi - lo, n_opt, lo, scale, kind, opt._step_buf.data_ptr(), opt.lr, getattr(opt, 'beta_1', 0.0),
+               getattr(opt, 'beta_2', 0.0), getattr(opt, 'epsilon', 0.0), int(opt.zero_grads_in_step), int(advance),
+               opt._specs, opt._nspecs, blocks or self._ar_blocks, self._stream())
+        torch.autograd.graph.increment_version(f.flat_grads)
 
     def allreduce_bf16_wire_(self, g: torch.Tensor, _w: torch.Tensor, op: ReduceOp = Average) -> torch.Tensor:
         """fp32 gradients, bf16 on the wire, fp32 accumulate — the cast is fused into the collective."""
@@ -428,6 +465,12 @@ class EmulatedPeerGroup(_HeapBase):
         stage, sbytes = self._ensure_stage(n, self.world, algo)
         N.call('ddls_comm_allreduce', ctypes.byref(self.desc), algo, off, off, stage, sbytes, n, scale, int(wire_bf16),
                blocks, self._stream())
+
+    def dp_step(self, grad_off: int, param_off: int, s1_off: int, s2_off: int, n: int, n_opt: int, elem0: int, scale: float,
+                kind: int, step: torch.Tensor, lr: float, b1: float = 0.0, b2: float = 0.0, eps: float = 1e-7,
+                zero_grads: bool = True, advance: bool = True, specs=None, nspecs: int = 0, blocks: int = 0):
+        N.call('ddls_comm_dp_step', ctypes.byref(self.desc), grad_off, param_off, s1_off, s2_off, n, n_opt, elem0, scale, kind,
+               step.data_ptr(), lr, b1, b2, eps, int(zero_grads), int(advance), specs, nspecs, blocks, self._stream())
 
     def broadcast(self, off: int, nbytes: int, root: int, blocks: int = 0):
         N.call('ddls_comm_broadcast', ctypes.byref(self.desc), off, nbytes, root, 0, blocks, self._stream())

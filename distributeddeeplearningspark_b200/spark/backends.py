@@ -103,9 +103,12 @@ class LocalBarrierBackend:
     """All-or-nothing stage of ``n`` spawned processes on this host."""
 
     def __init__(self, default_parallelism: Optional[int] = None, timeout: float = 600.0,
-                 start_method: str = 'spawn'):
+                 start_method: str = 'spawn', stage_timeout: Optional[float] = None):
+        """``timeout``: longest wait inside one barrier / all_gather for a missing peer.  ``stage_timeout``: optional
+        bound on the whole stage (default: none — a training run may take hours)."""
         self._default = default_parallelism
         self.timeout = float(timeout)
+        self.stage_timeout = float(stage_timeout) if stage_timeout else None
         self.start_method = start_method
 
     def default_parallelism(self) -> int:
@@ -135,7 +138,11 @@ class LocalBarrierBackend:
         done = [False] * n
         gather_buf: dict = {}
         error: Optional[str] = None
-        deadline = time.time() + self.timeout
+        # `timeout` bounds how long ranks may WAIT FOR EACH OTHER in a gather (a missing peer), not how long the stage
+        # runs: a healthy long training run has no pipe traffic for hours.  Total runtime is bounded only by the optional
+        # stage_timeout; rank death is caught by the liveness check below.
+        gather_deadline: Optional[float] = None
+        stage_deadline = (time.time() + self.stage_timeout) if self.stage_timeout else None
         try:
             while not all(done) and error is None:
                 progressed = False
@@ -154,6 +161,8 @@ class LocalBarrierBackend:
                             break
                         progressed = True
                         if kind == 'gather':
+                            if not gather_buf:
+                                gather_deadline = time.time() + self.timeout
                             gather_buf[i] = payload
                             if len(gather_buf) == n - sum(done):
                                 if sum(done):
@@ -163,7 +172,7 @@ class LocalBarrierBackend:
                                 gather_buf.clear()
                                 for cc in conns:
                                     cc.send(('gathered', msgs))
-                                deadline = time.time() + self.timeout
+                                gather_deadline = None
                         elif kind == 'result':
                             results[i] = cloudpickle.loads(payload)
                             done[i] = True
@@ -180,8 +189,12 @@ class LocalBarrierBackend:
                         error = f'rank {i} died (exit code {procs[i].exitcode}) before returning'
                         break
                 if error is None and not progressed:
-                    if time.time() > deadline:
-                        error = f'stage timed out after {self.timeout}s; unfinished ranks: ' \
+                    now = time.time()
+                    if gather_buf and gather_deadline is not None and now > gather_deadline:
+                        error = f'barrier timed out after {self.timeout}s; ranks that never arrived: ' \
+                                f'{[i for i in range(n) if not done[i] and i not in gather_buf]}'
+                    elif stage_deadline is not None and now > stage_deadline:
+                        error = f'stage timed out after {self.stage_timeout}s; unfinished ranks: ' \
                                 f'{[i for i in range(n) if not done[i]]}'
                     else:
                         time.sleep(0.002)

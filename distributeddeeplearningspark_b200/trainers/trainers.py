@@ -110,7 +110,9 @@ def _worker(spec: Dict) -> Dict:
         xb = batch['x']
         if xb.dtype != torch.float32:
             xb = xb.float()
-        losses.append(engine.step(xb, batch['y']))
+        # step() returns the engine's static loss tensor on every CUDA-graph replay: snapshot it (a tiny on-stream copy),
+        # otherwise the history would alias one buffer and read [.., last, last, last]
+        losses.append(engine.step(xb, batch['y']).detach().clone())
         it += 1
         if center is not None and it % window == 0:
             if mode == 'aeasgd':

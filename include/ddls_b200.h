@@ -77,20 +77,8 @@ int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* labels, float* x
 int ddls_gather_batch(const void* X, const void* Y, void* x, void* y, const int* perm, unsigned* cursor, int B, long long N,
                       long long row_x_bytes, long long row_y_bytes, void* stream);
 
-/* ---- persistent LSTM(128) recurrence, tcgen05 (Keras LSTM, /root/reference/ddl_nyiso_aztk.py:249-251) ---
- * x [B,T] fp32 (input dim 1), w_ih [4H], w_hh [H,4H], bias [4H] in Keras layout, gate order i,f,c,o.
- * out [B,H] (last step) or [B,T,H].  When save_for_backward: hs [T,B,H] bf16, gates [T,B,H,4] bf16
- * (post-activation), cs [T,B,H] fp32.  tile = batch rows per CTA (0 = auto; 32/64/128). */
-int ddls_lstm128_forward(const float* x, const float* w_ih, const float* w_hh, const float* bias, float* out,
-                         void* hs, void* gates, float* cs, int B, int T, int return_sequences,
-                         int save_for_backward, int tile, void* stream);
-/* BPTT.  dout [B,H] or [B,T,H].  Writes dz [T,B,4H] bf16 (gate pre-activation gradients, for the
- * recurrent weight-gradient GEMM) and ACCUMULATES d_wih [4H], d_bias [4H] (caller zeroes them). */
-int ddls_lstm128_backward(const float* dout, const float* x, const float* w_hh, const void* gates, const float* cs,
-                          void* dz, float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile,
-                          void* stream);
-
-/* ---- second-generation recurrent kernels (csrc/rnn128.cu) ---------------------------------------------
+/* ---- persistent LSTM(128) / GRU(128) recurrences, tcgen05 (csrc/rnn128.cu; Keras LSTM / GRU of
+ * /root/reference/ddl_nyiso_aztk.py:201-203, 249-251; x [B,T] fp32, gate order i,f,c,o / z,r,h) ------------------
  * ddls_rnn128_pack: recurrent [128, G*128], w_ih [G*128], bias [G*128] (fp32, Keras layout) -> bf16 UMMA
  * image [18][G*16][8][8] (16 hidden k-groups, 1 k-group of input-kernel/bias hi-lo rows, 1 zero k-group);
  * pulled into shared memory by the kernels below with bulk TMA copies. */
@@ -145,16 +133,6 @@ int ddls_lstm_big_seq_bwd(void* dz, const void* u_perm, const void* dout, const 
                           const float* cs, void* sync, int B, int T, int H, void* stream);
 
 
-/* ---- persistent GRU(128) recurrence, tcgen05 (Keras GRU reset_after=False, ddl_nyiso_aztk.py:201-203) ----
- * Gate order z,r,h.  When save_for_backward: hs [T,B,H] bf16 (h_t), rh [T,B,H] bf16 (r_t*h_{t-1}),
- * gates [T,B,H] float4 (z, r, hh, h_{t-1}). */
-int ddls_gru128_forward(const float* x, const float* w_ih, const float* w_hh, const float* bias, float* out, void* hs,
-                        void* rh, void* gates, int B, int T, int return_sequences, int save_for_backward, int tile,
-                        void* stream);
-/* BPTT.  Writes da [T,B,3H] bf16 = d(az), d(ar), d(ah); ACCUMULATES d_wih [3H], d_bias [3H]. */
-int ddls_gru128_backward(const float* dout, const float* x, const float* w_hh, const void* gates, void* da,
-                         float* d_wih, float* d_bias, int B, int T, int return_sequences, int tile, void* stream);
-
 /* ---- fused output heads (forward + backward in one launch) -------------------------------------- */
 /* Dense(H->O, linear) + Keras mean_squared_error (ddl_nyiso_aztk.py:203,207).  y == NULL: pred only.
  * One CTA; every output (pred, loss[1], dh [B,H], dwd [H,O], dbd [O]) is overwritten. */
@@ -173,7 +151,8 @@ int ddls_dense_softmax_xent(const float* a, const float* w, const float* bias, c
 /* ---- MNIST CNN trunk (/root/reference/ddl_mnist_aztk.py:180-190), NHWC, Keras kernel layouts --------
  * conv1+ReLU: x [B,28,28,1] fp32 -> a1 [B,26,26,32] bf16. */
 int ddls_cnn_conv1_fwd(const float* x, const float* w1, const float* b1, void* a1, int B, void* stream);
-/* conv2+bias+ReLU+maxpool 2x2 (tcgen05 implicit GEMM): a1 -> pooled [B,12,12,32] bf16 + arg-max idx u8. */
+/* conv2+bias+ReLU+maxpool 2x2 (csrc/cnn_tma.cu: persistent CTAs, one 4-D TMA box per filter tap with 64-byte swizzle,
+ * tcgen05 implicit GEMM, pool + arg-max in the epilogue): a1 -> pooled [B,12,12,32] bf16 + arg-max idx u8. */
 int ddls_cnn_conv2_pool_fwd(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
                             void* stream);
 /* dz = da*(a>0) as bf16 [B,ldz] (zero padded) and db[f] += sum_b dz  (caller zeroes db). */
@@ -181,21 +160,13 @@ int ddls_relu_bwd_bias(const float* da, const float* a, void* dz, float* db, int
 /* max-pool + ReLU backward: dflat [B,12,12,32] bf16 -> dz2 [B,24,24,32] bf16; db2[c] += sum (caller zeroes). */
 int ddls_cnn_unpool_bwd(const void* dflat, const void* pooled, const void* pidx, void* dz2, float* db2, int B,
                         void* stream);
-/* conv2 weight gradient dw2 [3,3,32,32] fp32 (tcgen05, split over pixels; partial tiles in `scratch`). */
+/* conv2 weight gradient dw2 [3,3,32,32] fp32 on the same TMA boxes (MN-major operands, K = pixels); one partial dW per
+ * persistent CTA in `scratch` (ddls_cnn_conv2_wgrad_scratch_bytes(B) lets every CTA run; at least 36,864 bytes). */
 size_t ddls_cnn_conv2_wgrad_scratch_bytes(int B);
 int ddls_cnn_conv2_wgrad(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
                          void* stream);
-/* conv2 data gradient fused with conv1's ReLU mask: dz1 [B,26,26,32] bf16. */
+/* conv2 data gradient fused with conv1's ReLU mask: dz1 [B,26,26,32] bf16 (zero padding = TMA out-of-bounds fill). */
 int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream);
-/* Second-generation conv2 kernels (csrc/cnn_tma.cu): persistent CTAs, one 4-D TMA box per filter tap (64-byte swizzle)
- * instead of a per-thread im2col gather; same arguments and results as the two functions above. */
-int ddls_cnn_conv2_pool_fwd_tma(const void* a1, const float* w2, const float* b2, void* pooled, void* pidx, int B,
-                                void* stream);
-int ddls_cnn_conv2_dgrad_tma(const void* dz2, const float* w2, const void* a1, void* dz1, int B, void* stream);
-/* Weight gradient on the same boxes (MN-major operands, K = pixels); one partial dW per persistent CTA in `scratch`
- * (at least 36,864 bytes; more lets more CTAs run), summed by a second kernel. */
-int ddls_cnn_conv2_wgrad_tma(const void* a1, const void* dz2, float* dw2, void* scratch, size_t scratch_bytes, int B,
-                             void* stream);
 /* conv1 gradients: dw1_db1 = [3*3*1*32 kernel gradient | 32 bias gradient] fp32; scratch B*320*4 bytes. */
 int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_db1, void* scratch, size_t scratch_bytes, int B,
                          void* stream);
@@ -243,16 +214,30 @@ enum { DDLS_AR_ONESHOT = 0, DDLS_AR_TWOSHOT = 1, DDLS_AR_NVLS = 2, DDLS_AR_ONESH
 /* out = scale * sum_ranks(in) over fp32 [n].  stage_off / stage_bytes: a scratch region in each heap, used as two
  * parity halves of stage_bytes/2 (each must hold world*n wire elements; the halves are fixed so that calls of different
  * sizes never overlap).  wire_bf16: values cross NVLink as bf16 (fp32 accumulate).  blocks = 0 picks by size. */
+#define DDLS_WIRE_BF16 1   /* wire_flags: values cross NVLink as bf16, fp32 accumulate */
+#define DDLS_LL_MC_PUSH 2 /* wire_flags: flag-in-data packets are pushed with one store through the multicast mapping */
 int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_off, uint64_t out_off, uint64_t stage_off,
-                        uint64_t stage_bytes, uint64_t n, float scale, int wire_bf16, int blocks, void* stream);
+                        uint64_t stage_bytes, uint64_t n, float scale, int wire_flags, int blocks, void* stream);
 /* Flag-in-data allreduce of the gradient range at grad_off FUSED with the optimizer update (kind 1 Keras Adam: slot1 = m,
  * slot2 = v; 2 Adagrad: slot1 = accumulator; 3 SGD): the thread that finishes summing a gradient vector updates the
  * matching parameter vector; `scale` already contains 1/N and the optimizer's gradient scale; step = the optimizer's
  * device counter {steps, ticket}.  With zero_grads the gradient range is cleared, else it holds the reduced gradient.
  * n_opt <= n: the optimizer owns the first n_opt elements; the rest of the message (metric slots) is only reduced. */
 int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off, uint64_t stage_off, uint64_t stage_bytes, uint64_t n,
-                            uint64_t n_opt, float scale, int wire_bf16, int kind, float* params, float* slot1, float* slot2, int* step,
-                            float lr, float b1, float b2, float eps, int zero_grads, void* stream);
+                            uint64_t n_opt, float scale, int wire_flags, int kind, float* params, float* slot1, float* slot2, int* step,
+                            float lr, float b1, float b2, float eps, int zero_grads, int advance_step, void* stream);
+/* Sharded data-parallel step of ONE gradient bucket (csrc/comm.cu, dp_step_kernel): reduce-scatter of the bucket's
+ * gradients (multimem.ld_reduce, or peer loads without multicast), the Keras optimizer on this rank's 1/world slice
+ * (rank r owns vectors [r*ceil(nvec/world), ...) of the bucket; its slots at slot*_off in ITS heap are the only valid
+ * ones), and an all-gather of the new parameters by multicast store; then every rank clears its gradient bucket and
+ * refreshes its bf16 shadow weights locally.  All offsets are symmetric heap offsets of the bucket's first element;
+ * elem0 is that element's index in the flat parameter space (shadow specs are in flat indices).  advance_step: only
+ * the last bucket kernel of a training step publishes step+1.  Replaces dist-keras' commit -> pull -> set_weights
+ * cycle (/root/reference/ddl_mnist_aztk.py:216-219 via SURVEY.md E5/E6) for synchronous training. */
+int ddls_comm_dp_step(const DdlsCommDesc* d, uint64_t grad_off, uint64_t param_off, uint64_t slot1_off, uint64_t slot2_off,
+                      uint64_t n, uint64_t n_opt, uint64_t elem0, float scale, int kind, int* step, float lr, float b1,
+                      float b2, float eps, int zero_grads, int advance_step, const DdlsShadowSpec* shadows, int n_shadows,
+                      int blocks, void* stream);
 int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast, int blocks,
                         void* stream);
 int ddls_comm_allgather(const DdlsCommDesc* d, uint64_t in_off, uint64_t out_off, uint64_t chunk_bytes, int blocks,

@@ -36,7 +36,7 @@ def test_conv1_fwd(dev, B):
     assert _rel(a1, ref) < 6e-3
 
 
-@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_pool_fwd', 'ddls_cnn_conv2_pool_fwd_tma'])
+@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_pool_fwd'])
 @pytest.mark.parametrize('B', [3, 128])
 def test_conv2_pool_fwd(dev, B, entry):
     torch.manual_seed(1)
@@ -75,7 +75,7 @@ def test_unpool_bwd(dev):
     torch.testing.assert_close(db2, g.sum(dim=(0, 1, 2)), rtol=1e-4, atol=1e-3)
 
 
-@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_wgrad', 'ddls_cnn_conv2_wgrad_tma'])
+@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_wgrad'])
 @pytest.mark.parametrize('B', [2, 128])
 def test_conv2_wgrad(dev, B, entry):
     torch.manual_seed(3)
@@ -90,7 +90,7 @@ def test_conv2_wgrad(dev, B, entry):
     assert _rel(dw, w.grad) < 5e-3
 
 
-@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_dgrad', 'ddls_cnn_conv2_dgrad_tma'])
+@pytest.mark.parametrize('entry', ['ddls_cnn_conv2_dgrad'])
 @pytest.mark.parametrize('B', [2, 128])
 def test_conv2_dgrad(dev, B, entry):
     torch.manual_seed(4)

@@ -123,6 +123,90 @@ def test_emulated_broadcast_every_root_and_allgather(world):
         assert torch.equal(o, ref)
 
 
+@pytest.mark.parametrize('world', [2, 4, 8])
+@pytest.mark.parametrize('kind', ['adam', 'adagrad', 'sgd'])
+def test_emulated_sharded_dp_step_matches_allreduce_then_optimizer(world, kind):
+    """ddls_comm_dp_step (reduce-scatter -> optimizer on the owner's slice -> parameter all-gather, one kernel) against
+    a plain fp32 restatement: average the ranks' gradients, apply the Keras update."""
+    from distributeddeeplearningspark_b200.ops.optimizer import make_specs
+    dev = torch.device('cuda', 0)
+    g = EmulatedPeerGroup(world, dev)
+    n_opt, tail, elem0 = 50000, 8, 128
+    n = n_opt + tail
+    goff, grads = g.alloc(n)
+    poff, params = g.alloc(n_opt)
+    s1off, s1 = g.alloc(n_opt)
+    s2off, s2 = g.alloc(n_opt)
+    step = torch.zeros(2, dtype=torch.int32, device=dev)
+    rows, cols, ld, mbeg = 37, 225, 232, 1000
+    shadow = torch.zeros((rows, ld), dtype=torch.bfloat16, device=dev)
+    specs, nspecs = make_specs([(elem0 + mbeg, rows, cols, ld, shadow)])
+    torch.manual_seed(world)
+    p_ref = torch.randn(n_opt, device=dev)
+    for p in params:
+        p.copy_(p_ref)
+    m_ref, v_ref = torch.zeros_like(p_ref), torch.zeros_like(p_ref)
+    lr, b1, b2, eps = (1e-3, 0.9, 0.999, 1e-7) if kind == 'adam' else (0.01, 0.0, 0.0, 1e-7)
+    k = {'adam': 1, 'adagrad': 2, 'sgd': 3}[kind]
+    for t in range(1, 4):
+        src = [torch.randn(n, device=dev) for _ in range(world)]
+        for b, s_ in zip(grads, src):
+            b.copy_(s_)
+        g.dp_step(goff, poff, s1off, s2off, n, n_opt, elem0, 1.0 / world, k, step, lr, b1, b2, eps, zero_grads=True,
+                  advance=True, specs=specs, nspecs=nspecs, blocks=(3 if t == 2 else 0))
+        torch.cuda.synchronize()
+        gm = (torch.stack(src).double().sum(0) / world).float()
+        ga = gm[:n_opt]
+        if kind == 'adam':
+            m_ref = b1 * m_ref + (1 - b1) * ga
+            v_ref = b2 * v_ref + (1 - b2) * ga * ga
+            lr_t = lr * (1 - b2 ** t) ** 0.5 / (1 - b1 ** t)
+            p_ref = p_ref - lr_t * m_ref / (v_ref.sqrt() + eps)
+        elif kind == 'adagrad':
+            m_ref = m_ref + ga * ga
+            p_ref = p_ref - lr * ga / (m_ref.sqrt() + eps)
+        else:
+            p_ref = p_ref - lr * ga
+        assert int(step[0]) == t
+        for r in range(world):
+            torch.testing.assert_close(params[r], p_ref, rtol=1e-5, atol=1e-6)
+            assert torch.equal(params[r], params[0])                      # replicas bit-identical
+            assert float(grads[r][:n_opt].abs().max()) == 0.0             # cleared on every rank
+            torch.testing.assert_close(grads[r][n_opt:], gm[n_opt:], rtol=1e-5, atol=1e-6)   # metric tail: reduced, kept
+        # slots are valid on the owner of each slice
+        nvec = n // 4
+        per = (nvec + world - 1) // world
+        for r in range(world):
+            lo, hi = min(nvec, r * per) * 4, min(min(nvec, (r + 1) * per) * 4, n_opt)
+            if kind != 'sgd':
+                torch.testing.assert_close(s1[r][lo:hi], m_ref[lo:hi], rtol=1e-4, atol=1e-6)
+            if kind == 'adam':
+                torch.testing.assert_close(s2[r][lo:hi], v_ref[lo:hi], rtol=1e-4, atol=1e-7)
+        want = params[0][mbeg - 0:mbeg + rows * cols].view(rows, cols).bfloat16()
+        assert torch.equal(shadow[:, :cols], want) and float(shadow[:, cols:].float().abs().max()) == 0.0
+
+
+def test_emulated_sharded_dp_step_two_buckets_share_one_step_counter():
+    """Two bucket kernels per training step: only the last one publishes step+1, both see the same Adam t."""
+    dev = torch.device('cuda', 0)
+    world = 4
+    g = EmulatedPeerGroup(world, dev)
+    n = 4096
+    offs = [g.alloc(n) for _ in range(4)]         # grads, params, m, v
+    step = torch.zeros(2, dtype=torch.int32, device=dev)
+    for t in range(1, 4):
+        for b in offs[0][1]:
+            b.fill_(1.0)
+        half = n // 2
+        for lo, adv in ((half, False), (0, True)):
+            o = [x[0] + 4 * lo for x in offs]
+            g.dp_step(o[0], o[1], o[2], o[3], half, half, lo, 1.0 / world, 1, step, 1e-3, 0.9, 0.999, 1e-7, advance=adv)
+        torch.cuda.synchronize()
+        assert int(step[0]) == t
+        p = offs[1][1][0]
+        assert float((p[:half] - p[half:]).abs().max()) == 0.0          # both halves took the same bias correction
+
+
 # --------------------------------------------------------------------------------------------------------
 # real multi-process, multi-GPU
 # --------------------------------------------------------------------------------------------------------
@@ -152,6 +236,21 @@ def _multi_rank_checks():
             chk = [torch.empty_like(t) for _ in range(n)]
             dist.all_gather(chk, t)
             assert all(torch.equal(chk[0], c) for c in chk), ('replicas differ', numel, algo)
+    # flag-in-data packets pushed through the multicast mapping (one store reaches every peer): many back-to-back calls
+    # over both parities, checked against the per-peer push
+    if comm.mc_base:
+        t = comm.alloc(16384 + 4)
+        bad = 0
+        for it in range(300):
+            torch.manual_seed(1000 + 17 * it + r)
+            src = torch.randn(t.numel(), device=dev)
+            comm._ll_mc_push = True
+            t.copy_(src); comm.allreduce_(t, ddls.Sum, algo=AR_ONESHOT_LL); a = t.clone()
+            comm._ll_mc_push = False
+            t.copy_(src); comm.allreduce_(t, ddls.Sum, algo=AR_ONESHOT_LL)
+            bad += int(not torch.equal(a, t))
+        res['ll_mc_push_mismatches'] = bad
+        comm._ll_mc_push = False
     # non-heap tensor path + average + odd size
     x = torch.full((1001,), float(r + 1), device=dev)
     ddls.allreduce_(x)
@@ -224,6 +323,73 @@ def _multi_rank_checks():
     res['fused_err'] = {k: float((finals[('1', k)] - finals[('0', k)]).abs().max()) for k in ('adam', 'adagrad', 'sgd')}
     res['fused_matches'] = all(v < 1e-6 for v in res['fused_err'].values())
     torch.cuda.synchronize()
+    res.update(_sharded_step_checks(ddls, comm, dev, r, n))
+    return res
+
+
+def _sharded_step_checks(ddls, comm, dev, r, n):
+    """Multi-bucket fused data parallelism: the big bucket runs the sharded kernel (multimem reduce-scatter -> optimizer on
+    the owner's slice -> multicast parameter all-gather), the small one the flag-in-data kernel; compared with the unfused
+    path (allreduce kernels + one optimizer kernel) on identical gradients."""
+    import os
+    import torch.distributed as dist
+    res = {}
+    finals, slots = {}, {}
+    for fused in ('1', '0'):
+        os.environ['DDLS_FUSED_OPT'] = fused
+        for kind in ('adam', 'adagrad'):
+            torch.manual_seed(7)
+            ps = [torch.nn.Parameter(torch.randn(3000, device=dev)), torch.nn.Parameter(torch.randn(37, 5, device=dev)),
+                  torch.nn.Parameter(torch.randn(2600, 225, device=dev))]      # 585,000 elements: its own >2 MB bucket
+            o2 = ddls.optim.get_optimizer(kind, ps, comm=comm, metric_slots=4)
+            o2.zero_grads_in_step = True
+            shadow = o2.add_shadow(ps[2], 232)
+            d2 = ddls.DistributedOptimizer(o2)
+            assert len(d2.buckets) == 2 and bool(d2._fused) == (fused == '1')
+            for k in range(4):
+                torch.manual_seed(1000 * k + r)
+                o2.flat.flat_grads[:o2.flat.numel].copy_(torch.randn(o2.flat.numel, device=dev))
+                d2.metrics[1] = float(r + k)
+                d2.step()
+                assert abs(float(d2.metrics[1]) - (k + (n - 1) / 2.0)) < 1e-5
+            torch.cuda.synchronize()
+            if fused == '1':
+                assert [d2._bucket_mode(b) for b in d2.buckets] == ['dp', 'll'], [d2._bucket_mode(b) for b in d2.buckets]
+            assert int(o2.step_count.item()) == 4 and float(o2.flat.flat_grads[:o2.flat.numel].abs().max()) == 0.0
+            assert torch.equal(shadow[:, :225], ps[2].detach().bfloat16())
+            sd = d2.state_dict()                        # collective: gathers the sharded slots
+            finals[(fused, kind)] = o2.flat.flat_params.clone()
+            slots[(fused, kind)] = {k_: v_.to(dev) for k_, v_ in sd['slots'].items()}
+            ws = [torch.empty_like(finals[(fused, kind)]) for _ in range(n)]
+            dist.all_gather(ws, finals[(fused, kind)])
+            assert all(torch.equal(ws[0], w_) for w_ in ws), 'replicas differ after the sharded step'
+    os.environ.pop('DDLS_FUSED_OPT')
+    res['sharded_err'] = {k: float((finals[('1', k)] - finals[('0', k)]).abs().max()) for k in ('adam', 'adagrad')}
+    res['sharded_slot_err'] = {k: max(float((slots[('1', k)][s_] - slots[('0', k)][s_]).abs().max()) for s_ in slots[('1', k)])
+                               for k in ('adam', 'adagrad')}
+    res['sharded_matches'] = all(v < 1e-6 for v in res['sharded_err'].values()) and \
+        all(v < 1e-6 for v in res['sharded_slot_err'].values())
+    # the MNIST CNN end to end: two buckets (sharded + flag-in-data), CUDA graph, weights identical on every rank
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    model = ddls.models.mnist_cnn(seed=r).to(dev)
+    opt = ddls.optim.KerasAdam(model.parameters(), comm=comm)
+    ddls.broadcast_parameters(opt, 0)
+    dopt = ddls.DistributedOptimizer(opt)
+    eng = StepEngine(model, optimizer=dopt, loss='categorical_crossentropy', device=dev, use_cuda_graph=True)
+    torch.manual_seed(100 + r)
+    losses = []
+    x = torch.rand(128, 28, 28, 1, device=dev)
+    y = torch.nn.functional.one_hot(torch.randint(0, 10, (128,), device=dev), 10).float()
+    for _ in range(12):
+        losses.append(float(eng.step(x, y)))
+    w = opt.flat.flat_params.clone()
+    ws = [torch.empty_like(w) for _ in range(n)]
+    dist.all_gather(ws, w)
+    res['cnn_weights_equal'] = all(torch.equal(ws[0], v) for v in ws)
+    res['cnn_modes'] = [dopt._bucket_mode(b) for b in dopt.buckets]
+    res['cnn_loss'] = (losses[0], losses[-1])
+    res['cnn_steps'] = int(opt.step_count.item())
+    res['cnn_shadow_ok'] = bool(torch.equal(eng._direct.w1s[:, :225], model.layers_list[6].kernel.detach().bfloat16()))
     return res
 
 
@@ -236,3 +402,12 @@ def test_peer_memory_comm_multi_gpu():
     assert [o['rank'] for o in out] == list(range(n))
     assert all(o['weights_equal'] for o in out) and all(o['graph'] for o in out)
     assert all(o['fused'] for o in out) and all(o['fused_matches'] for o in out), [o.get('fused_err') for o in out]
+    assert all(o.get('ll_mc_push_mismatches', 0) == 0 for o in out), [o.get('ll_mc_push_mismatches') for o in out]
+    assert all(o['sharded_matches'] for o in out), [(o.get('sharded_err'), o.get('sharded_slot_err')) for o in out]
+    assert all(o['cnn_weights_equal'] and o['cnn_shadow_ok'] for o in out)
+    assert all(o['cnn_modes'] == ['dp', 'll'] and o['cnn_steps'] == 12 for o in out), [(o['cnn_modes'], o['cnn_steps']) for o in out]
+    assert all(o['cnn_loss'][1] < o['cnn_loss'][0] for o in out), [o['cnn_loss'] for o in out]
+    import json, os
+    os.makedirs('gpurun_out', exist_ok=True)
+    with open('gpurun_out/multigpu_checks.json', 'w') as f:
+        json.dump(out, f, indent=1, default=str)

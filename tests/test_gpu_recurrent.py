@@ -26,12 +26,10 @@ def _make(cell, seed, dev):
     return [t.requires_grad_(True) for t in (k, r, b)]
 
 
-@pytest.mark.parametrize('gen', ['v2', 'v1'])
 @pytest.mark.parametrize('cell', ['lstm', 'gru'])
 @pytest.mark.parametrize('B,T,seq', [(32, 25, False), (7, 5, False), (70, 12, True), (32, 1, False), (300, 9, False)])
-def test_recurrent_forward_backward_match_fp32(cell, B, T, seq, gen, monkeypatch):
+def test_recurrent_forward_backward_match_fp32(cell, B, T, seq):
     from distributeddeeplearningspark_b200.ops import recurrent as R
-    monkeypatch.setenv('DDLS_RNN_V1', '1' if gen == 'v1' else '0')
     dev = torch.device('cuda', 0)
     k, r, b = _make(cell, 1, dev)
     x = torch.rand(B, T, 1, device=dev)
@@ -57,7 +55,6 @@ def test_recurrent_forward_backward_match_fp32(cell, B, T, seq, gen, monkeypatch
 def test_recurrent_v2_every_tile_size(cell, tile, monkeypatch):
     from distributeddeeplearningspark_b200.ops import recurrent as R
     monkeypatch.setenv('DDLS_RNN_TILE', str(tile))
-    monkeypatch.setenv('DDLS_RNN_V1', '0')
     dev = torch.device('cuda', 0)
     k, r, b = _make(cell, 3, dev)
     B, T = 150, 11

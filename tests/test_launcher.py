@@ -52,6 +52,22 @@ def test_killed_rank_is_detected_not_hung():
         spark.run(_die, num_proc=2, backend=LocalBarrierBackend(timeout=120))
 
 
+def _slow(seconds):
+    time.sleep(seconds)
+    return int(os.environ['RANK'])
+
+
+def test_barrier_timeout_is_not_a_runtime_limit():
+    """A task that runs longer than the barrier timeout without any pipe traffic is healthy, not hung."""
+    out = spark.run(_slow, args=(4.0,), num_proc=2, backend=LocalBarrierBackend(timeout=1.5))
+    assert out == [0, 1]
+
+
+def test_stage_timeout_bounds_total_runtime_when_asked():
+    with pytest.raises(BarrierStageError, match='stage timed out'):
+        spark.run(_slow, args=(30.0,), num_proc=2, backend=LocalBarrierBackend(timeout=60, stage_timeout=3.0))
+
+
 def _barrier_user():
     # tasks can keep using the stage barrier through torch.distributed after init
     import distributeddeeplearningspark_b200 as ddls
