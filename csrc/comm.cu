@@ -403,6 +403,8 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_twoshot_kernel(CommCtx
 // ---------------------------------------------------------------------------------------------------------
 // NVLS: in-switch reduction + multicast store.  in/out symmetric, bound to the multicast object.
 // ---------------------------------------------------------------------------------------------------------
+DDLS_DEVINL float4 mc_ld_reduce_nc(const float* mc_ptr);    // defined next to the sharded step kernel below
+
 __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c, ArParams p) {
   const int rank = c.rank_base + blockIdx.y;
   const uint32_t epoch = read_epoch(c, rank) + 1;
@@ -414,11 +416,24 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c,
   peer_barrier(c, rank, blockIdx.x, epoch);               // every rank's input is final
   const float* mc_in = reinterpret_cast<const float*>(c.mc_base + p.in_off);
   float* mc_out = reinterpret_cast<float*>(c.mc_base + p.out_off);
-#pragma unroll 4
-  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-    float4 v = multimem_ld_reduce_f32x4(mc_in + 4 * i);
-    v.x *= p.scale; v.y *= p.scale; v.z *= p.scale; v.w *= p.scale;
-    multimem_st_f32x4(mc_out + 4 * i, v);
+  // NVLS_U switch round trips in flight per thread: the loads of a round are all issued before the first store (a
+  // load/store pair per iteration leaves ONE load in flight per warp)
+  constexpr int NVLS_U = 4;
+  for (uint64_t i0 = lo + threadIdx.x; i0 < hi; i0 += (uint64_t)NVLS_U * blockDim.x) {
+    float4 v[NVLS_U];
+#pragma unroll
+    for (int k = 0; k < NVLS_U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i < hi) v[k] = mc_ld_reduce_nc(mc_in + 4 * i);
+    }
+#pragma unroll
+    for (int k = 0; k < NVLS_U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i < hi) {
+        v[k].x *= p.scale; v[k].y *= p.scale; v[k].z *= p.scale; v[k].w *= p.scale;
+        multimem_st_f32x4(mc_out + 4 * i, v[k]);
+      }
+    }
   }
   peer_barrier(c, rank, blockIdx.x, epoch + 1);
   advance_epoch(c, rank, epoch + 1);
@@ -450,18 +465,31 @@ struct DpStep {
   float scale, lr, b1, b2, eps;
   int kind;                       // 1 adam, 2 adagrad, 3 sgd
   int zero_grads, advance_step;
+  unsigned long long* trace;      // optional: 5 globaltimer stamps per block (entry, barrier A, slice done, barrier B, end)
 };
 
 DDLS_DEVINL float4 ldcg4(const float4* p) { return __ldcg(p); }
+// multimem.ld_reduce WITHOUT the "memory" clobber of the common.cuh wrapper: several of these must be in flight per
+// thread together with the local slot loads (a clobber serialises them; the flag barrier before the first one is the
+// ordering point).
+DDLS_DEVINL float4 mc_ld_reduce_nc(const float* mc_ptr) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc_ptr));
+  return v;
+}
 
-template <bool MC>
-__global__ void __launch_bounds__(COMM_THREADS) dp_step_kernel(CommCtx c, DpStep p, ShadowSet sh) {
+constexpr int DP_U = 4;          // vectors per thread per round: every remote load of a round is issued before the first use
+constexpr int DP_THREADS = 256;  // ~120 registers per thread: a 256-thread CTA leaves room for a compute CTA on the same SM
+
+template <bool MC, int KIND>
+__global__ void __launch_bounds__(DP_THREADS, 1) dp_step_kernel(CommCtx c, DpStep p, ShadowSet sh) {
   const int rank = c.rank_base + blockIdx.y;
   const uint32_t e0 = read_epoch(c, rank);
   const int t_step = *reinterpret_cast<volatile int*>(p.step) + 1;
   __shared__ float s_lr_t;
   if (threadIdx.x == 0)
-    s_lr_t = (p.kind == 1) ? p.lr * sqrtf(1.0f - powf(p.b2, (float)t_step)) / (1.0f - powf(p.b1, (float)t_step)) : p.lr;
+    s_lr_t = (KIND == 1) ? p.lr * sqrtf(1.0f - powf(p.b2, (float)t_step)) / (1.0f - powf(p.b1, (float)t_step)) : p.lr;
   const uint64_t nvec = p.n / 4, nopt = p.n_opt / 4;
   const uint64_t per_rank = (nvec + c.world - 1) / c.world;
   const uint64_t per_blk = (per_rank + gridDim.x - 1) / gridDim.x;
@@ -471,87 +499,128 @@ __global__ void __launch_bounds__(COMM_THREADS) dp_step_kernel(CommCtx c, DpStep
   float4* G = reinterpret_cast<float4*>(c.base[rank] + p.grad_off);
   float4* S1 = reinterpret_cast<float4*>(c.base[rank] + p.s1_off);
   float4* S2 = reinterpret_cast<float4*>(c.base[rank] + p.s2_off);
+  unsigned long long* tr = (p.trace != nullptr && threadIdx.x == 0) ? p.trace + 5 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
+  if (tr) tr[0] = globaltimer_ns();
   peer_barrier(c, rank, blockIdx.x, e0 + 1);
+  if (tr) tr[1] = globaltimer_ns();
   const float lr_t = s_lr_t;
   const float ob1 = 1.0f - p.b1, ob2 = 1.0f - p.b2;
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-#pragma unroll 2
-  for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
-    float4 g;
-    if (MC) {
-      g = multimem_ld_reduce_f32x4(reinterpret_cast<const float*>(c.mc_base + p.grad_off) + 4 * i);
-    } else {
-      g = zero4;
+  for (uint64_t i0 = lo + threadIdx.x; i0 < hi; i0 += (uint64_t)DP_U * blockDim.x) {
+    float4 g[DP_U], pi[DP_U], s1[DP_U], s2[DP_U];
+    // round 1: every remote load of this thread
 #pragma unroll
-      for (int r = 0; r < MAXR; ++r) {                      // fixed rank order => every rank would compute the same bits
-        if (r >= c.world) break;
-        const float4 x = ldcg4(reinterpret_cast<const float4*>(c.base[r] + p.grad_off) + i);
-        g.x += x.x; g.y += x.y; g.z += x.z; g.w += x.w;
-      }
-    }
-    g.x *= p.scale; g.y *= p.scale; g.z *= p.scale; g.w *= p.scale;
-    if (i < nopt) {
-      float4 pi = P[i];
-      if (p.kind == 1) {
-        float4 mi = S1[i], vi = S2[i];
-        mi.x = p.b1 * mi.x + ob1 * g.x; mi.y = p.b1 * mi.y + ob1 * g.y; mi.z = p.b1 * mi.z + ob1 * g.z; mi.w = p.b1 * mi.w + ob1 * g.w;
-        vi.x = p.b2 * vi.x + ob2 * g.x * g.x; vi.y = p.b2 * vi.y + ob2 * g.y * g.y;
-        vi.z = p.b2 * vi.z + ob2 * g.z * g.z; vi.w = p.b2 * vi.w + ob2 * g.w * g.w;
-        pi.x -= lr_t * mi.x / (sqrtf(vi.x) + p.eps); pi.y -= lr_t * mi.y / (sqrtf(vi.y) + p.eps);
-        pi.z -= lr_t * mi.z / (sqrtf(vi.z) + p.eps); pi.w -= lr_t * mi.w / (sqrtf(vi.w) + p.eps);
-        S1[i] = mi; S2[i] = vi;
-      } else if (p.kind == 2) {
-        float4 ai = S1[i];
-        ai.x += g.x * g.x; ai.y += g.y * g.y; ai.z += g.z * g.z; ai.w += g.w * g.w;
-        pi.x -= p.lr * g.x / (sqrtf(ai.x) + p.eps); pi.y -= p.lr * g.y / (sqrtf(ai.y) + p.eps);
-        pi.z -= p.lr * g.z / (sqrtf(ai.z) + p.eps); pi.w -= p.lr * g.w / (sqrtf(ai.w) + p.eps);
-        S1[i] = ai;
-      } else {
-        pi.x -= p.lr * g.x; pi.y -= p.lr * g.y; pi.z -= p.lr * g.z; pi.w -= p.lr * g.w;
-      }
-      if (MC) {
-        multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.param_off) + 4 * i, pi);
-        if (!p.zero_grads) multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.grad_off) + 4 * i, g);
-      } else {
+    for (int k = 0; k < DP_U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i < hi) {
+        if (MC) {
+          g[k] = mc_ld_reduce_nc(reinterpret_cast<const float*>(c.mc_base + p.grad_off) + 4 * i);
+        } else {
+          g[k] = zero4;
 #pragma unroll
-        for (int d = 0; d < MAXR; ++d) {
-          if (d >= c.world) break;
-          const int r = (rank + d) % c.world;
-          reinterpret_cast<float4*>(c.base[r] + p.param_off)[i] = pi;
-          if (!p.zero_grads) reinterpret_cast<float4*>(c.base[r] + p.grad_off)[i] = g;
+          for (int r = 0; r < MAXR; ++r) {                  // fixed rank order
+            if (r >= c.world) break;
+            const float4 x = ldcg4(reinterpret_cast<const float4*>(c.base[r] + p.grad_off) + i);
+            g[k].x += x.x; g[k].y += x.y; g[k].z += x.z; g[k].w += x.w;
+          }
         }
       }
-      if (p.zero_grads) G[i] = zero4;           // my replica of MY slice: nobody else reads it
-      const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
-      write_shadows(sh, p.elem0 + 4 * i, pv);
-    } else {                                    // metric tail: the reduced value goes to every replica, nothing is cleared
-      if (MC) {
-        multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.grad_off) + 4 * i, g);
-      } else {
-        for (int r = 0; r < c.world; ++r) reinterpret_cast<float4*>(c.base[r] + p.grad_off)[i] = g;
+    }
+    // round 2: the local parameter / slot vectors (independent of round 1: they overlap the switch round trip)
+#pragma unroll
+    for (int k = 0; k < DP_U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i < hi && i < nopt) {
+        pi[k] = P[i];
+        if (KIND <= 2) s1[k] = S1[i];
+        if (KIND == 1) s2[k] = S2[i];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < DP_U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i >= hi) continue;
+      float4 gg = g[k];
+      gg.x *= p.scale; gg.y *= p.scale; gg.z *= p.scale; gg.w *= p.scale;
+      if (i < nopt) {
+        float4 q = pi[k];
+        if (KIND == 1) {
+          float4 mi = s1[k], vi = s2[k];
+          mi.x = p.b1 * mi.x + ob1 * gg.x; mi.y = p.b1 * mi.y + ob1 * gg.y; mi.z = p.b1 * mi.z + ob1 * gg.z; mi.w = p.b1 * mi.w + ob1 * gg.w;
+          vi.x = p.b2 * vi.x + ob2 * gg.x * gg.x; vi.y = p.b2 * vi.y + ob2 * gg.y * gg.y;
+          vi.z = p.b2 * vi.z + ob2 * gg.z * gg.z; vi.w = p.b2 * vi.w + ob2 * gg.w * gg.w;
+          q.x -= lr_t * mi.x / (sqrtf(vi.x) + p.eps); q.y -= lr_t * mi.y / (sqrtf(vi.y) + p.eps);
+          q.z -= lr_t * mi.z / (sqrtf(vi.z) + p.eps); q.w -= lr_t * mi.w / (sqrtf(vi.w) + p.eps);
+          S1[i] = mi; S2[i] = vi;
+        } else if (KIND == 2) {
+          float4 ai = s1[k];
+          ai.x += gg.x * gg.x; ai.y += gg.y * gg.y; ai.z += gg.z * gg.z; ai.w += gg.w * gg.w;
+          q.x -= p.lr * gg.x / (sqrtf(ai.x) + p.eps); q.y -= p.lr * gg.y / (sqrtf(ai.y) + p.eps);
+          q.z -= p.lr * gg.z / (sqrtf(ai.z) + p.eps); q.w -= p.lr * gg.w / (sqrtf(ai.w) + p.eps);
+          S1[i] = ai;
+        } else {
+          q.x -= p.lr * gg.x; q.y -= p.lr * gg.y; q.z -= p.lr * gg.z; q.w -= p.lr * gg.w;
+        }
+        if (MC) {
+          multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.param_off) + 4 * i, q);
+          if (!p.zero_grads) multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.grad_off) + 4 * i, gg);
+        } else {
+#pragma unroll
+          for (int d = 0; d < MAXR; ++d) {
+            if (d >= c.world) break;
+            const int r = (rank + d) % c.world;
+            reinterpret_cast<float4*>(c.base[r] + p.param_off)[i] = q;
+            if (!p.zero_grads) reinterpret_cast<float4*>(c.base[r] + p.grad_off)[i] = gg;
+          }
+        }
+        if (p.zero_grads) G[i] = zero4;           // my replica of MY slice: nobody else reads it
+        const float pv[4] = {q.x, q.y, q.z, q.w};
+        write_shadows(sh, p.elem0 + 4 * i, pv);
+      } else {                                    // metric tail: the reduced value goes to every replica, nothing is cleared
+        if (MC) {
+          multimem_st_f32x4(reinterpret_cast<float*>(c.mc_base + p.grad_off) + 4 * i, gg);
+        } else {
+          for (int r = 0; r < c.world; ++r) reinterpret_cast<float4*>(c.base[r] + p.grad_off)[i] = gg;
+        }
       }
     }
   }
+  if (p.trace != nullptr) __syncthreads();
+  if (tr) tr[2] = globaltimer_ns();
   peer_barrier(c, rank, blockIdx.x, e0 + 2);
+  if (tr) tr[3] = globaltimer_ns();
   // local pass over the sub-slices the OTHER ranks' same-index blocks have just finished
   if (p.zero_grads || sh.n != 0) {
     for (int d = 1; d < c.world; ++d) {
       const int r = (rank + d) % c.world;
       const uint64_t qlo = min(nvec, (uint64_t)r * per_rank), qhi = min(nvec, qlo + per_rank);
       const uint64_t l2 = min(qhi, qlo + blockIdx.x * per_blk), h2 = min(min(qhi, l2 + per_blk), nopt);
-#pragma unroll 2
-      for (uint64_t i = l2 + threadIdx.x; i < h2; i += blockDim.x) {
-        if (p.zero_grads) G[i] = zero4;
-        const uint64_t e = p.elem0 + 4 * i;
-        if (sh.n != 0 && e + 4 > sh.lo && e < sh.hi) {
-          const float4 pi = ldcg4(P + i);       // written by a peer through NVLink: read it from L2, not a stale L1 line
-          const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
-          write_shadows(sh, e, pv);
+      const bool shadowed = sh.n != 0 && p.elem0 + 4 * h2 > sh.lo && p.elem0 + 4 * l2 < sh.hi;
+      for (uint64_t i0 = l2 + threadIdx.x; i0 < h2; i0 += (uint64_t)DP_U * blockDim.x) {
+        float4 q[DP_U];
+#pragma unroll
+        for (int k = 0; k < DP_U; ++k) {
+          const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+          if (i < h2) {
+            if (p.zero_grads) G[i] = zero4;
+            if (shadowed) q[k] = ldcg4(P + i);    // written by a peer through NVLink: read it from L2, not a stale L1 line
+          }
+        }
+        if (shadowed) {
+#pragma unroll
+          for (int k = 0; k < DP_U; ++k) {
+            const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+            if (i < h2) {
+              const float pv[4] = {q[k].x, q[k].y, q[k].z, q[k].w};
+              write_shadows(sh, p.elem0 + 4 * i, pv);
+            }
+          }
         }
       }
     }
   }
   __syncthreads();
+  if (tr) tr[4] = globaltimer_ns();
   if (threadIdx.x == 0) {
     uint32_t* seq = reinterpret_cast<uint32_t*>(c.base[rank] + c.seq_off);
     __threadfence();
@@ -672,6 +741,18 @@ __global__ void __launch_bounds__(COMM_THREADS) adag_pull_kernel(CommCtx c, floa
     *last_update = ld_relaxed_sys(reinterpret_cast<const uint32_t*>(c.base[rank] + updates_off));
 }
 
+// A kernel that uses (almost) no shared memory leaves its SM configured with the smallest shared-memory carve-out, and a
+// CTA that needs ~200 KB (the TMA convolution / GEMM kernels these collectives overlap with) cannot join that SM until
+// every resident CTA has left.  Asking for the largest carve-out keeps the SM in the configuration the compute kernels need.
+template <typename K>
+static void prefer_max_smem(K kern) {
+  static thread_local const void* done[48];
+  static thread_local int ndone = 0;
+  for (int i = 0; i < ndone; ++i) if (done[i] == (const void*)kern) return;
+  cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+  if (ndone < 48) done[ndone++] = (const void*)kern;
+}
+
 static int make_ctx(const DdlsCommDesc* d, CommCtx* c) {
   if (d->world < 1 || d->world > MAXR) { set_last_error("comm: world must be in [1,%d]", MAXR); return 1; }
   for (int r = 0; r < MAXR; ++r) c->base[r] = r < d->world ? static_cast<uint8_t*>(d->base[r]) : nullptr;
@@ -688,6 +769,7 @@ template <typename... Args>
 static int launch(const DdlsCommDesc* d, void (*kern)(Args...), int blocks, int threads, cudaStream_t st, Args... args) {
   if (d->emulate && blocks * d->world > 128) blocks = 128 / d->world;   // all emulated blocks must be co-resident
   dim3 grid(blocks, d->emulate ? d->world : 1);
+  prefer_max_smem(kern);
   if (d->emulate) {
     // emulated ranks spin on each other: all blocks must be co-resident => cooperative launch
     void* ptrs[] = {(void*)&args...};
@@ -704,7 +786,7 @@ static int pick_blocks(uint64_t n, int requested) {
   const uint64_t bytes = n * 4;
   int b = (int)((bytes + (32 << 10) - 1) / (32 << 10));     // ~32 KB of payload per block (4 x 16 B per thread)
   if (b < 1) b = 1;
-  if (b > MAX_CHANNELS) b = MAX_CHANNELS;
+  if (b > 64) b = 64;
   return b;
 }
 
@@ -791,6 +873,11 @@ extern "C" int ddls_comm_allreduce_opt(const DdlsCommDesc* d, uint64_t grad_off,
                    : launch(d, allreduce_oneshot_ll_kernel<float>, lb, COMM_THREADS, st, c, p, o);
 }
 
+// Debug aid (tools/dp_step_trace.py): a device buffer of 5 uint64 per block that later ddls_comm_dp_step launches of this
+// process fill with globaltimer stamps; NULL switches it off.
+static unsigned long long* g_dp_trace = nullptr;
+extern "C" int ddls_comm_dp_step_trace(unsigned long long* buf) { g_dp_trace = buf; return 0; }
+
 extern "C" int ddls_comm_dp_step(const DdlsCommDesc* d, uint64_t grad_off, uint64_t param_off, uint64_t slot1_off,
                                  uint64_t slot2_off, uint64_t n, uint64_t n_opt, uint64_t elem0, float scale, int kind,
                                  int* step, float lr, float b1, float b2, float eps, int zero_grads, int advance_step,
@@ -804,18 +891,24 @@ extern "C" int ddls_comm_dp_step(const DdlsCommDesc* d, uint64_t grad_off, uint6
     set_last_error("ddls_comm_dp_step: n, n_opt (<= n), elem0 must be multiples of 4 and offsets 16-byte aligned");
     return 1;
   }
-  DpStep p{grad_off, param_off, slot1_off, slot2_off, n, n_opt, elem0, step, scale, lr, b1, b2, eps, kind, zero_grads, advance_step};
+  DpStep p{grad_off, param_off, slot1_off, slot2_off, n, n_opt, elem0, step, scale, lr, b1, b2, eps, kind, zero_grads, advance_step,
+           g_dp_trace};
   const ShadowSet sh = make_shadows(shadows, n_shadows);
-  // ~16 KB of my slice per block: the kernel is latency-bound (two flag rounds + one switch round trip), so many blocks
-  // with few vectors each; `blocks` > 0 caps the SMs taken from the backward kernels this overlaps with
+  // the kernel is latency-bound (two flag rounds + one switch round trip): enough blocks that a thread's share of the slice
+  // is ONE round of DP_U vectors, all in flight together; `blocks` > 0 caps the SMs taken from the backward kernels this
+  // overlaps with
   const uint64_t slice_bytes = (n * 4 + d->world - 1) / d->world;
-  int nb = (int)((slice_bytes + (16 << 10) - 1) / (16 << 10));
+  const uint64_t per_block = (uint64_t)DP_THREADS * DP_U * 16;
+  int nb = (int)((slice_bytes + per_block - 1) / per_block);
   if (nb < 1) nb = 1;
   if (nb > MAX_CHANNELS) nb = MAX_CHANNELS;
   if (blocks > 0 && blocks < nb) nb = blocks;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (c.mc_base != nullptr && !d->emulate) return launch(d, dp_step_kernel<true>, nb, COMM_THREADS, st, c, p, sh);
-  return launch(d, dp_step_kernel<false>, nb, COMM_THREADS, st, c, p, sh);
+  const bool mc = c.mc_base != nullptr && !d->emulate;
+#define DDLS_DP_LAUNCH(M, K) launch(d, dp_step_kernel<M, K>, nb, DP_THREADS, st, c, p, sh)
+  if (mc) return kind == 1 ? DDLS_DP_LAUNCH(true, 1) : kind == 2 ? DDLS_DP_LAUNCH(true, 2) : DDLS_DP_LAUNCH(true, 3);
+  return kind == 1 ? DDLS_DP_LAUNCH(false, 1) : kind == 2 ? DDLS_DP_LAUNCH(false, 2) : DDLS_DP_LAUNCH(false, 3);
+#undef DDLS_DP_LAUNCH
 }
 
 extern "C" int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast,

@@ -36,9 +36,9 @@ from ..utils.misc import env_int, env_str
 from .comm import Average, Communicator, ReduceOp, Sum
 
 MAX_RANKS = 8
-CONTROL_BYTES = 4096
+CONTROL_BYTES = 8192
 FLAGS_OFF = 0
-SEQ_OFF = 2048
+SEQ_OFF = 4096
 ALIGN = 256
 
 AR_ONESHOT, AR_TWOSHOT, AR_NVLS, AR_ONESHOT_LL = 0, 1, 2, 3

@@ -196,8 +196,8 @@ int ddls_mc_bind_and_map(unsigned long long mc_handle, unsigned long long mem_ha
 
 /* ---- peer-memory collectives (one kernel each; offsets are symmetric offsets into the heaps) ---------- */
 #define DDLS_MAX_RANKS 8
-#define DDLS_COMM_MAX_BLOCKS 64
-#define DDLS_COMM_CONTROL_BYTES 4096 /* flags [64][8] u32 at offset 0, epoch counter at 2048 */
+#define DDLS_COMM_MAX_BLOCKS 128
+#define DDLS_COMM_CONTROL_BYTES 8192 /* flags [128][8] u32 at offset 0, epoch counter at 4096 */
 typedef struct {
   void* base[DDLS_MAX_RANKS]; /* this process' mappings of every rank's heap */
   void* mc_base;              /* multicast mapping or NULL */
@@ -238,6 +238,9 @@ int ddls_comm_dp_step(const DdlsCommDesc* d, uint64_t grad_off, uint64_t param_o
                       uint64_t n, uint64_t n_opt, uint64_t elem0, float scale, int kind, int* step, float lr, float b1,
                       float b2, float eps, int zero_grads, int advance_step, const DdlsShadowSpec* shadows, int n_shadows,
                       int blocks, void* stream);
+/* Debug aid: later ddls_comm_dp_step launches write 5 globaltimer stamps per block (entry, after barrier A, slice done,
+ * after barrier B, end) into buf (device memory, 5 * blocks uint64); NULL switches it off. */
+int ddls_comm_dp_step_trace(unsigned long long* buf);
 int ddls_comm_broadcast(const DdlsCommDesc* d, uint64_t off, uint64_t bytes, int root, int use_multicast, int blocks,
                         void* stream);
 int ddls_comm_allgather(const DdlsCommDesc* d, uint64_t in_off, uint64_t out_off, uint64_t chunk_bytes, int blocks,
