@@ -19,6 +19,7 @@
 // launch (never as separate launches that wait on each other).
 // The reference's equivalent is dist-keras' pickle-over-TCP commit/pull.
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "shadow.cuh"
@@ -38,7 +39,19 @@ struct CommCtx {
   uint64_t flags_off;    // uint32 [MAX_CHANNELS][MAXR] written by peers
   uint64_t seq_off;      // uint32 [2]: {completed epochs, arrival ticket}
   uint64_t timeout_ns;
+  int fence_mode;        // 0: fences chosen per call site (below); 1: every flag round has release + acquire fences
 };
+
+// Which system-scope fences a flag round needs.  A fence.acq_rel.sys costs ~3 us on this part, so a round only pays for
+// the ones its data flow requires:
+//   release  before signalling, when THIS kernel wrote data a peer will read after the round (stores pushed to peers,
+//            multimem.st).  Not needed when the data was written by earlier kernels of the stream: kernel completion has
+//            already made it visible system-wide.
+//   acquire  after the wait, when the data is then read through a path that could hold a stale copy.  The kernels here
+//            read peer-written data only through L2 (ld.cg / multimem / first-touch lines of an L1 that was invalidated
+//            at kernel start), after the control dependency on the polled flag, so no call site needs it; the stand-alone
+//            barrier keeps it.  DDLS_COMM_FENCES=strict restores both fences everywhere.
+constexpr int FENCE_NONE = 0, FENCE_REL = 1, FENCE_ACQ = 2, FENCE_BOTH = 3;
 
 DDLS_DEVINL uint64_t globaltimer_ns() {
   uint64_t t;
@@ -48,22 +61,32 @@ DDLS_DEVINL uint64_t globaltimer_ns() {
 
 // Flag barrier among same-index blocks of all ranks.  Called by the whole block; data written before the
 // call (by any thread of the block) is visible to peers' readers after their matching wait.
-DDLS_DEVINL void peer_barrier(const CommCtx& c, int rank, int channel, uint32_t epoch) {
-  __threadfence_system();
+DDLS_DEVINL void peer_barrier(const CommCtx& c, int rank, int channel, uint32_t epoch, int fences) {
+  if (c.fence_mode == 1) fences = FENCE_BOTH;
+  // One system-scope fence per signalling thread, not one per thread of the block: the bar.sync orders every thread's
+  // earlier writes before the fence of the signalling threads, and the fence is cumulative (the pattern of a cooperative
+  // grid barrier).  The poll is a relaxed load — an acquire load would pay a fence on every spin — followed by one fence.
+  // Measured here: the former form (__threadfence_system by all threads, st.release, ld.acquire polling) cost 10-12 us
+  // per flag round with 64-127 blocks in flight.
   __syncthreads();
   if (threadIdx.x < c.world) {
     const int r = threadIdx.x;
     uint32_t* remote = reinterpret_cast<uint32_t*>(c.base[r] + c.flags_off) + channel * MAXR + rank;
-    st_release_sys(remote, epoch);
+    if (fences & FENCE_REL) fence_acq_rel_sys();
+    st_relaxed_sys(remote, epoch);
     const uint32_t* mine = reinterpret_cast<const uint32_t*>(c.base[rank] + c.flags_off) + channel * MAXR + r;
-    const uint64_t t0 = globaltimer_ns();
-    while (static_cast<int32_t>(ld_acquire_sys(mine) - epoch) < 0) {
-      if (globaltimer_ns() - t0 > c.timeout_ns) {
-        printf("ddls comm: rank %d channel %d timed out waiting for rank %d at epoch %u (saw %u)\n", rank, channel, r,
-               epoch, ld_relaxed_sys(mine));
-        __trap();
+    if (static_cast<int32_t>(ld_relaxed_sys(mine) - epoch) < 0) {
+      const uint64_t t0 = globaltimer_ns();
+      uint32_t spins = 0;
+      while (static_cast<int32_t>(ld_relaxed_sys(mine) - epoch) < 0) {
+        if ((++spins & 255u) == 0 && globaltimer_ns() - t0 > c.timeout_ns) {
+          printf("ddls comm: rank %d channel %d timed out waiting for rank %d at epoch %u (saw %u)\n", rank, channel, r,
+                 epoch, ld_relaxed_sys(mine));
+          __trap();
+        }
       }
     }
+    if (fences & FENCE_ACQ) fence_acq_rel_sys();
   }
   __syncthreads();
 }
@@ -189,7 +212,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_kernel(CommCtx
       *dst = w;
     }
   }
-  peer_barrier(c, rank, blockIdx.x, epoch);
+  peer_barrier(c, rank, blockIdx.x, epoch, FENCE_REL);
   const V* stage = reinterpret_cast<const V*>(c.base[rank] + p.stage_off) + par * parity_vecs;
   float4* out = reinterpret_cast<float4*>(c.base[rank] + p.out_off);
 #pragma unroll 2
@@ -372,7 +395,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_twoshot_kernel(CommCtx
       dst[i] = W::pack(xv);
     }
   }
-  peer_barrier(c, rank, blockIdx.x, epoch);
+  peer_barrier(c, rank, blockIdx.x, epoch, FENCE_REL);
   {
     const uint64_t lo = blo + rank * per_rank, hi = min(bhi, lo + per_rank);
     const V* stage = reinterpret_cast<const V*>(c.base[rank] + p.stage_off) + par * parity_vecs;
@@ -396,7 +419,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_twoshot_kernel(CommCtx
       }
     }
   }
-  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  peer_barrier(c, rank, blockIdx.x, epoch + 1, FENCE_REL);
   advance_epoch(c, rank, epoch + 1);
 }
 
@@ -413,7 +436,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c,
   const uint64_t blo = blockIdx.x * per_blk, bhi = min(nvec, blo + per_blk);
   const uint64_t per_rank = (bhi > blo) ? ((bhi - blo) + c.world - 1) / c.world : 0;
   const uint64_t lo = blo + rank * per_rank, hi = min(bhi, lo + per_rank);
-  peer_barrier(c, rank, blockIdx.x, epoch);               // every rank's input is final
+  peer_barrier(c, rank, blockIdx.x, epoch, FENCE_NONE);               // every rank's input is final
   const float* mc_in = reinterpret_cast<const float*>(c.mc_base + p.in_off);
   float* mc_out = reinterpret_cast<float*>(c.mc_base + p.out_off);
   // NVLS_U switch round trips in flight per thread: the loads of a round are all issued before the first store (a
@@ -435,7 +458,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c,
       }
     }
   }
-  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  peer_barrier(c, rank, blockIdx.x, epoch + 1, FENCE_REL);
   advance_epoch(c, rank, epoch + 1);
 }
 
@@ -501,7 +524,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) dp_step_kernel(CommCtx c, DpSte
   float4* S2 = reinterpret_cast<float4*>(c.base[rank] + p.s2_off);
   unsigned long long* tr = (p.trace != nullptr && threadIdx.x == 0) ? p.trace + 5 * (blockIdx.y * gridDim.x + blockIdx.x) : nullptr;
   if (tr) tr[0] = globaltimer_ns();
-  peer_barrier(c, rank, blockIdx.x, e0 + 1);
+  peer_barrier(c, rank, blockIdx.x, e0 + 1, FENCE_NONE);
   if (tr) tr[1] = globaltimer_ns();
   const float lr_t = s_lr_t;
   const float ob1 = 1.0f - p.b1, ob2 = 1.0f - p.b2;
@@ -587,7 +610,7 @@ __global__ void __launch_bounds__(DP_THREADS, 1) dp_step_kernel(CommCtx c, DpSte
   }
   if (p.trace != nullptr) __syncthreads();
   if (tr) tr[2] = globaltimer_ns();
-  peer_barrier(c, rank, blockIdx.x, e0 + 2);
+  peer_barrier(c, rank, blockIdx.x, e0 + 2, FENCE_REL);
   if (tr) tr[3] = globaltimer_ns();
   // local pass over the sub-slices the OTHER ranks' same-index blocks have just finished
   if (p.zero_grads || sh.n != 0) {
@@ -642,7 +665,7 @@ __global__ void __launch_bounds__(COMM_THREADS) broadcast_kernel(CommCtx c, uint
   const uint32_t epoch = read_epoch(c, rank) + 1;
   const uint64_t per = (nvec16 + gridDim.x - 1) / gridDim.x;
   const uint64_t lo = blockIdx.x * per, hi = min(nvec16, lo + per);
-  peer_barrier(c, rank, blockIdx.x, epoch);               // receivers are done with the old contents
+  peer_barrier(c, rank, blockIdx.x, epoch, FENCE_NONE);               // receivers are done with the old contents
   if (rank == root) {
     const float4* src = reinterpret_cast<const float4*>(c.base[rank] + off);
     if (use_mc && c.mc_base != nullptr) {
@@ -656,7 +679,7 @@ __global__ void __launch_bounds__(COMM_THREADS) broadcast_kernel(CommCtx c, uint
       }
     }
   }
-  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  peer_barrier(c, rank, blockIdx.x, epoch + 1, FENCE_REL);
   advance_epoch(c, rank, epoch + 1);
 }
 
@@ -668,7 +691,7 @@ __global__ void __launch_bounds__(COMM_THREADS) allgather_kernel(CommCtx c, uint
   const uint64_t per = (chunk_vec16 + gridDim.x - 1) / gridDim.x;
   const uint64_t lo = blockIdx.x * per, hi = min(chunk_vec16, lo + per);
   const float4* src = reinterpret_cast<const float4*>(c.base[rank] + in_off);
-  peer_barrier(c, rank, blockIdx.x, epoch);
+  peer_barrier(c, rank, blockIdx.x, epoch, FENCE_NONE);
   for (uint64_t i = lo + threadIdx.x; i < hi; i += blockDim.x) {
     const float4 v = src[i];
     for (int d = 0; d < c.world; ++d) {
@@ -676,14 +699,14 @@ __global__ void __launch_bounds__(COMM_THREADS) allgather_kernel(CommCtx c, uint
       reinterpret_cast<float4*>(c.base[r] + out_off)[(uint64_t)rank * chunk_vec16 + i] = v;
     }
   }
-  peer_barrier(c, rank, blockIdx.x, epoch + 1);
+  peer_barrier(c, rank, blockIdx.x, epoch + 1, FENCE_REL);
   advance_epoch(c, rank, epoch + 1);
 }
 
 __global__ void __launch_bounds__(32) barrier_kernel(CommCtx c) {
   const int rank = c.rank_base + blockIdx.y;
   const uint32_t epoch = read_epoch(c, rank) + 1;
-  peer_barrier(c, rank, 0, epoch);
+  peer_barrier(c, rank, 0, epoch, FENCE_BOTH);
   advance_epoch(c, rank, epoch + 1);
 }
 
@@ -762,6 +785,8 @@ static int make_ctx(const DdlsCommDesc* d, CommCtx* c) {
   c->flags_off = d->flags_off;
   c->seq_off = d->seq_off;
   c->timeout_ns = d->timeout_ms ? (uint64_t)d->timeout_ms * 1000000ull : 20000000000ull;
+  static const int fence_mode = [] { const char* e = getenv("DDLS_COMM_FENCES"); return (e && e[0] == 's') ? 1 : 0; }();
+  c->fence_mode = fence_mode;
   return 0;
 }
 

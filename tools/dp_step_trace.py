@@ -22,7 +22,7 @@ opt.zero_grads_in_step = True
 if shadow:
     opt.add_shadow(ps[0], 232)
 nel = opt.flat.numel
-for blocks in [int(b) for b in os.environ.get('BLOCKS', '0,16,32,64').split(',')]:
+for blocks in [int(b) for b in os.environ.get('BLOCKS', '0,32,64').split(',')]:
     def call():
         comm.dp_step_(opt, 0, nel, ddls.Average, advance=True, blocks=blocks)
     for _ in range(5):
