@@ -53,6 +53,7 @@ def parse():
     ap.add_argument('--no-graph', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-dataset', action='store_true', help='feed step(x, y) from the device pool instead of the in-graph gather')
+    ap.add_argument('--no-secondary', action='store_true', help='skip the NYISO LSTM run and the allreduce latency table')
     ap.add_argument('--comm', default=None, help='peer (default on GPUs) | nccl')
     return ap.parse_args()
 
@@ -87,45 +88,25 @@ def make_batches(model_name, batch, n_batches, seed, device):
     return {'x': torch.from_numpy(x), 'y': torch.from_numpy(y)}
 
 
-def main():
-    args = parse()
-    if args.impl == 'reference':
-        return reference_arm(args)
-
+def measure(args, model_name, ddls, K, W, with_e2e=True, with_clocks=True):
+    """Train ``model_name`` for W untimed + K timed steps (kernel-only, then end to end) and return the result fields."""
     import torch
-    import distributeddeeplearningspark_b200 as ddls
     from distributeddeeplearningspark_b200 import _native
     from distributeddeeplearningspark_b200.trainers import StepEngine
     from distributeddeeplearningspark_b200.utils import ClockSampler
-
-    if not torch.cuda.is_available():
-        print(json.dumps({'impl': args.impl, 'unavailable': 'no CUDA device visible'}))
-        return 0
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            print(json.dumps({'impl': args.impl, 'unavailable':
-                              f'--gpus {args.gpus} must be launched with torch.distributed.run (one rank per GPU)'}))
-            return 0
-    if args.comm:
-        os.environ['DDLS_COMM'] = args.comm
-    ddls.init()
+    from distributeddeeplearningspark_b200.ops.preprocess import mnist_preprocess
     rank, size, dev = ddls.rank(), ddls.size(), ddls.device()
-    md = MODEL_DEFAULTS[args.model]
-    B = args.batch_per_rank or md['batch']
-    K, W = args.steps, max(3, args.warmup)
+    md = MODEL_DEFAULTS[model_name]
+    B = (args.batch_per_rank if (args.batch_per_rank and model_name == args.model) else None) or md['batch']
     use_graph = not args.no_graph
+    comm = ddls.runtime.communicator()
 
-    if args.impl == 'standin':
-        sys.path.insert(0, os.path.join(ROOT, 'baseline'))
-        import standin
-        return standin.run(args, ddls, md, B, K, W)
+    def max_over_ranks(v: float) -> float:
+        return max(comm.allgather_object(float(v))) if size > 1 else float(v)
 
     torch.manual_seed(1234)
-    model = getattr(ddls.models, args.model)(seed=1234).to(dev)
-    loss_name = model.loss_name
-    opt_name = model.optimizer_name
-    comm = ddls.runtime.communicator()
+    model = getattr(ddls.models, model_name)(seed=1234).to(dev)
+    loss_name, opt_name = model.loss_name, model.optimizer_name
     base_opt = ddls.optim.get_optimizer(opt_name, model.parameters(), comm=comm)
     base_opt.zero_grads_in_step = True
     ddls.broadcast_parameters(base_opt, root_rank=0)
@@ -133,11 +114,10 @@ def main():
     engine = StepEngine(model, optimizer=dopt, loss=loss_name, device=dev, use_cuda_graph=use_graph)
 
     # ---- data: a device pool larger than L2 for the kernel-only number; pinned host for e2e ------------
-    is_mnist = args.model == 'mnist_cnn'
+    is_mnist = model_name == 'mnist_cnn'
     bytes_per_batch = B * (784 * 4 + 10 * 4) if is_mnist else B * (md['seq'] + 1) * 4
     pool_n = max(8, min(4096, (160 << 20) // bytes_per_batch + 1))
-    host = make_batches(args.model, B, pool_n, seed=rank, device=dev)
-    from distributeddeeplearningspark_b200.ops.preprocess import mnist_preprocess
+    host = make_batches(model_name, B, pool_n, seed=rank, device=dev)
     if is_mnist:
         px = host['pixels'].to(dev); lab = host['labels'].to(dev)
         x_all, y_all = mnist_preprocess(px, lab)
@@ -175,7 +155,7 @@ def main():
     sync_all()
 
     # ---- kernel-only: device-resident inputs, CUDA events, max over ranks ---------------------------------
-    sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=100).start() if rank == 0 else None
+    sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=20).start() if (rank == 0 and with_clocks) else None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     ev0.record()
@@ -183,17 +163,12 @@ def main():
         train_step(i)
     ev1.record()
     sync_all()
-    ms = ev0.elapsed_time(ev1)
-    t = torch.tensor([ms], device=dev)
-    if size > 1:
-        import torch.distributed as dist
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+    ms = max_over_ranks(ev0.elapsed_time(ev1))
     last_loss = float(engine.step(pool_x[0], pool_y[0]).item())
 
     # ---- end to end: pinned host -> H2D every step, device -> host loss read every step -------------------
     e2e = None
-    if not args.no_e2e:
+    if with_e2e and not args.no_e2e:
         n_host = min(pool_n, 512)
         if is_mnist:
             hp = host['pixels'][:n_host * B].reshape(n_host, B, 784).pin_memory()
@@ -226,26 +201,24 @@ def main():
         e2e_losses = engine.run_stream(host_batches(K), pool_x[0], pool_y[0], stage=stage)
         sync_all()
         assert len(e2e_losses) == K
-        e2e_s = time.perf_counter() - t0
-        te = torch.tensor([e2e_s], device=dev)
-        if size > 1:
-            import torch.distributed as dist
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-        e2e_s = float(te.item())
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
         e2e = {'value': B * size * K / e2e_s, 'unit': md['unit'], 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': 4,
                'ms_per_step': 1e3 * e2e_s / K}
 
     clocks = sampler.stop() if sampler is not None else None
     value = B * size * K / (ms / 1e3)
-    pub = PUBLISHED.get(args.model)
-    out = {
+    pub = PUBLISHED.get(model_name)
+    fused = bool(getattr(dopt, '_fused', False))
+    return {
         'metric': md['metric'], 'value': value, 'unit': md['unit'], 'n_gpus': size, 'steps': K, 'warmup': W,
         'ms_per_step': ms / K, 'higher_is_better': True, 'scaling': 'weak',
         'vs_baseline': (value / pub) if pub else None, 'dtype': 'bf16 tensor-core operands, fp32 accumulate/master',
         'data': 'synthetic', 'impl': 'ours',
-        'config': {'model': args.model, 'global_batch': B * size, 'per_rank_batch': B, 'seq_len': md['seq'],
+        'config': {'model': model_name, 'global_batch': B * size, 'per_rank_batch': B, 'seq_len': md['seq'],
                    'parallelism': f'dp{size}', 'optimizer': opt_name, 'loss': loss_name,
-                   'comm': type(comm).__name__, 'cuda_graph': bool(engine.use_cuda_graph and (engine._graph is not None or
+                   'comm': type(comm).__name__,
+                   'dp_step': ([dopt._bucket_mode(b) for b in dopt.buckets] if fused else ('unfused' if size > 1 else 'single rank')),
+                   'cuda_graph': bool(engine.use_cuda_graph and (engine._graph is not None or
                                                                  getattr(engine, '_ds_graph', None) is not None)),
                    'l2': (f'inputs rotate through a {pool_bytes >> 20} MB device pool (> 126 MB L2)'
                           if pool_bytes > (126 << 20) else f'{pool_bytes >> 20} MB input pool (smaller than L2)'),
@@ -254,6 +227,103 @@ def main():
         'e2e': e2e, 'gpu_launches': int(per_step_launches * K), 'gpu_launches_per_step': int(per_step_launches),
         'clocks': clocks, 'final_loss': last_loss,
     }
+
+
+def allreduce_latency(ddls, sizes=(4 << 10, 256 << 10, 4 << 20)):
+    """Device time per allreduce call (fp32 SUM, in place), this library's selected algorithm vs NCCL, both timed inside a
+    CUDA graph of 16 calls (no host launch overhead on either side), max over ranks.  The third leg of BASELINE.json's
+    metric ("allreduce us")."""
+    import torch
+    import torch.distributed as dist
+    rank, size, dev = ddls.rank(), ddls.size(), ddls.device()
+    comm = ddls.runtime.communicator()
+    if size == 1 or not hasattr(comm, 'select_algo'):
+        return None
+    names = {0: 'oneshot', 1: 'twoshot', 2: 'nvls', 3: 'flag-in-data'}
+
+    def graph_us(fn, calls=16, replays=10):
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            for _ in range(3):
+                fn()
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev); comm.barrier(); torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(calls):
+                fn()
+        g.replay(); torch.cuda.synchronize(dev); comm.barrier(); torch.cuda.synchronize(dev)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(replays):
+            g.replay()
+        b.record(); torch.cuda.synchronize(dev)
+        return max(comm.allgather_object(a.elapsed_time(b) / (replays * calls) * 1e3))
+
+    out = {}
+    nccl_group = None
+    try:
+        nccl_group = dist.group.WORLD if dist.get_backend() == 'nccl' else dist.new_group(backend='nccl')
+    except Exception:  # noqa: BLE001
+        nccl_group = None
+    for nbytes in sizes:
+        n = nbytes // 4
+        t = comm.alloc(n)
+        row = {'ours_us': graph_us(lambda: comm.allreduce_(t, ddls.Sum)),
+               'algorithm': names[comm.select_algo(nbytes, True, bool(comm.mc_base))]}
+        if nccl_group is not None:
+            tn = torch.zeros(n, device=dev)
+            try:
+                row['nccl_us'] = graph_us(lambda: dist.all_reduce(tn, group=nccl_group))
+            except Exception as e:  # noqa: BLE001
+                row['nccl_us'] = None
+        out[str(nbytes)] = row
+    return out
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        return reference_arm(args)
+
+    import torch
+    import distributeddeeplearningspark_b200 as ddls
+
+    if not torch.cuda.is_available():
+        print(json.dumps({'impl': args.impl, 'unavailable': 'no CUDA device visible'}))
+        return 0
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            print(json.dumps({'impl': args.impl, 'unavailable':
+                              f'--gpus {args.gpus} must be launched with torch.distributed.run (one rank per GPU)'}))
+            return 0
+    if args.comm:
+        os.environ['DDLS_COMM'] = args.comm
+    ddls.init()
+    rank = ddls.rank()
+    K, W = args.steps, max(3, args.warmup)
+
+    if args.impl == 'standin':
+        sys.path.insert(0, os.path.join(ROOT, 'baseline'))
+        import standin
+        md = MODEL_DEFAULTS[args.model]
+        return standin.run(args, ddls, md, args.batch_per_rank or md['batch'], K, W)
+
+    out = measure(args, args.model, ddls, K, W)
+    # BASELINE.json's metric has three legs: MNIST images/s (the primary line), NYISO LSTM samples/s and allreduce latency.
+    # The default run measures all three so that the driver's record carries them at every N.
+    if args.model == 'mnist_cnn' and not args.no_secondary:
+        sec = measure(args, 'nyiso_lstm', ddls, K, W, with_clocks=False)
+        pub = PUBLISHED['nyiso_lstm']
+        out['secondary'] = {k: sec[k] for k in ('metric', 'value', 'unit', 'ms_per_step', 'steps', 'warmup', 'e2e',
+                                                'gpu_launches', 'gpu_launches_per_step', 'final_loss')}
+        out['secondary']['vs_published'] = sec['value'] / pub
+        out['secondary']['published'] = {'value': pub, 'unit': 'samples/s', 'what': '4 CPU workers, ddl_nyiso_hdi.ipynb:817-818'}
+        out['secondary']['config'] = sec['config']
+        if ddls.size() > 1:
+            out['allreduce_us'] = allreduce_latency(ddls)
     if rank == 0:
         print(json.dumps(out))
     ddls.shutdown()

@@ -8,6 +8,8 @@
 //   unpool_relu_bwd       max-pool / ReLU backward to a dense dz2 map + conv2 bias gradient
 //   (conv2 forward+pool, data gradient and weight gradient: csrc/cnn_tma.cu, TMA-fed tcgen05 implicit GEMMs)
 //   conv1_wgrad           FMA reduction for the 3x3x1x32 kernel and its bias
+#include <atomic>
+
 #include "common.cuh"
 #include "../include/ddls_b200.h"
 
@@ -18,21 +20,24 @@ constexpr int K2 = 9 * CH;                                      // conv2 reducti
 constexpr int CT = 256;                                         // threads per CTA in the tcgen05 kernels
 
 // ------------------------------------------------------------------------------------------------
-// conv1 + bias + ReLU : x [B,28,28,1] fp32 -> a1 [B,26,26,32] bf16.  One CTA per image.
+// conv1 + bias + ReLU : x [B,28,28,1] fp32 -> a1 [B,26,26,32] bf16.  Two CTAs per image (13 output rows each): a
+// batch of 128 then fills every SM instead of 128 of 148, and the per-CTA dependent chain is half as long.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) conv1_relu_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                              const float* __restrict__ bias,
                                                              __nv_bfloat16* __restrict__ a1, int B) {
+  pdl_wait();
   __shared__ float sx[IMG * IMG];
   __shared__ float sw[9 * CH];
   __shared__ float sb[CH];
-  const int b = blockIdx.x;
+  const int b = blockIdx.x >> 1, half = blockIdx.x & 1;
   for (int i = threadIdx.x; i < IMG * IMG; i += blockDim.x) sx[i] = x[(size_t)b * IMG * IMG + i];
   for (int i = threadIdx.x; i < 9 * CH; i += blockDim.x) sw[i] = w[i];
   if (threadIdx.x < CH) sb[threadIdx.x] = bias[threadIdx.x];
   __syncthreads();
   // item = (pixel, group of 8 channels); 4 consecutive threads write one pixel's 64 bytes
-  for (int it = threadIdx.x; it < C1 * C1 * 4; it += blockDim.x) {
+  constexpr int HALF_ITEMS = C1 * C1 * 2;            // 13 rows x 26 pixels x 4 channel groups
+  for (int it = half * HALF_ITEMS + threadIdx.x; it < (half + 1) * HALF_ITEMS; it += blockDim.x) {
     const int pix = it >> 2, cg = it & 3;
     const int oh = pix / C1, ow = pix - oh * C1;
     float acc[8];
@@ -59,6 +64,7 @@ __global__ void __launch_bounds__(256) conv1_relu_fwd_kernel(const float* __rest
 __global__ void __launch_bounds__(256) relu_bwd_bias_kernel(const float* __restrict__ da, const float* __restrict__ a,
                                                             __nv_bfloat16* __restrict__ dz, float* __restrict__ db,
                                                             int B, int F, int ldz) {
+  pdl_wait();
   const int f = blockIdx.x * blockDim.x + threadIdx.x;
   if (f >= ldz) return;
   float s = 0.f;
@@ -79,6 +85,7 @@ __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const __nv_bfloat1
                                                               const uint8_t* __restrict__ pidx,
                                                               __nv_bfloat16* __restrict__ dz2, float* __restrict__ db2,
                                                               int B) {
+  pdl_wait();
   __shared__ float sdb[CH];
   if (threadIdx.x < CH) sdb[threadIdx.x] = 0.f;
   __syncthreads();
@@ -124,6 +131,7 @@ __global__ void __launch_bounds__(256) unpool_relu_bwd_kernel(const __nv_bfloat1
 // out[i] = sum_s partial[s][i] : 8 lanes cooperate on one output
 __global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restrict__ partial, float* __restrict__ out,
                                                            int n, int splits) {
+  pdl_wait();
   const int gid = blockIdx.x * blockDim.x + threadIdx.x;
   const int i = gid >> 3, sub = gid & 7;
   float acc = 0.f;
@@ -143,6 +151,7 @@ __global__ void __launch_bounds__(256) sum_partials_kernel(const float* __restri
 __global__ void __launch_bounds__(640) conv1_wgrad_kernel(const float* __restrict__ x,
                                                           const __nv_bfloat16* __restrict__ dz1,
                                                           float* __restrict__ partial, int B) {
+  pdl_wait();
   extern __shared__ __align__(16) uint8_t smem[];
   __nv_bfloat16* sdz = reinterpret_cast<__nv_bfloat16*>(smem);                       // [676][32]
   float* sx = reinterpret_cast<float*>(smem + C1 * C1 * CH * 2);                     // [784]
@@ -197,7 +206,7 @@ using namespace ddls;
 
 extern "C" int ddls_cnn_conv1_fwd(const float* x, const float* w1, const float* b1, void* a1, int B, void* stream) {
   if (B <= 0) return 0;
-  conv1_relu_fwd_kernel<<<B, 256, 0, ST(stream)>>>(x, w1, b1, static_cast<__nv_bfloat16*>(a1), B);
+  DDLS_CUDA_OK(launch_k(conv1_relu_fwd_kernel, dim3(2 * B), dim3(256), 0, ST(stream), x, w1, b1, static_cast<__nv_bfloat16*>(a1), B));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "conv1_relu_fwd_kernel launch");
 }
@@ -206,7 +215,7 @@ extern "C" int ddls_relu_bwd_bias(const float* da, const float* a, void* dz, flo
                                   void* stream) {
   if (B <= 0) return 0;
   dim3 grid((ldz + 255) / 256, B < 8 ? B : 8);
-  relu_bwd_bias_kernel<<<grid, 256, 0, ST(stream)>>>(da, a, static_cast<__nv_bfloat16*>(dz), db, B, F, ldz);
+  DDLS_CUDA_OK(launch_k(relu_bwd_bias_kernel, grid, dim3(256), 0, ST(stream), da, a, static_cast<__nv_bfloat16*>(dz), db, B, F, ldz));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "relu_bwd_bias_kernel launch");
 }
@@ -215,9 +224,9 @@ extern "C" int ddls_cnn_unpool_bwd(const void* dflat, const void* pooled, const 
                                    void* stream) {
   if (B <= 0) return 0;
   const int total = B * PL * PL * 4;
-  unpool_relu_bwd_kernel<<<(total + 255) / 256, 256, 0, ST(stream)>>>(
+  DDLS_CUDA_OK(launch_k(unpool_relu_bwd_kernel, dim3((total + 255) / 256), dim3(256), 0, ST(stream),
       static_cast<const __nv_bfloat16*>(dflat), static_cast<const __nv_bfloat16*>(pooled),
-      static_cast<const uint8_t*>(pidx), static_cast<__nv_bfloat16*>(dz2), db2, B);
+      static_cast<const uint8_t*>(pidx), static_cast<__nv_bfloat16*>(dz2), db2, B));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "unpool_relu_bwd_kernel launch");
 }
@@ -233,9 +242,9 @@ extern "C" int ddls_cnn_conv1_wgrad(const float* x, const void* dz1, float* dw1_
   const int smem = C1 * C1 * CH * 2 + IMG * IMG * 4;
   DDLS_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   float* part = static_cast<float*>(scratch);
-  conv1_wgrad_kernel<<<B, 640, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
+  DDLS_CUDA_OK(launch_k(conv1_wgrad_kernel, dim3(B), dim3(640), smem, ST(stream), x, static_cast<const __nv_bfloat16*>(dz1), part, B));
   // per-image partial rows are [9*32 dW1 | 32 db1]; the output buffer has the same 320-float layout
-  sum_partials_kernel<<<(320 * 8 + 255) / 256, 256, 0, ST(stream)>>>(part, dw1_db1, 320, B);
+  DDLS_CUDA_OK(launch_k(sum_partials_kernel, dim3((320 * 8 + 255) / 256), dim3(256), 0, ST(stream), part, dw1_db1, 320, B));
   count_launch(2);
   return check_cuda(cudaGetLastError(), "conv1_wgrad launch");
 }
@@ -266,7 +275,9 @@ namespace ddls {
 constexpr int NOALLOC_MAX_B = DDLS_NOALLOC_CONV1_MAX_BATCH;
 static __device__ __align__(256) float g_conv1_wgrad_scratch[(size_t)NOALLOC_MAX_B * 10 * CH];
 constexpr int NOALLOC_MAX_DEVICES = 64;
-static float* g_conv1_scratch_addr[NOALLOC_MAX_DEVICES] = {};
+// resolved once per device; atomic because two host threads may make the first call on a device at the same time (both
+// would store the same address, but a plain static is still a data race)
+static std::atomic<float*> g_conv1_scratch_addr[NOALLOC_MAX_DEVICES];
 }  // namespace ddls
 
 extern "C" int ddls_cnn_conv1_wgrad_noalloc(const float* x, const void* dz1, float* dw1_db1, int B, void* stream) {
@@ -282,17 +293,17 @@ extern "C" int ddls_cnn_conv1_wgrad_noalloc(const float* x, const void* dz1, flo
     set_last_error("ddls_cnn_conv1_wgrad_noalloc: device ordinal %d out of range", dev);
     return 1;
   }
-  if (g_conv1_scratch_addr[dev] == nullptr) {   // first call on this device: resolve the symbol's device address
+  if (g_conv1_scratch_addr[dev].load(std::memory_order_acquire) == nullptr) {   // first call on this device: resolve the symbol's device address
     float* p = nullptr;
     DDLS_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_conv1_wgrad_scratch));
     const int smem0 = C1 * C1 * CH * 2 + IMG * IMG * 4;
     DDLS_CUDA_OK(cudaFuncSetAttribute(conv1_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem0));
-    g_conv1_scratch_addr[dev] = p;
+    g_conv1_scratch_addr[dev].store(p, std::memory_order_release);
   }
-  float* part = g_conv1_scratch_addr[dev];
+  float* part = g_conv1_scratch_addr[dev].load(std::memory_order_acquire);
   const int smem = C1 * C1 * CH * 2 + IMG * IMG * 4;
-  conv1_wgrad_kernel<<<B, 640, smem, ST(stream)>>>(x, static_cast<const __nv_bfloat16*>(dz1), part, B);
-  sum_partials_kernel<<<(320 * 8 + 255) / 256, 256, 0, ST(stream)>>>(part, dw1_db1, 320, B);
+  DDLS_CUDA_OK(launch_k(conv1_wgrad_kernel, dim3(B), dim3(640), smem, ST(stream), x, static_cast<const __nv_bfloat16*>(dz1), part, B));
+  DDLS_CUDA_OK(launch_k(sum_partials_kernel, dim3((320 * 8 + 255) / 256), dim3(256), 0, ST(stream), part, dw1_db1, 320, B));
   count_launch(2);
   return check_cuda(cudaGetLastError(), "conv1_wgrad (no-alloc) launch");
 }

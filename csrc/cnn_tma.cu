@@ -82,12 +82,13 @@ __global__ void __launch_bounds__(CV_THREADS, 1) conv2_tma_kernel(const __grid_c
     tma_prefetch_desc(&tmap);
   }
   if (warp == 1) tmem_alloc(&tmem_slot, 64);
-  stage_filter<DGRAD>(sB, p.w2);
   // rows ROWS..127 of every tap block are never written by TMA: clear them once so the unused accumulator rows stay finite
   for (int i = threadIdx.x; i < CV_STAGES * 9 * (128 - ROWS) * 4; i += blockDim.x) {
     const int blk = i / ((128 - ROWS) * 4), r = i - blk * (128 - ROWS) * 4;
     *reinterpret_cast<uint4*>(smem + blk * TAP_BYTES + ROWS * 64 + r * 16) = make_uint4(0u, 0u, 0u, 0u);
   }
+  pdl_wait();                                         // everything above overlapped the previous kernel's tail
+  stage_filter<DGRAD>(sB, p.w2);
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -246,6 +247,7 @@ conv2_wgrad_tma_kernel(const __grid_constant__ CUtensorMap ta, const __grid_cons
     const int s = i / (3 * (TAP_BYTES / 16)), r = i - s * 3 * (TAP_BYTES / 16);
     *reinterpret_cast<uint4*>(smem + s * WG_STAGE_BYTES + 9 * TAP_BYTES + r * 16) = make_uint4(0u, 0u, 0u, 0u);
   }
+  pdl_wait();                                         // everything above overlapped the previous kernel's tail
   fence_proxy_async_smem();
   tc_fence_before();
   __syncthreads();
@@ -353,7 +355,7 @@ extern "C" int ddls_cnn_conv2_pool_fwd(const void* a1, const float* w2, const fl
   ConvParams p{w2, b2, nullptr, static_cast<__nv_bfloat16*>(pooled), static_cast<uint8_t*>(pidx), B, B * 6};
   DDLS_CUDA_OK(cudaFuncSetAttribute(conv2_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, CV_SMEM));
   const int grid = p.tiles < conv_sm_count() ? p.tiles : conv_sm_count();
-  conv2_tma_kernel<false><<<grid, CV_THREADS, CV_SMEM, static_cast<cudaStream_t>(stream)>>>(tm, p);
+  DDLS_CUDA_OK(launch_k(conv2_tma_kernel<false>, dim3(grid), dim3(CV_THREADS), CV_SMEM, static_cast<cudaStream_t>(stream), tm, p));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "conv2_tma_kernel<fwd> launch");
 }
@@ -365,7 +367,7 @@ extern "C" int ddls_cnn_conv2_dgrad(const void* dz2, const float* w2, const void
   ConvParams p{w2, nullptr, static_cast<const __nv_bfloat16*>(a1), static_cast<__nv_bfloat16*>(dz1), nullptr, B, B * 7};
   DDLS_CUDA_OK(cudaFuncSetAttribute(conv2_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, CV_SMEM));
   const int grid = p.tiles < conv_sm_count() ? p.tiles : conv_sm_count();
-  conv2_tma_kernel<true><<<grid, CV_THREADS, CV_SMEM, static_cast<cudaStream_t>(stream)>>>(tm, p);
+  DDLS_CUDA_OK(launch_k(conv2_tma_kernel<true>, dim3(grid), dim3(CV_THREADS), CV_SMEM, static_cast<cudaStream_t>(stream), tm, p));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "conv2_tma_kernel<dgrad> launch");
 }
@@ -396,9 +398,9 @@ extern "C" int ddls_cnn_conv2_wgrad(const void* a1, const void* dz2, float* dw2,
   if (nhwc_map(&ta, a1, B, C1, C2) || nhwc_map(&tz, dz2, B, C2, C2)) return 1;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   DDLS_CUDA_OK(cudaFuncSetAttribute(conv2_wgrad_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WG_SMEM));
-  conv2_wgrad_tma_kernel<<<grid, CV_THREADS, WG_SMEM, st>>>(ta, tz, static_cast<float*>(scratch), tiles);
+  DDLS_CUDA_OK(launch_k(conv2_wgrad_tma_kernel, dim3(grid), dim3(CV_THREADS), WG_SMEM, st, ta, tz, static_cast<float*>(scratch), tiles));
   const int n = K2 * CH;
-  sum_partials_kernel<<<(n * 8 + 255) / 256, 256, 0, st>>>(static_cast<const float*>(scratch), dw2, n, grid);
+  DDLS_CUDA_OK(launch_k(sum_partials_kernel, dim3((n * 8 + 255) / 256), dim3(256), 0, st, static_cast<const float*>(scratch), dw2, n, grid));
   count_launch(2);
   return check_cuda(cudaGetLastError(), "conv2_wgrad_tma launch");
 }

@@ -269,6 +269,7 @@ DDLS_DEVINL uint4 ll_wait(const CommCtx& c, const uint4* p, uint32_t epoch, int 
 template <typename Wire>
 __global__ void __launch_bounds__(COMM_THREADS) allreduce_oneshot_ll_kernel(CommCtx c, ArParams p, OptFuse opt) {
   constexpr bool F32 = sizeof(Wire) == 4;
+  pdl_wait();
   int t_step = 0;
   float lr_t = 0.f;
   if (opt.kind != 0) {
@@ -508,6 +509,7 @@ constexpr int DP_THREADS = 256;  // ~120 registers per thread: a 256-thread CTA 
 template <bool MC, int KIND>
 __global__ void __launch_bounds__(DP_THREADS, 1) dp_step_kernel(CommCtx c, DpStep p, ShadowSet sh) {
   const int rank = c.rank_base + blockIdx.y;
+  pdl_wait();
   const uint32_t e0 = read_epoch(c, rank);
   const int t_step = *reinterpret_cast<volatile int*>(p.step) + 1;
   __shared__ float s_lr_t;
@@ -790,6 +792,11 @@ static int make_ctx(const DdlsCommDesc* d, CommCtx* c) {
   return 0;
 }
 
+static bool is_dp_step_kernel(const void* k) {
+  return k == (const void*)dp_step_kernel<true, 1> || k == (const void*)dp_step_kernel<true, 2> || k == (const void*)dp_step_kernel<true, 3> ||
+         k == (const void*)dp_step_kernel<false, 1> || k == (const void*)dp_step_kernel<false, 2> || k == (const void*)dp_step_kernel<false, 3>;
+}
+
 template <typename... Args>
 static int launch(const DdlsCommDesc* d, void (*kern)(Args...), int blocks, int threads, cudaStream_t st, Args... args) {
   if (d->emulate && blocks * d->world > 128) blocks = 128 / d->world;   // all emulated blocks must be co-resident
@@ -800,7 +807,13 @@ static int launch(const DdlsCommDesc* d, void (*kern)(Args...), int blocks, int 
     void* ptrs[] = {(void*)&args...};
     DDLS_CUDA_OK(cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(threads), ptrs, 0, st));
   } else {
-    kern<<<grid, threads, 0, st>>>(args...);
+    // only the kernels that call pdl_wait() may be launched with the programmatic-serialization attribute
+    if ((const void*)kern == (const void*)allreduce_oneshot_ll_kernel<float> ||
+        (const void*)kern == (const void*)allreduce_oneshot_ll_kernel<__nv_bfloat16> || is_dp_step_kernel((const void*)kern)) {
+      DDLS_CUDA_OK(launch_k(kern, grid, dim3(threads), 0, st, args...));
+    } else {
+      kern<<<grid, threads, 0, st>>>(args...);
+    }
   }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "comm kernel launch");

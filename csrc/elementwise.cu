@@ -18,6 +18,7 @@ static inline int ew_grid(size_t n_vec) {
 }
 
 __global__ void __launch_bounds__(EW_THREADS) refresh_shadows_kernel(const float4* __restrict__ p, size_t n4, ShadowSet sh) {
+  pdl_wait();
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     if (4 * i + 4 <= sh.lo || 4 * i >= sh.hi) continue;
     const float4 pi = p[i];
@@ -45,6 +46,7 @@ __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p
                                                           float4* __restrict__ m, float4* __restrict__ v, int* step,
                                                           size_t n4, float lr, float b1, float b2, float eps,
                                                           float gs, int zero_grads, ShadowSet sh) {
+  pdl_wait();
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   __shared__ float s_lr_t;                 // two powf per thread cost more than the update itself: one thread computes
   if (threadIdx.x == 0) s_lr_t = lr * sqrtf(1.0f - powf(b2, (float)t)) / (1.0f - powf(b1, (float)t));
@@ -70,6 +72,7 @@ __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p
 __global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict__ p, float4* __restrict__ g,
                                                              float4* __restrict__ a, int* step, size_t n4, float lr,
                                                              float eps, float gs, int zero_grads, ShadowSet sh) {
+  pdl_wait();
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
     float4 gi = g[i], ai = a[i], pi = p[i];
@@ -87,6 +90,7 @@ __global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict_
 
 __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, int* step,
                                                          size_t n4, float lr, float gs, int zero_grads, ShadowSet sh) {
+  pdl_wait();
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   const float a = lr * gs;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -105,6 +109,7 @@ __global__ void __launch_bounds__(EW_THREADS) mnist_preprocess_kernel(const uint
                                                                       float* __restrict__ x, float* __restrict__ onehot,
                                                                       int n, int npix, int classes, float o_min,
                                                                       float scale, float n_min) {
+  pdl_wait();
   const size_t total4 = (size_t)n * npix / 4;
   const uchar4* pix4 = reinterpret_cast<const uchar4*>(pix);
   float4* x4 = reinterpret_cast<float4*>(x);
@@ -140,7 +145,7 @@ extern "C" int ddls_adam_step(float* params, float* grads, float* m, float* v, i
                               const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
   if (n == 0) return 0;
   if (check_flat(params, n, "ddls_adam_step") || check_flat(grads, n, "ddls_adam_step")) return 1;
-  adam_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(adam_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
       reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(m),
       reinterpret_cast<float4*>(v), step, n / 4, lr, beta1, beta2, eps, grad_scale, zero_grads,
       make_shadows(shadows, n_shadows));
@@ -153,7 +158,7 @@ extern "C" int ddls_adagrad_step(float* params, float* grads, float* acc, int* s
                                  void* stream) {
   if (n == 0) return 0;
   if (check_flat(params, n, "ddls_adagrad_step") || check_flat(grads, n, "ddls_adagrad_step")) return 1;
-  adagrad_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(adagrad_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
       reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(acc), step, n / 4,
       lr, eps, grad_scale, zero_grads, make_shadows(shadows, n_shadows));
   count_launch(1);
@@ -164,7 +169,7 @@ extern "C" int ddls_sgd_step(float* params, float* grads, int* step, size_t n, f
                              int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
   if (n == 0) return 0;
   if (check_flat(params, n, "ddls_sgd_step") || check_flat(grads, n, "ddls_sgd_step")) return 1;
-  sgd_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(sgd_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
       reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), step, n / 4, lr, grad_scale, zero_grads,
       make_shadows(shadows, n_shadows));
   count_launch(1);
@@ -182,6 +187,7 @@ __global__ void __launch_bounds__(EW_THREADS) gather_batch_kernel(const VecT* __
                                                                   VecT* __restrict__ x, VecT* __restrict__ y,
                                                                   const int* __restrict__ perm, unsigned* cursor,
                                                                   int B, long long N, int xw, int yw) {
+  pdl_wait();
   const unsigned long long k = cursor[0];
   const size_t total_x = (size_t)B * xw, total = total_x + (size_t)B * yw;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
@@ -217,13 +223,13 @@ extern "C" int ddls_gather_batch(const void* X, const void* Y, void* x, void* y,
     const int xw = (int)(row_x_bytes / 16), yw = (int)(row_y_bytes / 16);
     int blocks = ew_grid((size_t)B * (xw + yw));
     if (blocks > 64) blocks = 64;
-    gather_batch_kernel<uint4><<<blocks, EW_THREADS, 0, st>>>(static_cast<const uint4*>(X), static_cast<const uint4*>(Y),
+    launch_k(gather_batch_kernel<uint4>, dim3(blocks), dim3(EW_THREADS), 0, st, static_cast<const uint4*>(X), static_cast<const uint4*>(Y),
                                                                static_cast<uint4*>(x), static_cast<uint4*>(y), perm, cursor, B, N, xw, yw);
   } else {
     const int xw = (int)(row_x_bytes / 4), yw = (int)(row_y_bytes / 4);
     int blocks = ew_grid((size_t)B * (xw + yw));
     if (blocks > 64) blocks = 64;
-    gather_batch_kernel<uint32_t><<<blocks, EW_THREADS, 0, st>>>(static_cast<const uint32_t*>(X), static_cast<const uint32_t*>(Y),
+    launch_k(gather_batch_kernel<uint32_t>, dim3(blocks), dim3(EW_THREADS), 0, st, static_cast<const uint32_t*>(X), static_cast<const uint32_t*>(Y),
                                                                   static_cast<uint32_t*>(x), static_cast<uint32_t*>(y), perm, cursor, B, N, xw, yw);
   }
   count_launch(1);
@@ -234,7 +240,7 @@ extern "C" int ddls_mnist_preprocess(const uint8_t* pixels, const int64_t* label
                                      int npix, int classes, float o_min, float scale, float n_min, void* stream) {
   if (n <= 0) return 0;
   if (((size_t)n * npix) % 4 != 0) { set_last_error("ddls_mnist_preprocess: n*npix must be a multiple of 4"); return 1; }
-  mnist_preprocess_kernel<<<ew_grid((size_t)n * npix / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(mnist_preprocess_kernel, dim3(ew_grid((size_t)n * npix / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
       pixels, labels, x, onehot, n, npix, classes, o_min, scale, n_min);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "mnist_preprocess_kernel launch");
@@ -244,7 +250,7 @@ extern "C" int ddls_refresh_shadows(const float* params, size_t n, const DdlsSha
                                     void* stream) {
   if (n == 0 || n_shadows <= 0) return 0;
   if (check_flat(params, n, "ddls_refresh_shadows")) return 1;
-  refresh_shadows_kernel<<<ew_grid(n / 4), EW_THREADS, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(refresh_shadows_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
       reinterpret_cast<const float4*>(params), n / 4, make_shadows(shadows, n_shadows));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "refresh_shadows_kernel launch");

@@ -72,6 +72,7 @@ DDLS_DEVINL uint32_t gemm_pipe_run(uint8_t* smem, uint64_t* mma_done, uint32_t* 
   const uint32_t tmem_d = tmem_base_s;
   constexpr uint32_t idesc = umma_idesc_bf16(GEMM_BM, BN, A_MN, B_MN);
   const int nkb = (kend - kbeg + GEMM_KC - 1) / GEMM_KC;
+  pdl_wait();                             // TMEM / barrier set-up above overlapped the previous kernel's tail
 
   auto issue_loads = [&](int kb) {
     uint8_t* sa = smem + (kb % V2_STAGES) * STAGE;

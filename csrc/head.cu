@@ -37,6 +37,7 @@ __global__ void __launch_bounds__(XH_THREADS) head_softmax_xent_kernel(
     const float* __restrict__ onehot, float* __restrict__ probs, float* __restrict__ loss, float* __restrict__ da_f32,
     __nv_bfloat16* __restrict__ da_bf16, int ldz, float* __restrict__ dw, float* __restrict__ db,
     float* __restrict__ dprev_bias, float* __restrict__ scratch, int B, int F, int C, int relu_input) {
+  pdl_wait();
   extern __shared__ float sm[];
   float* sw = sm;                               // [F][C]
   float* sa = sw + F * C;                       // [XH_ROWS][F]
@@ -157,6 +158,7 @@ __global__ void __launch_bounds__(MH_THREADS, 1) head_mse_kernel(const float* __
                                                                  float* __restrict__ pred, float* __restrict__ loss,
                                                                  float* __restrict__ dh, float* __restrict__ dwd,
                                                                  float* __restrict__ dbd, int B, int H) {
+  pdl_wait();
   extern __shared__ float sm[];
   float* sd = sm;                    // [B][O]  dL/dpred
   __shared__ float sloss[MH_THREADS / 32];
@@ -223,6 +225,7 @@ template <int O>
 __global__ void __launch_bounds__(256) head_mse_rows_kernel(const float* __restrict__ h, const float* __restrict__ wd,
                                                             const float* __restrict__ bd, const float* __restrict__ y,
                                                             float* __restrict__ pred, float* __restrict__ dh, int B, int H) {
+  pdl_wait();
   const int lane = threadIdx.x & 31, b = blockIdx.x * 8 + (threadIdx.x >> 5);
   if (b >= B) return;
   const float inv = 1.0f / ((float)B * (float)O);
@@ -254,6 +257,7 @@ template <int O>
 __global__ void __launch_bounds__(256) head_mse_cols_kernel(const float* __restrict__ h, const float* __restrict__ y,
                                                             const float* __restrict__ pred, float* __restrict__ loss,
                                                             float* __restrict__ dwd, float* __restrict__ dbd, int B, int H) {
+  pdl_wait();
   __shared__ float red[8][32][O];
   __shared__ float red2[8][O + 1];
   const int lane = threadIdx.x & 31, ry = threadIdx.x >> 5;
@@ -309,8 +313,8 @@ extern "C" int ddls_dense_mse(const float* h, const float* wd, const float* bd, 
   if ((size_t)B * H > 32768) {
 #define DDLS_LAUNCH_MSE_BIG(OO)                                                                                    \
   {                                                                                                                 \
-    head_mse_rows_kernel<OO><<<(B + 7) / 8, 256, 0, st0>>>(h, wd, bd, y, pred, dh, B, H);                          \
-    if (y != nullptr) head_mse_cols_kernel<OO><<<(H + 31) / 32, 256, 0, st0>>>(h, y, pred, loss, dwd, dbd, B, H);   \
+    launch_k(head_mse_rows_kernel<OO>, dim3((B + 7) / 8), dim3(256), 0, st0, h, wd, bd, y, pred, dh, B, H);                          \
+    if (y != nullptr) launch_k(head_mse_cols_kernel<OO>, dim3((H + 31) / 32), dim3(256), 0, st0, h, y, pred, loss, dwd, dbd, B, H);   \
   }
     switch (O) {
       case 1: DDLS_LAUNCH_MSE_BIG(1) break;
@@ -329,7 +333,7 @@ extern "C" int ddls_dense_mse(const float* h, const float* wd, const float* bd, 
   {                                                                                                                 \
     if (smem > 48 * 1024)                                                                                           \
       DDLS_CUDA_OK(cudaFuncSetAttribute(head_mse_kernel<OO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-    head_mse_kernel<OO><<<1, MH_THREADS, smem, st>>>(h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H);                 \
+    launch_k(head_mse_kernel<OO>, dim3(1), dim3(MH_THREADS), smem, st, h, wd, bd, y, pred, loss, dh, dwd, dbd, B, H);                 \
   }
   switch (O) {
     case 1: DDLS_LAUNCH_MSE(1) break;
@@ -361,10 +365,10 @@ extern "C" int ddls_dense_softmax_xent(const float* a, const float* w, const flo
   const size_t smem = ((size_t)F * C + (size_t)XH_ROWS * F + (size_t)XH_ROWS * CCsel) * sizeof(float);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   if (C == 10)
-    head_softmax_xent_kernel<10><<<blocks, XH_THREADS, smem, st>>>(a, w, bias, onehot, probs, loss, da_f32,
+    launch_k(head_softmax_xent_kernel<10>, dim3(blocks), dim3(XH_THREADS), smem, st, a, w, bias, onehot, probs, loss, da_f32,
         static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, scratch, B, F, C, relu_input);
   else
-    head_softmax_xent_kernel<XH_MAXC><<<blocks, XH_THREADS, smem, st>>>(a, w, bias, onehot, probs, loss, da_f32,
+    launch_k(head_softmax_xent_kernel<XH_MAXC>, dim3(blocks), dim3(XH_THREADS), smem, st, a, w, bias, onehot, probs, loss, da_f32,
         static_cast<__nv_bfloat16*>(da_bf16), ldz, dw, db, dprev_bias, scratch, B, F, C, relu_input);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "head_softmax_xent_kernel launch");

@@ -28,6 +28,7 @@ constexpr int R_KG = 18;            // k-groups in the weight image: 16 (hidden)
 __global__ void __launch_bounds__(256) rnn128_pack_kernel(const float* __restrict__ rec, const float* __restrict__ wih,
                                                           const float* __restrict__ bias, __nv_bfloat16* __restrict__ img,
                                                           int GH) {
+  pdl_wait();
   const int MG = GH / 8;
   const int total = R_KG * MG * 8;                  // one item = (k, m-group): 8 consecutive m
   for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
@@ -164,6 +165,7 @@ __global__ void __launch_bounds__(RCfg<NB>::ALL, 1) lstm_fwd_v2_kernel(LstmV2Fwd
   if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
+  pdl_wait();                                               // set-up above overlapped the previous kernel\'s drain
   if (tid == R_EPI) {                                        // bulk TMA copies bring the whole weight image
     mbar_expect_tx(&bar_w, W_BYTES);
 #pragma unroll
@@ -325,6 +327,7 @@ __global__ void __launch_bounds__(RCfg<NB>::ALL, 1) lstm_bwd_v2_kernel(LstmV2Bwd
   if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_mma, 1); mbar_fence_init(); }
   __syncthreads();
+  pdl_wait();                                               // set-up above overlapped the previous kernel\'s drain
   if (tid == R_EPI) {
     mbar_expect_tx(&bar_w, W_BYTES);
 #pragma unroll
@@ -523,6 +526,7 @@ __global__ void __launch_bounds__(RCfg<NB>::ALL, 1) gru_fwd_v2_kernel(GruV2Fwd p
   if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_a, 1); mbar_init(&bar_b, 1); mbar_fence_init(); }
   __syncthreads();
+  pdl_wait();                                               // set-up above overlapped the previous kernel\'s drain
   if (tid == R_EPI) {
     mbar_expect_tx(&bar_w, W_BYTES);
 #pragma unroll
@@ -723,6 +727,7 @@ __global__ void __launch_bounds__(RCfg<NB>::ALL, 1) gru_bwd_v2_kernel(GruV2Bwd p
   if (warp == RCfg<NB>::MMA_WARP) tmem_alloc(&tmem_s, TM_COLS);
   if (tid == 0) { mbar_init(&bar_w, 1); mbar_init(&bar_1, 1); mbar_init(&bar_2, 1); mbar_fence_init(); }
   __syncthreads();
+  pdl_wait();                                               // set-up above overlapped the previous kernel\'s drain
   if (tid == R_EPI) {
     mbar_expect_tx(&bar_w, W_BYTES);
 #pragma unroll
@@ -951,6 +956,7 @@ __global__ void __launch_bounds__(WG2_THREADS, 1) rnn128_wgrad_kernel(const uint
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
+  pdl_wait();
   const uint32_t tmem = tmem_s;
   const int nkb = kgroups / 8;
   if (warp == 0) {
@@ -1019,7 +1025,7 @@ extern "C" int ddls_rnn128_pack(const float* recurrent, const float* w_ih, const
   if (gates != 3 && gates != 4) { set_last_error("ddls_rnn128_pack: gates must be 3 (GRU) or 4 (LSTM)"); return 1; }
   const int GH = gates * RH;
   const int total = R_KG * (GH / 8) * 8;
-  rnn128_pack_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(rnn128_pack_kernel, dim3((total + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream), 
       recurrent, w_ih, bias, static_cast<__nv_bfloat16*>(image), GH);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "rnn128_pack_kernel launch");
@@ -1042,13 +1048,13 @@ extern "C" int ddls_lstm128_forward_v2(const float* x, const void* image, float*
   if (smem > 227 * 1024) { set_last_error("ddls_lstm128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
   if (nb == 16) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+    launch_k(lstm_fwd_v2_kernel<16>, dim3((B + 15) / 16), dim3(RCfg<16>::ALL), smem, st, p);
   } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
+    launch_k(lstm_fwd_v2_kernel<32>, dim3((B + 31) / 32), dim3(RCfg<32>::ALL), smem, st, p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_fwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+    launch_k(lstm_fwd_v2_kernel<64>, dim3((B + 63) / 64), dim3(RCfg<64>::ALL), smem, st, p);
   } else { set_last_error("ddls_lstm128_forward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_fwd_v2_kernel launch");
@@ -1066,13 +1072,13 @@ extern "C" int ddls_lstm128_backward_v2(const float* dout, const float* x, const
   if (smem > 227 * 1024) { set_last_error("ddls_lstm128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
   if (nb == 16) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+    launch_k(lstm_bwd_v2_kernel<16>, dim3((B + 15) / 16), dim3(RCfg<16>::ALL), smem, st, p);
   } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
+    launch_k(lstm_bwd_v2_kernel<32>, dim3((B + 31) / 32), dim3(RCfg<32>::ALL), smem, st, p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(lstm_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    lstm_bwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+    launch_k(lstm_bwd_v2_kernel<64>, dim3((B + 63) / 64), dim3(RCfg<64>::ALL), smem, st, p);
   } else { set_last_error("ddls_lstm128_backward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "lstm_bwd_v2_kernel launch");
@@ -1087,7 +1093,7 @@ extern "C" int ddls_rnn128_wgrad(const void* a_img, const void* b_img, float* C,
   constexpr int BN = 64;
   const int smem = WG2_STAGES * (8 * RH * 16 + 8 * BN * 16);
   DDLS_CUDA_OK(cudaFuncSetAttribute(rnn128_wgrad_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  rnn128_wgrad_kernel<BN><<<n / BN, WG2_THREADS, smem, static_cast<cudaStream_t>(stream)>>>(
+  launch_k(rnn128_wgrad_kernel<BN>, dim3(n / BN), dim3(WG2_THREADS), smem, static_cast<cudaStream_t>(stream), 
       static_cast<const uint8_t*>(a_img), static_cast<const uint8_t*>(b_img), C, kgroups, b_ntotal, b_noff, ldc);
   count_launch(1);
   return check_cuda(cudaGetLastError(), "rnn128_wgrad_kernel launch");
@@ -1105,13 +1111,13 @@ extern "C" int ddls_gru128_forward_v2(const float* x, const void* image, float* 
   if (smem > 227 * 1024) { set_last_error("ddls_gru128_forward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
   if (nb == 16) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_fwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+    launch_k(gru_fwd_v2_kernel<16>, dim3((B + 15) / 16), dim3(RCfg<16>::ALL), smem, st, p);
   } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_fwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
+    launch_k(gru_fwd_v2_kernel<32>, dim3((B + 31) / 32), dim3(RCfg<32>::ALL), smem, st, p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_fwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_fwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+    launch_k(gru_fwd_v2_kernel<64>, dim3((B + 63) / 64), dim3(RCfg<64>::ALL), smem, st, p);
   } else { set_last_error("ddls_gru128_forward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "gru_fwd_v2_kernel launch");
@@ -1129,13 +1135,13 @@ extern "C" int ddls_gru128_backward_v2(const float* dout, const float* x, const 
   if (smem > 227 * 1024) { set_last_error("ddls_gru128_backward_v2: T=%d too long for a %d-row tile", T, nb); return 1; }
   if (nb == 16) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_bwd_v2_kernel<16><<<(B + 15) / 16, RCfg<16>::ALL, smem, st>>>(p);
+    launch_k(gru_bwd_v2_kernel<16>, dim3((B + 15) / 16), dim3(RCfg<16>::ALL), smem, st, p);
   } else if (nb == 32) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_bwd_v2_kernel<32><<<(B + 31) / 32, RCfg<32>::ALL, smem, st>>>(p);
+    launch_k(gru_bwd_v2_kernel<32>, dim3((B + 31) / 32), dim3(RCfg<32>::ALL), smem, st, p);
   } else if (nb == 64) {
     DDLS_CUDA_OK(cudaFuncSetAttribute(gru_bwd_v2_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    gru_bwd_v2_kernel<64><<<(B + 63) / 64, RCfg<64>::ALL, smem, st>>>(p);
+    launch_k(gru_bwd_v2_kernel<64>, dim3((B + 63) / 64), dim3(RCfg<64>::ALL), smem, st, p);
   } else { set_last_error("ddls_gru128_backward_v2: tile must be 16, 32 or 64"); return 1; }
   count_launch(1);
   return check_cuda(cudaGetLastError(), "gru_bwd_v2_kernel launch");

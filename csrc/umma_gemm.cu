@@ -31,7 +31,17 @@ struct GemmParams {
   int k_per_split;
   uint32_t flags;     // DDLS_GEMM_* bits
   float* workspace;   // split-K partials [splits][M][N] fp32 (DDLS_GEMM_SPLITK_WS)
+  uint32_t epi;       // epilogue flags applied by the in-kernel split-K reduction (SPLITK_FUSED)
 };
+
+// In-kernel split-K reduction (v2 kernel): when every CTA of the launch is resident at once (<= one CTA per SM), the CTAs
+// of an output tile write their partial tiles, meet at a counter and each reduces 1/splits of the tile's rows with the
+// fused epilogue - no second kernel (the MNIST Dense(225) forward GEMM: 8.1 + 7.4 us as two launches).  The counters are
+// self-resetting: {arrivals, departures} per output tile; the last CTA to leave zeroes both.  Like the split-K workspace
+// they serialise split-K GEMMs of one device (launch them on one stream).
+constexpr uint32_t SPLITK_FUSED = 1u << 20;
+constexpr int SPLITK_MAX_TILES = 64;
+static __device__ unsigned g_splitk_sync[2 * SPLITK_MAX_TILES];
 
 // 8 consecutive elements starting at `src` (bf16 or fp32 in memory) -> one 16-byte bf16 vector.
 // `n_valid` (1..8) elements are in range, the rest are zero-filled; `vec` says 16-byte vector loads are legal.
@@ -220,6 +230,7 @@ __global__ void __launch_bounds__(GEMM_THREADS) umma_gemm_kernel(GemmParams p) {
 __global__ void __launch_bounds__(256) splitk_finish_kernel(const float* __restrict__ ws, void* __restrict__ C,
                                                             const float* __restrict__ bias, int M, int N, int ldc,
                                                             int splits, uint32_t flags) {
+  pdl_wait();
   const size_t total = (size_t)M * N;
   const bool relu = flags & DDLS_GEMM_RELU, has_bias = flags & DDLS_GEMM_BIAS, out_bf16 = flags & DDLS_GEMM_OUT_BF16;
   const bool accum = flags & DDLS_GEMM_ACCUMULATE;
@@ -293,6 +304,51 @@ __global__ void __launch_bounds__(V2_THREADS, 1) umma_gemm_v2_kernel(GemmParams 
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tmem_d, TM_COLS);
+  if (p.flags & SPLITK_FUSED) {
+    unsigned* arrive = g_splitk_sync + 2 * (blockIdx.x * gridDim.y + blockIdx.y);
+    unsigned* depart = arrive + 1;
+    __threadfence();                                   // my partial tile is visible device-wide
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      atomicAdd(arrive, 1u);
+      while (*reinterpret_cast<volatile unsigned*>(arrive) < gridDim.z) {}
+      __threadfence();
+    }
+    __syncthreads();
+    const bool relu2 = p.epi & DDLS_GEMM_RELU, bias2 = p.epi & DDLS_GEMM_BIAS, bf2 = p.epi & DDLS_GEMM_OUT_BF16;
+    const bool acc2 = p.epi & DDLS_GEMM_ACCUMULATE;
+    const int rows_per = (GEMM_BM + gridDim.z - 1) / gridDim.z;
+    const int r0 = blockIdx.z * rows_per, r1 = min(GEMM_BM, r0 + rows_per);
+    const int splits = gridDim.z;
+    for (int idx = threadIdx.x; idx < (r1 - r0) * BN; idx += blockDim.x) {
+      const int row = m0 + r0 + idx / BN, col = n0 + idx % BN;
+      if (row < p.M && col < p.N) {
+        float acc = 0.f;
+#pragma unroll 6
+        for (int sidx = 0; sidx < splits; ++sidx) acc += __ldcg(p.workspace + ((size_t)sidx * p.M + row) * p.N + col);
+        if (bias2) acc += p.bias[col];
+        if (relu2) acc = fmaxf(acc, 0.f);
+        const size_t o = (size_t)row * p.ldc + col;
+        if (bf2) reinterpret_cast<__nv_bfloat16*>(p.C)[o] = __float2bfloat16(acc);
+        else if (acc2) reinterpret_cast<float*>(p.C)[o] += acc;
+        else reinterpret_cast<float*>(p.C)[o] = acc;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (atomicAdd(depart, 1u) == gridDim.z - 1) { *arrive = 0; *depart = 0; __threadfence(); }
+    }
+  }
+}
+
+static int sm_count() {
+  static int n = 0;
+  if (n == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+  }
+  return n;
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -301,9 +357,13 @@ static int launch_gemm_v2(const GemmParams& p, int splits, cudaStream_t st) {
   const int smem = V2_STAGES * (GEMM_BM * GEMM_KC * 2 + BN * GEMM_KC * 2);
   DDLS_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   dim3 grid((p.M + GEMM_BM - 1) / GEMM_BM, (p.N + BN - 1) / BN, splits);
-  kern<<<grid, V2_THREADS, smem, st>>>(p);
+  GemmParams q = p;
+  if (splits > 1 && (int)(grid.x * grid.y) <= SPLITK_MAX_TILES && (int)(grid.x * grid.y * grid.z) <= sm_count())
+    q.flags |= SPLITK_FUSED;                  // every CTA resident at once: reduce in the kernel, no finish launch
+  DDLS_CUDA_OK(launch_k(kern, grid, dim3(V2_THREADS), smem, st, q));
   count_launch(1);
-  return check_cuda(cudaGetLastError(), "umma_gemm_v2 launch");
+  int rc = check_cuda(cudaGetLastError(), "umma_gemm_v2 launch");
+  return rc ? rc : ((q.flags & SPLITK_FUSED) ? -1 : 0);     // -1: done, including the split-K reduction
 }
 
 template <bool A_MN, bool B_MN>
@@ -352,7 +412,8 @@ extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float
   GemmParams p;
   p.A = A; p.B = B; p.C = C; p.bias = bias;
   p.M = M; p.N = N; p.K = K; p.lda = lda; p.ldb = ldb; p.ldc = ldc; p.workspace = static_cast<float*>(workspace);
-  p.flags = flags & ~(DDLS_GEMM_ATOMIC_ADD | DDLS_GEMM_SPLITK_WS);
+  p.flags = flags & ~(DDLS_GEMM_ATOMIC_ADD | DDLS_GEMM_SPLITK_WS | SPLITK_FUSED);
+  p.epi = 0;
   int splits = split_k < 1 ? 1 : split_k;
   int kps = (K + splits - 1) / splits;
   kps = (kps + GEMM_KC - 1) / GEMM_KC * GEMM_KC;
@@ -369,6 +430,7 @@ extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float
       return 1;
     }
     p.flags = (p.flags & ~epi) | DDLS_GEMM_SPLITK_WS;
+    p.epi = epi;
   } else if (flags & DDLS_GEMM_ACCUMULATE) {
     p.flags |= DDLS_GEMM_ATOMIC_ADD;   // single split accumulating into C
   }
@@ -384,11 +446,12 @@ extern "C" int ddls_gemm_bf16(const void* A, const void* B, void* C, const float
     if (a_mn_major) rc = b_mn_major ? dispatch_bn<true, true>(p, splits, st) : dispatch_bn<true, false>(p, splits, st);
     else rc = b_mn_major ? dispatch_bn<false, true>(p, splits, st) : dispatch_bn<false, false>(p, splits, st);
   }
+  if (rc == -1) return 0;                     // the kernel reduced its own split-K partials
   if (rc || splits == 1) return rc;
   const size_t total = (size_t)M * N;
   int blocks = (int)((total + 255) / 256);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  splitk_finish_kernel<<<blocks, 256, 0, st>>>(p.workspace, C, bias, M, N, ldc, splits, epi);
+  DDLS_CUDA_OK(launch_k(splitk_finish_kernel, dim3(blocks), dim3(256), 0, st, p.workspace, C, bias, M, N, ldc, splits, epi));
   count_launch(1);
   return check_cuda(cudaGetLastError(), "splitk_finish_kernel launch");
 }

@@ -19,6 +19,9 @@ const char* ddls_last_error(void);
 int ddls_version(void);
 /* Number of kernels this library has launched in this process (bench.py reports it). */
 unsigned long long ddls_launch_count(void);
+/* Programmatic dependent launch between the kernels of a training step (on by default, DDLS_PDL=0 at start-up or
+ * ddls_set_pdl(0) switch it off): the next kernel's prologue overlaps the tail of its predecessor. */
+int ddls_set_pdl(int on);
 
 /* ---- generic tcgen05 GEMM ------------------------------------------------------------------ */
 #define DDLS_GEMM_RELU 1u
