@@ -54,6 +54,7 @@ def parse():
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-dataset', action='store_true', help='feed step(x, y) from the device pool instead of the in-graph gather')
     ap.add_argument('--no-secondary', action='store_true', help='skip the NYISO LSTM run and the allreduce latency table')
+    ap.add_argument('--nccl-compare', action='store_true', help='also time NCCL in the allreduce latency table')
     ap.add_argument('--comm', default=None, help='peer (default on GPUs) | nccl')
     return ap.parse_args()
 
@@ -147,6 +148,7 @@ def measure(args, model_name, ddls, K, W, with_e2e=True, with_clocks=True):
     for i in range(max(W, 5)):                      # includes the three eager warm-ups and the graph capture
         train_step(i)
     sync_all()
+    _log(f'{model_name}: warm')
     c0 = _native.launch_count()
     if use_dataset:
         engine._gather()
@@ -164,6 +166,7 @@ def measure(args, model_name, ddls, K, W, with_e2e=True, with_clocks=True):
     ev1.record()
     sync_all()
     ms = max_over_ranks(ev0.elapsed_time(ev1))
+    _log(f'{model_name}: kernel-only timed')
     last_loss = float(engine.step(pool_x[0], pool_y[0]).item())
 
     # ---- end to end: pinned host -> H2D every step, device -> host loss read every step -------------------
@@ -229,10 +232,11 @@ def measure(args, model_name, ddls, K, W, with_e2e=True, with_clocks=True):
     }
 
 
-def allreduce_latency(ddls, sizes=(4 << 10, 256 << 10, 4 << 20)):
-    """Device time per allreduce call (fp32 SUM, in place), this library's selected algorithm vs NCCL, both timed inside a
-    CUDA graph of 16 calls (no host launch overhead on either side), max over ranks.  The third leg of BASELINE.json's
-    metric ("allreduce us")."""
+def allreduce_latency(ddls, sizes=(4 << 10, 256 << 10, 4 << 20), with_nccl=False):
+    """Device time per allreduce call (fp32 SUM, in place) of this library's selected algorithm, timed inside a CUDA graph
+    of 16 calls (no host launch overhead), max over ranks.  The third leg of BASELINE.json's metric ("allreduce us").
+    ``with_nccl`` (``--nccl-compare``) adds NCCL timed the same way; by default the bench never creates an NCCL
+    communicator (the full comparison, 4 KB - 256 MB, is ``bench/allreduce_sweep.py`` -> ``profiles/sweep_n*.json``)."""
     import torch
     import torch.distributed as dist
     rank, size, dev = ddls.rank(), ddls.size(), ddls.device()
@@ -263,10 +267,11 @@ def allreduce_latency(ddls, sizes=(4 << 10, 256 << 10, 4 << 20)):
 
     out = {}
     nccl_group = None
-    try:
-        nccl_group = dist.group.WORLD if dist.get_backend() == 'nccl' else dist.new_group(backend='nccl')
-    except Exception:  # noqa: BLE001
-        nccl_group = None
+    if with_nccl:
+        try:
+            nccl_group = dist.group.WORLD if dist.get_backend() == 'nccl' else dist.new_group(backend='nccl')
+        except Exception:  # noqa: BLE001
+            nccl_group = None
     for nbytes in sizes:
         n = nbytes // 4
         t = comm.alloc(n)
@@ -282,10 +287,18 @@ def allreduce_latency(ddls, sizes=(4 << 10, 256 << 10, 4 << 20)):
     return out
 
 
+def _log(msg):
+    if os.environ.get('RANK', '0') == '0':
+        print(f'[bench] {msg}', file=sys.stderr, flush=True)
+
+
 def main():
     args = parse()
     if args.impl == 'reference':
         return reference_arm(args)
+    import faulthandler
+    # a hung collective must not hang the caller for ever: dump every thread's stack and exit after DDLS_BENCH_WATCHDOG_S
+    faulthandler.dump_traceback_later(int(os.environ.get('DDLS_BENCH_WATCHDOG_S', '900')), exit=True)
 
     import torch
     import distributeddeeplearningspark_b200 as ddls
@@ -312,10 +325,12 @@ def main():
         return standin.run(args, ddls, md, args.batch_per_rank or md['batch'], K, W)
 
     out = measure(args, args.model, ddls, K, W)
+    _log(f'{args.model}: {out["value"]:.0f} {out["unit"]}, {out["ms_per_step"] * 1e3:.1f} us/step')
     # BASELINE.json's metric has three legs: MNIST images/s (the primary line), NYISO LSTM samples/s and allreduce latency.
     # The default run measures all three so that the driver's record carries them at every N.
     if args.model == 'mnist_cnn' and not args.no_secondary:
         sec = measure(args, 'nyiso_lstm', ddls, K, W, with_clocks=False)
+        _log(f'nyiso_lstm: {sec["value"]:.0f} samples/s')
         pub = PUBLISHED['nyiso_lstm']
         out['secondary'] = {k: sec[k] for k in ('metric', 'value', 'unit', 'ms_per_step', 'steps', 'warmup', 'e2e',
                                                 'gpu_launches', 'gpu_launches_per_step', 'final_loss')}
@@ -323,7 +338,7 @@ def main():
         out['secondary']['published'] = {'value': pub, 'unit': 'samples/s', 'what': '4 CPU workers, ddl_nyiso_hdi.ipynb:817-818'}
         out['secondary']['config'] = sec['config']
         if ddls.size() > 1:
-            out['allreduce_us'] = allreduce_latency(ddls)
+            out['allreduce_us'] = allreduce_latency(ddls, with_nccl=args.nccl_compare)
     if rank == 0:
         print(json.dumps(out))
     ddls.shutdown()

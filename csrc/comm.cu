@@ -463,6 +463,74 @@ __global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_kernel(CommCtx c,
   advance_epoch(c, rank, epoch + 1);
 }
 
+// NVLS with bf16 on the wire (Compression.bf16 on buckets above the one-shot range): the fp32 input is cast into a bf16
+// staging buffer of the heap, the switch reduces the bf16 replicas with fp32 accumulation
+// (`multimem.ld_reduce.add.acc::f32.v4.bf16x2`, 8 elements per 16 bytes), the scaled sum goes back to every replica as
+// bf16 by multicast store, and each rank widens it to fp32 locally: half the NVLink bytes of the fp32 form in both
+// directions.  Staging: one parity half of the push-collective region, n bf16 elements; n % 8 == 0.
+DDLS_DEVINL uint4 mc_ld_reduce_bf16x8(const void* mc_ptr) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_ptr));
+  return v;
+}
+DDLS_DEVINL void mc_st_b128(void* mc_ptr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_ptr), "f"(__uint_as_float(v.x)),
+               "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w)) : "memory");
+}
+DDLS_DEVINL uint32_t scale_bf16x2(uint32_t w, float s) {
+  return pack_bf16x2(__uint_as_float(w << 16) * s, __uint_as_float(w & 0xFFFF0000u) * s);
+}
+
+__global__ void __launch_bounds__(COMM_THREADS) allreduce_nvls_bf16_kernel(CommCtx c, ArParams p) {
+  const int rank = c.rank_base + blockIdx.y;
+  const uint32_t e0 = read_epoch(c, rank);
+  const uint64_t nv8 = p.n / 8;                            // 16-byte bf16 vectors
+  const uint64_t per_blk = (nv8 + gridDim.x - 1) / gridDim.x;
+  const uint64_t blo = blockIdx.x * per_blk, bhi = min(nv8, blo + per_blk);
+  const uint64_t per_rank = (bhi > blo) ? ((bhi - blo) + c.world - 1) / c.world : 0;
+  const uint64_t lo = blo + rank * per_rank, hi = min(bhi, lo + per_rank);
+  const uint64_t par_off = ((e0 >> 1) & 1u) * p.parity_bytes;
+  const float4* in = reinterpret_cast<const float4*>(c.base[rank] + p.in_off);
+  uint4* st_local = reinterpret_cast<uint4*>(c.base[rank] + p.stage_off + par_off);
+  uint8_t* st_mc = c.mc_base + p.stage_off + par_off;
+  // cast my whole block range (every rank's slice of it: the owners reduce MY replica too)
+  for (uint64_t i = blo + threadIdx.x; i < bhi; i += blockDim.x) {
+    const float4 a = in[2 * i], b = in[2 * i + 1];
+    st_local[i] = make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+  }
+  peer_barrier(c, rank, blockIdx.x, e0 + 1, FENCE_REL);
+  constexpr int U = 4;
+  for (uint64_t i0 = lo + threadIdx.x; i0 < hi; i0 += (uint64_t)U * blockDim.x) {
+    uint4 v[U];
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i < hi) v[k] = mc_ld_reduce_bf16x8(st_mc + 16 * i);
+    }
+#pragma unroll
+    for (int k = 0; k < U; ++k) {
+      const uint64_t i = i0 + (uint64_t)k * blockDim.x;
+      if (i < hi) {
+        if (p.scale != 1.0f)
+          v[k] = make_uint4(scale_bf16x2(v[k].x, p.scale), scale_bf16x2(v[k].y, p.scale), scale_bf16x2(v[k].z, p.scale),
+                            scale_bf16x2(v[k].w, p.scale));
+        mc_st_b128(st_mc + 16 * i, v[k]);
+      }
+    }
+  }
+  peer_barrier(c, rank, blockIdx.x, e0 + 2, FENCE_REL);
+  float4* out = reinterpret_cast<float4*>(c.base[rank] + p.out_off);
+  for (uint64_t i = blo + threadIdx.x; i < bhi; i += blockDim.x) {
+    const uint4 w = __ldcg(st_local + i);                  // written through NVLink: read from L2
+    out[2 * i] = make_float4(__uint_as_float(w.x << 16), __uint_as_float(w.x & 0xFFFF0000u), __uint_as_float(w.y << 16),
+                             __uint_as_float(w.y & 0xFFFF0000u));
+    out[2 * i + 1] = make_float4(__uint_as_float(w.z << 16), __uint_as_float(w.z & 0xFFFF0000u), __uint_as_float(w.w << 16),
+                                 __uint_as_float(w.w & 0xFFFF0000u));
+  }
+  advance_epoch(c, rank, e0 + 2);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Sharded data-parallel step: reduce-scatter -> Keras optimizer on my 1/N slice -> parameter all-gather, ONE kernel per
 // gradient bucket (the training loop of /root/reference/ddl_mnist_aztk.py:216-219 does commit + pull + optimizer as three
@@ -872,7 +940,16 @@ extern "C" int ddls_comm_allreduce(const DdlsCommDesc* d, int algo, uint64_t in_
       return wire_bf16 ? launch(d, allreduce_twoshot_kernel<__nv_bfloat16>, nb, COMM_THREADS, st, c, p)
                        : launch(d, allreduce_twoshot_kernel<float>, nb, COMM_THREADS, st, c, p);
     case DDLS_AR_NVLS:
-      if (c.mc_base == nullptr) { set_last_error("ddls_comm_allreduce: NVLS needs a multicast mapping"); return 1; }
+      if (c.mc_base == nullptr || d->emulate) { set_last_error("ddls_comm_allreduce: NVLS needs a multicast mapping"); return 1; }
+      if (wire_bf16) {
+        if (n % 8 != 0) { set_last_error("ddls_comm_allreduce: NVLS with a bf16 wire needs n %% 8 == 0 (got %llu)", (unsigned long long)n); return 1; }
+        if (n * 2 > parity_bytes) {
+          set_last_error("ddls_comm_allreduce: NVLS with a bf16 wire needs %llu bytes of staging per parity half (got %llu)",
+                         (unsigned long long)(n * 2), (unsigned long long)parity_bytes);
+          return 1;
+        }
+        return launch(d, allreduce_nvls_bf16_kernel, nb, COMM_THREADS, st, c, p);
+      }
       return launch(d, allreduce_nvls_kernel, nb, COMM_THREADS, st, c, p);
   }
   set_last_error("ddls_comm_allreduce: unknown algorithm %d", algo);

@@ -13,6 +13,8 @@
 // (MN-major operands), and as the validation vehicle for the descriptor encodings every other
 // tcgen05 kernel in this library relies on.  The reference has no GEMM of its own (Keras→TF Eigen on
 // CPU).
+#include <cstdio>
+
 #include "common.cuh"
 #include "gemm_pipe.cuh"
 #include "../include/ddls_b200.h"
@@ -311,7 +313,19 @@ __global__ void __launch_bounds__(V2_THREADS, 1) umma_gemm_v2_kernel(GemmParams 
     __syncthreads();
     if (threadIdx.x == 0) {
       atomicAdd(arrive, 1u);
-      while (*reinterpret_cast<volatile unsigned*>(arrive) < gridDim.z) {}
+      unsigned long long t0 = 0, now = 0;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+      unsigned spins = 0;
+      while (*reinterpret_cast<volatile unsigned*>(arrive) < gridDim.z) {
+        if ((++spins & 1023u) == 0) {
+          asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+          if (now - t0 > 2000000000ull) {      // 2 s: the CTAs of this launch are not all resident (never expected)
+            printf("ddls gemm: split-K rendezvous timed out (tile %d,%d split %d saw %u of %u)\n", blockIdx.x, blockIdx.y,
+                   blockIdx.z, *reinterpret_cast<volatile unsigned*>(arrive), gridDim.z);
+            __trap();
+          }
+        }
+      }
       __threadfence();
     }
     __syncthreads();

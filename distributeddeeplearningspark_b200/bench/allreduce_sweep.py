@@ -20,20 +20,29 @@ import torch.distributed as dist
 LINK_GBS = 770.0
 
 
+_COMM = None          # this library's communicator: host barriers and max-over-ranks go through it, not through NCCL
+_NCCL = None          # NCCL group for the comparison arm only
+
+
+def _max_over_ranks(v):
+    return max(_COMM.allgather_object(float(v)))
+
+
+def _barrier(dev):
+    torch.cuda.synchronize(dev); _COMM.barrier(); torch.cuda.synchronize(dev)
+
+
 def _time(fn, iters, dev):
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     for _ in range(3):
         fn()
-    torch.cuda.synchronize(dev)
-    dist.barrier(device_ids=[dev.index])
+    _barrier(dev)
     a.record()
     for _ in range(iters):
         fn()
     b.record()
     torch.cuda.synchronize(dev)
-    t = torch.tensor([a.elapsed_time(b) / iters * 1e3], device=dev)   # us
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    return _max_over_ranks(a.elapsed_time(b) / iters * 1e3)   # us
 
 
 def _time_graph(fn, dev, calls=16, replays=20):
@@ -43,24 +52,20 @@ def _time_graph(fn, dev, calls=16, replays=20):
     with torch.cuda.stream(side):
         fn()
     torch.cuda.current_stream(dev).wait_stream(side)
-    torch.cuda.synchronize(dev)
-    dist.barrier(device_ids=[dev.index])
+    _barrier(dev)
     g = torch.cuda.CUDAGraph()
     with torch.cuda.graph(g):
         for _ in range(calls):
             fn()
     g.replay()
-    torch.cuda.synchronize(dev)
-    dist.barrier(device_ids=[dev.index])
+    _barrier(dev)
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(replays):
         g.replay()
     b.record()
     torch.cuda.synchronize(dev)
-    t = torch.tensor([a.elapsed_time(b) / (replays * calls) * 1e3], device=dev)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
+    return _max_over_ranks(a.elapsed_time(b) / (replays * calls) * 1e3)
 
 
 def main():
@@ -71,11 +76,16 @@ def main():
     args = ap.parse_args()
     import distributeddeeplearningspark_b200 as ddls
     from distributeddeeplearningspark_b200.parallel.peer import AR_NVLS, AR_ONESHOT, AR_ONESHOT_LL, AR_TWOSHOT, PeerMemoryComm
-    os.environ.setdefault('DDLS_HEAP_MB', str(768 + 44 * args.max_mb))   # buffer + one-shot staging (2 x N x message) at N = 8
+    os.environ.setdefault('DDLS_HEAP_MB', str(768 + 44 * min(args.max_mb, 64) + 2 * args.max_mb))   # buffer + one-shot staging (2 x N x message, <= 16 MB messages) at N = 8
     ddls.init()
     comm = ddls.runtime.communicator()
     assert isinstance(comm, PeerMemoryComm), f'peer-memory communicator unavailable: {type(comm).__name__}'
+    global _COMM, _NCCL
+    _COMM = comm
+    _NCCL = dist.group.WORLD if dist.get_backend() == 'nccl' else dist.new_group(backend='nccl')
     r, n, dev = ddls.rank(), ddls.size(), ddls.device()
+    from distributeddeeplearningspark_b200.utils import ClockSampler
+    sampler = ClockSampler(gpu_index=dev.index or 0, period_ms=100).start() if r == 0 else None
     sizes = []
     s = 4 << 10
     while s <= args.max_mb << 20:
@@ -87,8 +97,9 @@ def main():
         numel = nbytes // 4
         t, tn = buf[:numel], nccl_buf[:numel]
         iters = 200 if nbytes <= (1 << 20) else (50 if nbytes <= (32 << 20) else 10)
-        row = {'bytes': nbytes, 'nccl_us': _time(lambda: dist.all_reduce(tn), iters, dev)}
-        algos = [('oneshot', AR_ONESHOT), ('twoshot', AR_TWOSHOT)] + ([('nvls', AR_NVLS)] if comm.mc_base else [])
+        row = {'bytes': nbytes, 'nccl_us': _time(lambda: dist.all_reduce(tn, group=_NCCL), iters, dev)}
+        algos = [('oneshot', AR_ONESHOT)] + ([('twoshot', AR_TWOSHOT)] if nbytes <= (64 << 20) else []) + \
+            ([('nvls', AR_NVLS)] if comm.mc_base else [])
         if nbytes <= comm._ll_elems * 4:
             algos.insert(0, ('ll', AR_ONESHOT_LL))
         for name, a in algos:
@@ -103,7 +114,7 @@ def main():
             row[name + '_roofline_frac'] = (link_bytes / (LINK_GBS * 1e3)) / us      # t_link / t_measured
         if args.graph and nbytes <= (4 << 20):
             try:
-                row['nccl_graph_us'] = _time_graph(lambda: dist.all_reduce(tn), dev)
+                row['nccl_graph_us'] = _time_graph(lambda: dist.all_reduce(tn, group=_NCCL), dev)
             except Exception as e:  # noqa: BLE001
                 row['nccl_graph_us'] = None
         best = min((row[k], k) for k in row if k.endswith('_us') and not k.startswith('nccl') and 'graph' not in k)
@@ -112,10 +123,13 @@ def main():
         rows.append(row)
         if r == 0:
             print(json.dumps(row), flush=True)
+    clocks = sampler.stop() if sampler is not None else None
     if r == 0 and args.out:
         os.makedirs(os.path.dirname(args.out) or '.', exist_ok=True)
         with open(args.out, 'w') as f:
-            json.dump({'n_gpus': n, 'multicast': bool(comm.mc_base), 'link_gbs': LINK_GBS, 'rows': rows}, f, indent=1)
+            json.dump({'n_gpus': n, 'multicast': bool(comm.mc_base), 'link_gbs': LINK_GBS, 'clocks': clocks,
+                       'timing': 'CUDA events on the launching stream, warm, max over ranks; *_graph_us: 16 calls per captured '
+                                 'graph (no host launch overhead on either side)', 'rows': rows}, f, indent=1)
     ddls.shutdown()
 
 

@@ -88,41 +88,59 @@ class LocalComm(Communicator):
 
 
 class TorchDistComm(Communicator):
-    """gloo (CPU plumbing tests) or NCCL (the baseline a product path must beat)."""
+    """``torch.distributed`` collectives: gloo (CPU plumbing tests; CUDA tensors bounce through the host) or NCCL (the
+    baseline a product path must beat, ``DDLS_COMM=nccl``)."""
 
     name = 'torch.distributed'
+
+    def __init__(self, rank, size, device, group=None):
+        super().__init__(rank, size, device)
+        self.group = group
+        self._host_bounce = device.type == 'cuda' and dist.get_backend(group) != 'nccl'
+
+    def _host(self, t):
+        return t.detach().cpu() if self._host_bounce else t
 
     def allreduce_(self, t, op=Average, prescale=1.0):
         if prescale != 1.0:
             t.mul_(prescale)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        h = self._host(t)
+        dist.all_reduce(h, op=dist.ReduceOp.SUM, group=self.group)
+        if h is not t:
+            t.copy_(h)
         if op is Average:
             t.div_(self.size)
         return t
 
     def broadcast_(self, t, root=0):
-        dist.broadcast(t, src=root)
+        h = self._host(t)
+        dist.broadcast(h, src=root, group=self.group)
+        if h is not t:
+            t.copy_(h)
         return t
 
     def allgather(self, t):
-        out = [torch.empty_like(t) for _ in range(self.size)]
-        dist.all_gather(out, t.contiguous())
-        return torch.stack(out)
+        h = self._host(t.contiguous())
+        out = [torch.empty_like(h) for _ in range(self.size)]
+        dist.all_gather(out, h, group=self.group)
+        return torch.stack(out).to(t.device)
 
     def barrier(self):
         if self.device.type == 'cuda':
-            dist.barrier(device_ids=[self.device.index])
+            torch.cuda.synchronize(self.device)
+        if dist.get_backend(self.group) == 'nccl':
+            dist.barrier(group=self.group, device_ids=[self.device.index])
         else:
-            dist.barrier()
+            dist.barrier(group=self.group)
 
     def allgather_object(self, obj):
         out = [None] * self.size
-        dist.all_gather_object(out, obj)
+        dist.all_gather_object(out, obj, group=self.group)
         return out
 
     def broadcast_object(self, obj, root=0):
         box = [obj]
-        dist.broadcast_object_list(box, src=root)
+        dist.broadcast_object_list(box, src=root, group=self.group)
         return box[0]
 
 
@@ -137,5 +155,11 @@ def make_communicator(state, prefer: str = 'auto') -> Communicator:
             if prefer == 'peer':
                 raise
             from ..utils.logging import get_logger
-            get_logger().warning('peer-memory communicator unavailable (%s); using NCCL', e)
-    return TorchDistComm(state.rank, state.size, state.device)
+            get_logger().warning('peer-memory communicator unavailable (%s); using torch.distributed', e)
+    group = None
+    if state.device.type == 'cuda' and dist.get_backend() != 'nccl':
+        try:                                    # a GPU fallback / baseline communicator wants NCCL, not host bounces
+            group = dist.new_group(backend='nccl')
+        except Exception:  # noqa: BLE001
+            group = None
+    return TorchDistComm(state.rank, state.size, state.device, group=group)

@@ -178,7 +178,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
         self._heap_u8 = _tensor_from_ptr(self._bases[rank], heap_bytes, torch.uint8, device, owner=self)
         self._heap_u8[:CONTROL_BYTES].zero_()
         torch.cuda.synchronize(device)
-        dist.barrier(device_ids=[self.dev_index])
+        self._pg_barrier()
         # 4. multicast
         self.mc_base = 0
         self._mc_handle = 0
@@ -206,7 +206,14 @@ class PeerMemoryComm(Communicator, _HeapBase):
         self._ll_mc_push = env_int('DDLS_LL_MC_PUSH', 0) != 0
         self._heap_u8[self._ll_off:self._ll_off + self._ll_bytes].zero_()
         torch.cuda.synchronize(device)
-        dist.barrier(device_ids=[self.dev_index])
+        self._pg_barrier()
+
+    def _pg_barrier(self) -> None:
+        """Host-side barrier of the bootstrap process group (gloo by default: no NCCL on the product path)."""
+        if dist.get_backend() == 'nccl':
+            dist.barrier(device_ids=[self.dev_index])
+        else:
+            dist.barrier()
 
     # ------------------------------------------------------------------ fd exchange
     def _exchange_fds(self, my_fd: int, tag: str, only_from: Optional[int] = None) -> Dict[int, int]:
@@ -224,7 +231,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
             pass
         srv.bind(path(self.rank))
         srv.listen(self.size)
-        dist.barrier(device_ids=[self.dev_index])
+        self._pg_barrier()
         received: Dict[int, int] = {}
         senders = [only_from] if only_from is not None else list(range(self.size))
         # send my fd to every peer that expects it
@@ -243,7 +250,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
             msg, fds, _, _ = socket.recv_fds(conn, 4, 1)
             received[int.from_bytes(msg, 'little')] = fds[0]
             conn.close()
-        dist.barrier(device_ids=[self.dev_index])
+        self._pg_barrier()
         srv.close()
         try:
             os.unlink(path(self.rank))
@@ -263,10 +270,10 @@ class PeerMemoryComm(Communicator, _HeapBase):
             N.call('ddls_mc_import', got[0], ctypes.byref(mch))
             os.close(got[0])
         N.call('ddls_mc_add_device', mch.value, self.dev_index)
-        dist.barrier(device_ids=[self.dev_index])       # every device joined before anyone binds
+        self._pg_barrier()       # every device joined before anyone binds
         p = P(0)
         N.call('ddls_mc_bind_and_map', mch.value, self._handles[self.rank], heap_bytes, self.dev_index, ctypes.byref(p))
-        dist.barrier(device_ids=[self.dev_index])
+        self._pg_barrier()
         self._mc_handle, self.mc_base = mch.value, p.value
 
     # ------------------------------------------------------------------ memory
@@ -300,7 +307,12 @@ class PeerMemoryComm(Communicator, _HeapBase):
         off = self.offset_of(t) if (n % 4 == 0 and t.is_contiguous()) else None
         if off is not None and off % 16 == 0:
             a = algo if algo is not None else self.select_algo(n * 4, True, bool(self.mc_base))
-            stage, sbytes = self._ensure_stage(n, self.size, a) if a != AR_NVLS else (0, 0)
+            if a == AR_NVLS and wire_bf16 and n % 8 != 0:
+                a = AR_TWOSHOT                            # the bf16 NVLS form moves 8-element vectors
+            if a == AR_NVLS:                              # fp32 NVLS is in place; the bf16 wire needs n bf16 of staging
+                stage, sbytes = self._ensure_stage((n + 2 * self.size - 1) // (2 * self.size), self.size, a) if wire_bf16 else (0, 0)
+            else:
+                stage, sbytes = self._ensure_stage(n, self.size, a)
             blocks = self._ar_blocks if a in (AR_NVLS, AR_TWOSHOT) else 0
             N.call('ddls_comm_allreduce', ctypes.byref(self.desc), a, off, off, stage, sbytes, n, scale,
                    self._wire_flags(wire_bf16), blocks, self._stream())
@@ -401,19 +413,22 @@ class PeerMemoryComm(Communicator, _HeapBase):
         return t
 
     def allgather(self, t: torch.Tensor) -> torch.Tensor:
+        """[size, *t.shape]: every rank's tensor, through the scratch region of the heap (chunked when it does not fit)."""
         t = t.contiguous()
         nbytes = t.numel() * t.element_size()
-        chunk = (nbytes + 15) // 16 * 16
-        if chunk * (self.size + 1) > self._scratch_bytes:
-            out = [torch.empty_like(t) for _ in range(self.size)]
-            dist.all_gather(out, t)
-            return torch.stack(out)
+        src = t.view(-1).view(torch.uint8)
+        out = torch.empty((self.size, nbytes), dtype=torch.uint8, device=t.device)
+        cap = (self._scratch_bytes // (self.size + 1)) // 16 * 16
         scratch = self._heap_u8[self._scratch_off:self._scratch_off + self._scratch_bytes]
-        scratch[:nbytes].copy_(t.view(-1).view(torch.uint8))
-        out_off = self._scratch_off + chunk
-        N.call('ddls_comm_allgather', ctypes.byref(self.desc), self._scratch_off, out_off, chunk, 0, self._stream())
-        res = scratch[chunk:chunk + chunk * self.size].view(self.size, chunk)[:, :nbytes].clone()
-        return res.view(torch.uint8).reshape(self.size, nbytes).view(t.dtype).reshape((self.size,) + tuple(t.shape))
+        for lo in range(0, max(nbytes, 1), cap):
+            m = min(cap, nbytes - lo)
+            chunk = (m + 15) // 16 * 16
+            scratch[:m].copy_(src[lo:lo + m])
+            N.call('ddls_comm_allgather', ctypes.byref(self.desc), self._scratch_off, self._scratch_off + chunk, chunk, 0,
+                   self._stream())
+            # (the next chunk's kernel starts with a flag round: no peer pushes before every rank has copied this one out)
+            out[:, lo:lo + m].copy_(scratch[chunk:chunk + chunk * self.size].view(self.size, chunk)[:, :m])
+        return out.view(t.dtype).reshape((self.size,) + tuple(t.shape))
 
     def barrier(self) -> None:
         N.call('ddls_comm_barrier', ctypes.byref(self.desc), self._stream())

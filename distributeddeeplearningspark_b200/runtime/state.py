@@ -2,10 +2,13 @@
 
 Horovod-shaped surface required by BASELINE.json (the reference itself gets its
 worker count from ``num_executors * num_processes``,
-/root/reference/ddl_mnist_aztk.py:49-53).  ``torch.distributed`` (NCCL on GPU,
-gloo on CPU) is used for *plumbing only* — rendezvous, handle exchange, barriers,
-object gathers.  The gradient/parameter collectives on GPUs run through the
-hand-written peer-memory kernels in ``parallel.comm``.
+/root/reference/ddl_mnist_aztk.py:49-53).  ``torch.distributed`` with the **gloo**
+backend (a TCP store + CPU collectives) is used for *plumbing only* — rendezvous,
+handle exchange, host barriers, object gathers — on CPUs and GPUs alike, so the
+product path never initialises NCCL.  The gradient/parameter collectives on GPUs
+run through the hand-written peer-memory kernels in ``parallel.comm``; NCCL is
+only created when asked for by name (``DDLS_COMM=nccl``, the labelled baseline,
+and the comparison arms of the benchmarks).
 """
 from __future__ import annotations
 
@@ -81,7 +84,8 @@ def init(backend: Optional[str] = None, timeout_s: float = 300.0, comm: Optional
         _S.device = torch.device('cuda', idx)
     else:
         _S.device = torch.device('cpu')
-    _S.backend = backend or ('nccl' if use_cuda else 'gloo')
+    prefer = comm or env.get('DDLS_COMM', 'auto')
+    _S.backend = backend or env.get('DDLS_PG_BACKEND') or ('nccl' if (use_cuda and prefer == 'nccl') else 'gloo')
     if _S.size > 1:
         if dist.is_initialized():
             _S.owns_pg = False
@@ -97,7 +101,7 @@ def init(backend: Optional[str] = None, timeout_s: float = 300.0, comm: Optional
     _S.topology = _probe_topology(_S.device)
     _S.initialized = True
     from ..parallel.comm import make_communicator
-    _S.comm = make_communicator(_S, prefer=comm or env.get('DDLS_COMM', 'auto'))
+    _S.comm = make_communicator(_S, prefer=prefer)
     log = get_logger()
     if _S.rank == 0:
         t = _S.topology

@@ -227,14 +227,11 @@ def _multi_rank_checks():
             t.copy_(torch.randn(numel, device=dev))
             mine = t.clone()
             comm.allreduce_(t, ddls.Sum, algo=algo)
-            gathered = [torch.empty_like(mine) for _ in range(n)]
-            import torch.distributed as dist
-            dist.all_gather(gathered, mine)
-            ref = torch.stack(gathered).double().sum(0).float()
+            gathered = comm.allgather(mine)          # this library's own all-gather (chunked through the heap)
+            ref = gathered.double().sum(0).float()
             err = float((t - ref).abs().max())
             assert err < 1e-4 * max(1.0, float(ref.abs().max())), (numel, algo, err)
-            chk = [torch.empty_like(t) for _ in range(n)]
-            dist.all_gather(chk, t)
+            chk = comm.allgather(t)
             assert all(torch.equal(chk[0], c) for c in chk), ('replicas differ', numel, algo)
     # flag-in-data packets pushed through the multicast mapping (one store reaches every peer): many back-to-back calls
     # over both parities, checked against the per-peer push
@@ -251,6 +248,20 @@ def _multi_rank_checks():
             bad += int(not torch.equal(a, t))
         res['ll_mc_push_mismatches'] = bad
         comm._ll_mc_push = False
+    # bf16 on the wire through the switch (NVLS): contributions rounded to bf16, fp32 accumulation, bf16 result
+    if comm.mc_base:
+        for numel in (1048576, 3 * 1048576 + 8):
+            t = comm.alloc(numel)
+            vals = []
+            for rr in range(n):
+                torch.manual_seed(4000 + rr)
+                vals.append(torch.randn(numel, device=dev))
+            t.copy_(vals[r])
+            comm.allreduce_(t, ddls.Average, algo=AR_NVLS, wire_bf16=True)
+            ref = (torch.stack([v.bfloat16().float() for v in vals]).sum(0) / n)
+            err = float((t - ref).abs().max())
+            assert err < 2e-2 * max(1.0, float(ref.abs().max())), ('nvls bf16', numel, err)
+            assert torch.equal(t, t.bfloat16().float())       # the result really is a bf16 value
     # non-heap tensor path + average + odd size
     x = torch.full((1001,), float(r + 1), device=dev)
     ddls.allreduce_(x)
@@ -287,9 +298,7 @@ def _multi_rank_checks():
     for _ in range(8):
         eng.step(torch.rand(32, 25, 1, device=dev), torch.rand(32, 1, device=dev))
     w = opt.flat.flat_params.clone()
-    ws = [torch.empty_like(w) for _ in range(n)]
-    import torch.distributed as dist
-    dist.all_gather(ws, w)
+    ws = comm.allgather(w)
     res['weights_equal'] = all(torch.equal(ws[0], v) for v in ws)
     res['graph'] = eng._graph is not None
     res['fused'] = bool(dopt._fused)
@@ -332,7 +341,6 @@ def _sharded_step_checks(ddls, comm, dev, r, n):
     the owner's slice -> multicast parameter all-gather), the small one the flag-in-data kernel; compared with the unfused
     path (allreduce kernels + one optimizer kernel) on identical gradients."""
     import os
-    import torch.distributed as dist
     res = {}
     finals, slots = {}, {}
     for fused in ('1', '0'):
@@ -360,8 +368,7 @@ def _sharded_step_checks(ddls, comm, dev, r, n):
             sd = d2.state_dict()                        # collective: gathers the sharded slots
             finals[(fused, kind)] = o2.flat.flat_params.clone()
             slots[(fused, kind)] = {k_: v_.to(dev) for k_, v_ in sd['slots'].items()}
-            ws = [torch.empty_like(finals[(fused, kind)]) for _ in range(n)]
-            dist.all_gather(ws, finals[(fused, kind)])
+            ws = comm.allgather(finals[(fused, kind)])
             assert all(torch.equal(ws[0], w_) for w_ in ws), 'replicas differ after the sharded step'
     os.environ.pop('DDLS_FUSED_OPT')
     res['sharded_err'] = {k: float((finals[('1', k)] - finals[('0', k)]).abs().max()) for k in ('adam', 'adagrad')}
@@ -383,8 +390,7 @@ def _sharded_step_checks(ddls, comm, dev, r, n):
     for _ in range(12):
         losses.append(float(eng.step(x, y)))
     w = opt.flat.flat_params.clone()
-    ws = [torch.empty_like(w) for _ in range(n)]
-    dist.all_gather(ws, w)
+    ws = comm.allgather(w)
     res['cnn_weights_equal'] = all(torch.equal(ws[0], v) for v in ws)
     res['cnn_modes'] = [dopt._bucket_mode(b) for b in dopt.buckets]
     res['cnn_loss'] = (losses[0], losses[-1])
