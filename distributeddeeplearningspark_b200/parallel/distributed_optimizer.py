@@ -137,7 +137,8 @@ class DistributedOptimizer:
         """Can every bucket run as a fused kernel?  Sets ``_dp_ok`` (sharded kernel usable) and ``_ll_ok`` per bucket."""
         comm = self.comm
         self._dp_ok = hasattr(comm, 'dp_step_') and comm.can_shard_step(self.inner) and self._bf16 is None
-        self._dp_min_bytes = env_int('DDLS_DP_STEP_MIN_BYTES', 512 << 10)
+        # above this size the sharded kernel (in-switch reduce-scatter) beats the flag-in-data one (see ll_max_bytes)
+        self._dp_min_bytes = env_int('DDLS_DP_STEP_MIN_BYTES', 0) or (comm.ll_max_bytes(self.size) if hasattr(comm, 'll_max_bytes') else 512 << 10)
         for b in self.buckets:
             b.ll_ok = comm.can_fuse_optimizer(self.flat.flat_grads[b.lo:b.hi])
             if not (b.ll_ok or self._dp_ok):
@@ -147,7 +148,7 @@ class DistributedOptimizer:
     def _bucket_mode(self, b) -> str:
         """'ll' or 'dp' for bucket ``b`` (decided at launch time: bf16 shadows are registered after construction)."""
         shadowed = any(beg < b.hi and beg + rows * cols > b.lo for beg, rows, cols, _, _ in getattr(self.inner, '_shadows', ()))
-        if b.ll_ok and not shadowed and ((b.hi - b.lo) * 4 < self._dp_min_bytes or not self._dp_ok):
+        if b.ll_ok and not shadowed and ((b.hi - b.lo) * 4 <= self._dp_min_bytes or not self._dp_ok):
             return 'll'
         if not self._dp_ok:
             raise RuntimeError('bucket holds bf16 shadow weights but the sharded step kernel is unavailable '

@@ -127,16 +127,28 @@ class _HeapBase:
             self._stage_elems = want
         return self._stage_off, self._stage_bytes
 
+    def ll_max_bytes(self, world: int) -> int:
+        """Largest message the flag-in-data one-shot still wins at ``world`` ranks.  Every rank receives (world-1) packets
+        per element, the in-switch reduction one: measured crossovers (profiles/sweep_n{2,8}.json, graph-timed) are
+        above 256 KB at 2 GPUs and ~64 KB at 8, i.e. about 512 KB of inbound payload."""
+        return min(self._ll_elems * 4, env_int('DDLS_LL_INBOUND_BYTES', 512 << 10) // max(1, world - 1))
+
     def select_algo(self, nbytes: int, symmetric_out: bool, have_mc: bool) -> int:
+        """Measured selection (profiles/sweep_n{2,4,8}.json): flag-in-data one-shot while its (world-1)-fold inbound
+        traffic is small, then the in-switch reduction; without multicast, fenced one-shot up to 1 MB and two-shot above.
+        At two ranks the switch has nothing to save (each rank's own data loops through it), so two-shot takes over."""
+        world = getattr(self, 'size', None) or getattr(self, 'world', 2)
         one_max = env_int('DDLS_ONESHOT_MAX_BYTES', 1 << 20)
         forced = env_str('DDLS_ALLREDUCE_ALGO', '')
         if forced:
             return {'oneshot': AR_ONESHOT, 'twoshot': AR_TWOSHOT, 'nvls': AR_NVLS, 'll': AR_ONESHOT_LL}[forced]
-        if nbytes <= self._ll_elems * 4:
+        if nbytes <= (self.ll_max_bytes(world) if have_mc else self._ll_elems * 4):
             return AR_ONESHOT_LL
-        if nbytes <= one_max or not symmetric_out:
+        if not symmetric_out:
             return AR_ONESHOT
-        return AR_NVLS if have_mc else AR_TWOSHOT
+        if have_mc and not (world == 2 and nbytes >= (2 << 20)):
+            return AR_NVLS
+        return AR_ONESHOT if nbytes <= one_max else AR_TWOSHOT
 
 
 class PeerMemoryComm(Communicator, _HeapBase):
@@ -203,7 +215,7 @@ class PeerMemoryComm(Communicator, _HeapBase):
         # gradient allreduce overlaps with
         self._ar_blocks = env_int('DDLS_AR_BLOCKS', 0)
         # flag-in-data packets pushed with one store through the multicast mapping instead of one store per peer
-        self._ll_mc_push = env_int('DDLS_LL_MC_PUSH', 0) != 0
+        self._ll_mc_push = env_int('DDLS_LL_MC_PUSH', 1) != 0
         self._heap_u8[self._ll_off:self._ll_off + self._ll_bytes].zero_()
         torch.cuda.synchronize(device)
         self._pg_barrier()
