@@ -34,6 +34,40 @@ def _plan(model):
     return plan
 
 
+class NativePathError(RuntimeError):
+    """A CUDA model would train on PyTorch's eager cuDNN / cuBLAS kernels because no hand-written kernel covers it."""
+
+
+def covers(model, x: torch.Tensor, loss_name: str) -> bool:
+    """Do the hand-written kernels cover training ``model`` on batch ``x`` with this loss (through the autograd-free
+    DirectStep or the autograd wrappers of the same kernels)?"""
+    plan = _plan(model)
+    if not x.is_cuda:
+        return False
+    if plan['kind'] == 'rnn_regressor':
+        from . import recurrent
+        return recurrent.native_available(x, plan['rnn'].units)
+    if plan['kind'] == 'cnn':
+        from . import cnn
+        return loss_name == 'categorical_crossentropy' and cnn.native_available(plan, x)
+    if plan['kind'] == 'stacked_lstm':
+        from . import lstm_big
+        return loss_name in ('mean_squared_error', 'mse') and lstm_big.supported(plan['lstms'], x)
+    return False
+
+
+def require_native(model, x: torch.Tensor, loss_name: str) -> None:
+    """Raise instead of silently training a CUDA model on eager PyTorch ops (set DDLS_ALLOW_EAGER=1 to allow it)."""
+    import os
+    if x.is_cuda and not covers(model, x, loss_name) and os.environ.get('DDLS_ALLOW_EAGER', '0') != '1':
+        kinds = [l.keras_class for l in model.layers_list]
+        raise NativePathError(
+            f'no hand-written sm_100a kernel path covers this model on CUDA (layers {kinds}, input {tuple(x.shape)}, loss '
+            f'{loss_name!r}).  Covered: LSTM/GRU(128) + Dense(<=4) on [B,T,1] inputs with mean_squared_error; the 28x28x1 '
+            f'Conv(32)-Conv(32)-MaxPool-Dense-Dense CNN with categorical_crossentropy; stacked LSTM (units % 128 == 0) + '
+            f'Dense.  Set DDLS_ALLOW_EAGER=1 to train it on PyTorch eager kernels (cuDNN / cuBLAS) instead.')
+
+
 def _cnn_trunk(plan, x):
     from . import cnn
     if cnn.native_available(plan, x):

@@ -95,7 +95,9 @@ def broadcast_optimizer_state(optimizer, root_rank: int = 0) -> None:
     comm = _comm()
     inner = getattr(optimizer, 'inner', optimizer)
     if isinstance(inner, _FlatOptimizer):
-        inner.gather_slots()            # slots sharded by the data-parallel step kernel: complete them on every rank first
+        # The root's slots are taken as complete and authoritative (a freshly constructed optimizer, or one that has just
+        # loaded a checkpoint).  Mid-training, when the sharded data-parallel step keeps each slice of m / v up to date
+        # only on its owner, call ``optimizer.gather_slots()`` on every rank first.
         comm.broadcast_(inner.step_count, root_rank)
         for t in inner.slots().values():
             comm.broadcast_(t, root_rank)

@@ -122,6 +122,9 @@ class _HeapBase:
             return self._ll_off, self._ll_bytes
         if n_elems > self._stage_elems:
             want = max(n_elems, 1 << 20)
+            if self._stage_bytes and self._stage_off + self._stage_bytes == self._top:
+                self._top = self._stage_off          # the old region is the last allocation: grow it in place
+            # (otherwise the bump allocator cannot give the old region back; size DDLS_HEAP_MB for the largest message)
             self._stage_bytes = 2 * world * want * 4
             self._stage_off = self._alloc_off(self._stage_bytes)
             self._stage_elems = want
@@ -456,10 +459,34 @@ class PeerMemoryComm(Communicator, _HeapBase):
         return box[0]
 
     def close(self) -> None:
+        """Drain the device, wait for every rank (nobody may still be reading this heap), then unmap the multicast view,
+        the peers' heaps and this rank's own heap and release their handles.  Tensors handed out by ``alloc`` are dead
+        afterwards.  If the ranks cannot be synchronised (a peer died) the mappings are left to process exit."""
+        if getattr(self, '_closed', False):
+            return
+        self._closed = True
         try:
             torch.cuda.synchronize(self.device)
-        except Exception:
-            pass
+            self._pg_barrier()
+        except Exception:  # noqa: BLE001 - a dead peer: do not unmap under a possibly running kernel
+            return
+        self._heap_u8 = None
+        size = self.heap_bytes
+        try:
+            if self.mc_base:
+                N.call('ddls_symm_unmap', self.mc_base, size, self._mc_handle)
+                self.mc_base, self._mc_handle = 0, 0
+            for r in range(self.size):
+                if r != self.rank and self._bases[r]:
+                    N.call('ddls_symm_unmap', self._bases[r], size, self._handles[r])
+                    self._bases[r] = self._handles[r] = 0
+            self._pg_barrier()                       # every importer has dropped its mapping of my heap
+            if self._bases[self.rank]:
+                N.call('ddls_symm_unmap', self._bases[self.rank], size, self._handles[self.rank])
+                self._bases[self.rank] = self._handles[self.rank] = 0
+        except Exception as e:  # noqa: BLE001
+            from ..utils.logging import get_logger
+            get_logger().warning('peer-memory close: %s', e)
 
 
 class EmulatedPeerGroup(_HeapBase):

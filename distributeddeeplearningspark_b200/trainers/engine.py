@@ -79,6 +79,7 @@ class StepEngine:
         self._inner = inner
         self._direct = None          # autograd-free fused step (ops.fused.DirectStep), built lazily
         self._direct_checked = False
+        self._native_checked = False
         self.use_direct = self.cuda and env_flag('DDLS_DIRECT_STEP', True)
         # the fused optimizer kernels can clear the gradient buffer after consuming it
         self._skip_zero = self.cuda and bool(getattr(inner, 'zero_grads_in_step', False))
@@ -108,6 +109,10 @@ class StepEngine:
             loss = direct.run(x, y)
             self.optimizer.step()
             return loss.reshape(())
+        if self.cuda and not self._native_checked:
+            from ..ops import fused
+            fused.require_native(self.model, x, self.loss_name)      # no silent cuDNN / cuBLAS training on a GPU box
+            self._native_checked = True
         if not self._skip_zero:
             self.optimizer.zero_grad()
         loss = self._loss(x, y)

@@ -28,7 +28,8 @@ from .. import runtime
 from ..data.feeder import DeviceFeeder
 from ..data.frame import DataFrame
 from ..models.sequential import Sequential, deserialize_model, serialize_model
-from ..utils.logging import get_logger
+from ..utils.logging import MetricsWriter, get_logger
+from ..utils.timing import PhaseTimers, Timeline
 from .engine import StepEngine
 from .parameter_server import CollectiveCenter, MulticastCenter, ParameterServerView
 
@@ -61,14 +62,25 @@ def load_partition(d: str, i: int):
 # worker bodies (run inside each rank)
 # ----------------------------------------------------------------------------
 def _worker(spec: Dict) -> Dict:
+    # Observability (the reference only has get_training_time()): host-side phase timers are always on and
+    # come back with the result; DDLS_TIMELINE=<path> writes a Chrome trace per rank (Horovod-timeline analogue);
+    # DDLS_METRICS=<path> appends {step, loss, samples_per_s} every DDLS_METRICS_EVERY steps (rank 0) as JSON lines.
+    phases = PhaseTimers()
+    t_init = time.perf_counter()
     runtime.init()
     rank, size = runtime.rank(), runtime.size()
     dev = runtime.device()
     comm = runtime.communicator()
+    timeline = Timeline(rank=rank)
+    metrics = MetricsWriter(os.environ.get('DDLS_METRICS'), rank=rank)
+    metrics_every = max(1, int(os.environ.get('DDLS_METRICS_EVERY', '50')))
+    phases.total['init'] = time.perf_counter() - t_init; phases.count['init'] = 1
+    timeline.instant('runtime.init done', size=size, comm=type(comm).__name__)
     if spec.get('seed') is not None:
         torch.manual_seed(spec['seed'] + rank)
-    model = deserialize_model(spec['model']).to(dev)
-    x, y = load_partition(spec['parts'], rank)
+    with phases.phase('load'), timeline.span('load model + partition', cat='setup'):
+        model = deserialize_model(spec['model']).to(dev)
+        x, y = load_partition(spec['parts'], rank)
     mode = spec['mode']
     engine = StepEngine(model, optimizer=spec['worker_optimizer'], loss=spec['loss'], device=dev,
                         comm=comm if mode == 'allreduce' else None, distributed=(mode == 'allreduce'),
@@ -104,22 +116,30 @@ def _worker(spec: Dict) -> Dict:
     losses: List[torch.Tensor] = []
     t0 = time.perf_counter()
     it = 0
-    for batch in feeder:
-        if it >= n_batches:
+    feed = iter(feeder)
+    while it < n_batches:
+        with phases.phase('feed'):
+            batch = next(feed, None)
+        if batch is None:
             break
         xb = batch['x']
         if xb.dtype != torch.float32:
             xb = xb.float()
         # step() returns the engine's static loss tensor on every CUDA-graph replay: snapshot it (a tiny on-stream copy),
         # otherwise the history would alias one buffer and read [.., last, last, last]
-        losses.append(engine.step(xb, batch['y']).detach().clone())
+        with phases.phase('step'), timeline.span('step', step=it):
+            losses.append(engine.step(xb, batch['y']).detach().clone())
         it += 1
         if center is not None and it % window == 0:
-            if mode == 'aeasgd':
-                center.elastic_round(flat.flat_params, alpha, active=True)
-                engine.notify_params_changed()
-            else:
-                center.commit_pull(flat.flat_params, 1.0 / window if mode == 'adag' else 1.0, active=True)
+            with phases.phase('exchange'), timeline.span('commit+pull', cat='comm', update=it // window):
+                if mode == 'aeasgd':
+                    center.elastic_round(flat.flat_params, alpha, active=True)
+                    engine.notify_params_changed()
+                else:
+                    center.commit_pull(flat.flat_params, 1.0 / window if mode == 'adag' else 1.0, active=True)
+        if metrics.enabled and it % metrics_every == 0:
+            metrics.write(step=it, loss=float(losses[-1]), samples_per_s=it * spec['batch_size'] / (time.perf_counter() - t0),
+                          mode=mode)
         if avg_every and it % avg_every == 0 and size > 1:
             from ..parallel.comm import Average
             comm.allreduce_(flat.flat_params, Average)
@@ -141,7 +161,12 @@ def _worker(spec: Dict) -> Dict:
         torch.cuda.synchronize(dev)
     elapsed = time.perf_counter() - t0
     hist = torch.stack(losses).float().cpu().tolist() if losses else []
-    out = {'rank': rank, 'history': hist, 'num_updates': num_updates, 'elapsed': elapsed, 'steps': it}
+    out = {'rank': rank, 'history': hist, 'num_updates': num_updates, 'elapsed': elapsed, 'steps': it,
+           'phases': phases.summary()}
+    metrics.write(step=it, loss=(hist[-1] if hist else None), samples_per_s=it * spec['batch_size'] / max(elapsed, 1e-9),
+                  mode=mode, final=True)
+    metrics.close()
+    timeline.dump()
     if rank == 0 or mode == 'ensemble':
         out['weights'] = model.get_weights()
         if spec.get('checkpoint'):
@@ -198,6 +223,11 @@ class Trainer:
     def get_history(self):
         return self.history
 
+    def get_phase_times(self):
+        """Per-rank host-side phase timers of the last ``train()``: {'init' | 'load' | 'feed' | 'step' | 'exchange':
+        {'total_s', 'count', 'mean_ms'}} (the breakdown ``get_training_time()`` of the reference does not give)."""
+        return getattr(self, 'phase_times', [])
+
     def get_averaged_history(self):
         if not self.history:
             return []
@@ -234,6 +264,7 @@ class Trainer:
             shutil.rmtree(parts_dir, ignore_errors=True)
         self.worker_results = results
         self.history = [r['history'] for r in results]
+        self.phase_times = [r.get('phases', {}) for r in results]
         model = deserialize_model(self.master_model)
         model.set_weights(results[0]['weights'])
         self.parameter_server = ParameterServerView(self._count_updates(results), model)

@@ -398,6 +398,25 @@ def _sharded_step_checks(ddls, comm, dev, r, n):
     res['cnn_loss'] = (losses[0], losses[-1])
     res['cnn_steps'] = int(opt.step_count.item())
     res['cnn_shadow_ok'] = bool(torch.equal(eng._direct.w1s[:, :225], model.layers_list[6].kernel.detach().bfloat16()))
+    # checkpoint on CUDA ranks with sharded optimizer slots: rank 0 saves (the slots are gathered first), a fresh model +
+    # optimizer on every rank resumes (load on rank 0, broadcast), and one more step of both runs lands on the same weights
+    import tempfile
+    from distributeddeeplearningspark_b200.ckpt import resume, save_checkpoint
+    path = ddls.broadcast_object(os.path.join(tempfile.mkdtemp(prefix='ddls_ckpt_'), 'cnn') if r == 0 else None, 0)
+    save_checkpoint(path, model, dopt, step=12)
+    ddls.barrier(); torch.cuda.synchronize()
+    model2 = ddls.models.mnist_cnn(seed=50 + r).to(dev)
+    opt2 = ddls.optim.KerasAdam(model2.parameters(), comm=comm)
+    dopt2 = ddls.DistributedOptimizer(opt2)
+    eng2 = StepEngine(model2, optimizer=dopt2, loss='categorical_crossentropy', device=dev, use_cuda_graph=False)
+    eng2.step(x, y)                                   # builds the fused step and its bf16 shadows from the wrong weights
+    meta = resume(path, model2, dopt2)
+    res['resume_step'] = int(meta.get('step') or -1), int(opt2.step_count.item())
+    la, lb = float(eng.step(x, y)), float(eng2.step(x, y))
+    torch.cuda.synchronize()
+    res['resume_loss'] = (la, lb)
+    res['resume_err'] = float((opt.flat.flat_params - opt2.flat.flat_params).abs().max())
+    res['resume_ok'] = abs(la - lb) < 1e-4 * max(1.0, abs(la)) and res['resume_err'] < 5e-5
     return res
 
 
@@ -415,7 +434,38 @@ def test_peer_memory_comm_multi_gpu():
     assert all(o['cnn_weights_equal'] and o['cnn_shadow_ok'] for o in out)
     assert all(o['cnn_modes'][0] == 'dp' and o['cnn_steps'] == 12 for o in out), [(o['cnn_modes'], o['cnn_steps']) for o in out]
     assert all(o['cnn_loss'][1] < o['cnn_loss'][0] for o in out), [o['cnn_loss'] for o in out]
+    assert all(o['resume_ok'] and o['resume_step'] == (12, 13) for o in out), [(o['resume_step'], o['resume_loss'], o['resume_err']) for o in out]
     import json, os
     os.makedirs('gpurun_out', exist_ok=True)
     with open('gpurun_out/multigpu_checks.json', 'w') as f:
         json.dump(out, f, indent=1, default=str)
+
+
+def _stalled_peer():
+    """Rank 1 never joins the collective: rank 0's kernel must give up after DDLS_COMM_TIMEOUT_MS, not spin for ever."""
+    import time
+    import distributeddeeplearningspark_b200 as ddls
+    ddls.init()
+    comm = ddls.runtime.communicator()
+    t = comm.alloc(1024)
+    if ddls.rank() == 1:
+        time.sleep(40)                                   # alive (the launcher sees no dead process) but silent
+        return 'late'
+    t0 = time.time()
+    comm.allreduce_(t, ddls.Sum, algo=AR_ONESHOT)
+    torch.cuda.synchronize()                             # the trapped kernel surfaces here as a CUDA error
+    return time.time() - t0
+
+
+@pytest.mark.multigpu
+def test_silent_peer_trips_the_flag_timeout_and_surfaces_as_stage_error():
+    """Failure detection on the device side: a flag wait that exceeds DDLS_COMM_TIMEOUT_MS prints rank / peer /
+    epoch and traps; the launcher turns the resulting CUDA error of that rank into a BarrierStageError and tears the
+    stalled peer down."""
+    import time
+    from distributeddeeplearningspark_b200 import spark
+    from distributeddeeplearningspark_b200.spark import BarrierStageError, LocalBarrierBackend
+    t0 = time.time()
+    with pytest.raises(BarrierStageError, match='rank 0 failed'):
+        spark.run(_stalled_peer, num_proc=2, backend=LocalBarrierBackend(timeout=120), env={'DDLS_COMM_TIMEOUT_MS': '2000'})
+    assert time.time() - t0 < 35, 'the timeout did not fire before the stalled peer woke up'

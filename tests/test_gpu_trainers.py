@@ -58,3 +58,28 @@ def test_cnn_checkpoint_resume_on_cuda_refreshes_bf16_shadows(tmp_path):
     for a, b in zip(m1.get_weights(), m2.get_weights()):
         np.testing.assert_allclose(a, b, rtol=0, atol=2e-5)
     assert int(e1.optimizer.step_count.item()) == int(e2.optimizer.step_count.item()) == 6
+
+
+def test_uncovered_model_on_cuda_raises_instead_of_falling_back(monkeypatch):
+    """'No silent PyTorch fallback on a GPU box': a model no hand-written kernel covers (GRU(64) over 3 input features,
+    the LEN_EXTRA_IN > 1 case of /root/reference/ddl_nyiso_aztk.py:80-88) must raise, and train eagerly only when asked."""
+    from distributeddeeplearningspark_b200.models import Sequential
+    from distributeddeeplearningspark_b200.models.layers import GRU, Dense
+    from distributeddeeplearningspark_b200.ops.fused import NativePathError
+    from distributeddeeplearningspark_b200.trainers import StepEngine
+    dev = torch.device('cuda', 0)
+
+    def make():
+        m = Sequential([GRU(64, input_shape=(25, 3)), Dense(1)])
+        m.compile(optimizer='adagrad', loss='mean_squared_error')
+        return m.to(dev)
+    x, y = torch.rand(32, 25, 3, device=dev), torch.rand(32, 1, device=dev)
+    monkeypatch.delenv('DDLS_ALLOW_EAGER', raising=False)
+    with pytest.raises(NativePathError, match='DDLS_ALLOW_EAGER'):
+        StepEngine(make(), optimizer='adagrad', loss='mean_squared_error', device=dev, use_cuda_graph=False).step(x, y)
+    monkeypatch.setenv('DDLS_ALLOW_EAGER', '1')
+    eng = StepEngine(make(), optimizer='adagrad', loss='mean_squared_error', device=dev, use_cuda_graph=False)
+    l0 = float(eng.step(x, y))
+    for _ in range(10):
+        l1 = float(eng.step(x, y))
+    assert l1 < l0
