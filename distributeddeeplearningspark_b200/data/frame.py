@@ -263,6 +263,13 @@ class DataFrame:
             print_fn(f'only showing top {n} row' + ('s' if n != 1 else ''))
 
 
+    def to_string(self, n: int = 20, truncate: int = 20) -> str:
+        """What ``show`` prints, as a string (run records, logs)."""
+        lines: List[str] = []
+        self.show(n, truncate, print_fn=lines.append)
+        return '\n'.join(lines)
+
+
 class VectorAssembler:
     """``pyspark.ml.feature.VectorAssembler`` analogue: stack scalar/vector columns into one vector
     column (/root/reference/ddl_mnist_aztk.py:118, /root/reference/ddl_nyiso_aztk.py:154,165,169)."""

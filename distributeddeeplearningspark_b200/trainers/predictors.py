@@ -38,7 +38,7 @@ class Predictor:
 def _predict_batches(model: Sequential, x: np.ndarray, batch_size: int, dev: torch.device) -> np.ndarray:
     model = model.to(dev).eval()
     outs = []
-    xt = torch.from_numpy(np.ascontiguousarray(x, dtype=np.float32))
+    xt = torch.from_numpy(np.array(x, dtype=np.float32, order='C'))       # a writable copy (partitions may be mmap'ed)
     pin = dev.type == 'cuda'
     with torch.no_grad():
         for lo in range(0, xt.shape[0], batch_size):

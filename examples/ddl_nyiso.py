@@ -7,6 +7,12 @@ reachable here, so an hourly synthetic series with the same columns stands in (`
 
     python examples/ddl_nyiso.py --num-workers 4
     python examples/ddl_nyiso.py --num-workers 2 --cpu --epochs 2 --hours 1200
+    python examples/ddl_nyiso.py --num-workers 4 --hours 11566 --cell lstm --report docs/ddl_nyiso_run.md
+
+``--cell`` runs one of the notebook's two training cells (``gru`` = ddl_nyiso_hdi.ipynb cells up to :730, ``lstm`` = :772-934)
+or ``all``; ``--report`` writes what the notebook keeps as recorded cell outputs — worker count, sample rows of every
+pipeline stage, parameter counts, parameter-server updates, training seconds, MAPE — next to the values recorded in
+the reference notebook, as a Markdown file.
 """
 import argparse
 import os
@@ -31,14 +37,18 @@ def main():
     ap.add_argument('--hours', type=int, default=11688)
     ap.add_argument('--csv', default=None)
     ap.add_argument('--trainer', default='adag', choices=['adag', 'dynsgd'])
+    ap.add_argument('--cell', default='all', choices=['all', 'gru', 'lstm'])
+    ap.add_argument('--report', default=None, help='write a notebook-style run record (Markdown) here')
     ap.add_argument('--cpu', action='store_true')
     a = ap.parse_args()
+    rec = []          # (cell title, recorded text) pairs of the run record
     if a.cpu:
         os.environ['DDLS_FORCE_CPU'] = '1'
     num_workers = a.num_workers or a.num_executors * a.num_processes
     print('Number of desired executors: ' + str(a.num_executors))
     print('Number of desired processes per executor: ' + str(a.num_processes))
     print('Total number of workers: ' + str(num_workers))
+    rec.append(('Workers', f'Total number of workers: {num_workers}   (notebook: 4, ipynb:93)'))
 
     ## Define variables
     LEN_SEQ_IN, LEN_SEQ_OUT = 24, 1
@@ -57,6 +67,7 @@ def main():
         raw_df = nyiso_like_frame(a.hours, seed=0)
     df = raw_df.select(['TimeStamp', 'Name', 'HourAvgLoad', 'temperature'])
     df.show(3)
+    rec.append(('Raw rows (ipynb:207-209)', df.to_string(3) + f'\nrows: {df.count()}'))
 
     # Normalize the data
     orig_min, orig_max = df.agg_min('temperature'), df.agg_max('temperature')
@@ -66,6 +77,7 @@ def main():
     df = MinMaxTransformer(n_min=0.0, n_max=1.0, o_min=orig_min, o_max=orig_max, input_col='HourAvgLoad',
                            output_col='NormLoad', is_vector=False).transform(df)
     df.show(3)
+    rec.append(('Min-max normalised rows (ipynb:237-239)', df.to_string(3)))
 
     # Create input features and output targets
     wSpec = Window.partitionBy('Name').orderBy('TimeStamp')
@@ -96,6 +108,8 @@ def main():
     cols = ['features', 'feature_matrix', 'labels', 'labels2', 'label_matrix']
     df_train = df_train.select(*cols).repartition(num_workers).cache()
     df_test = df_test.select(*cols).repartition(num_workers).cache()
+    rec.append(('Train / test split (ipynb:478)', f'training windows: {df_train.count()}, test windows: {df_test.count()}, '
+                f'partitions: {[len(df_train.partition_indices(i, num_workers)) for i in range(num_workers)]}'))
 
     inverse_transformer = MinMaxTransformer(n_min=orig_min, n_max=orig_max, o_min=0.0, o_max=1.0,
                                             input_col='prediction', output_col='prediction2', is_vector=True)
@@ -116,19 +130,42 @@ def main():
         pred = [list(r) for r in np.asarray(df_pred['prediction2'])]
         mape = get_MAPE(actual, pred)
         print(f'{tag} MAPE on 24 test hours: {mape:.3f} %')
+        ref = {'GRU': '1425 updates, 88.475 s, MAPE 2.809 % (ipynb:608-609, 730), 50,049 parameters (ipynb:549-553)',
+               'LSTM': '1425 updates, 99.254 s, MAPE 3.587 % (ipynb:817-818, 934), 66,689 parameters (ipynb:772-776)'}[tag]
+        rec.append((f'{tag} + ADAG({optimizer})',
+                    f'parameters: {sum(p.numel() for p in model.parameters()):,}\n'
+                    f'Number of parameter updates {trainer.parameter_server.num_updates}\n'
+                    f'Total training time in seconds {trainer.get_training_time():.3f}\n'
+                    f'MAPE on 24 test hours: {mape:.3f} %\n'
+                    f'samples/s: {trainer.parameter_server.num_updates * COM_WINDOW * BATCH_SIZE / trainer.get_training_time():,.0f}\n'
+                    f'reference notebook (4 CPU workers, real NYISO data): {ref}'))
         return mape
 
     # Create the GRU network (ddl_nyiso_aztk.py:200-246)
     gru_model = Sequential()
     gru_model.add(GRU(N_UNITS, input_shape=(LEN_SEQ_IN + LEN_EXTRA_IN, 1)))
     gru_model.add(Dense(LEN_SEQ_OUT, activation='linear'))
-    fit_and_score(gru_model, 'adagrad', 'GRU')
+    if a.cell in ('all', 'gru'):
+        fit_and_score(gru_model, 'adagrad', 'GRU')
 
     # Create the LSTM network (ddl_nyiso_aztk.py:248-274)
     lstm_model = Sequential()
     lstm_model.add(LSTM(N_UNITS, input_shape=(LEN_SEQ_IN + LEN_EXTRA_IN, 1)))
     lstm_model.add(Dense(LEN_SEQ_OUT, activation='linear'))
-    fit_and_score(lstm_model, 'adam', 'LSTM')
+    if a.cell in ('all', 'lstm'):
+        fit_and_score(lstm_model, 'adam', 'LSTM')
+    if a.report:
+        import platform
+        import torch
+        where = torch.cuda.get_device_name(0) if (torch.cuda.is_available() and not a.cpu) else platform.processor() or 'cpu'
+        with open(a.report, 'w') as f:
+            f.write('# NYISO load forecast: run record\n\nThe counterpart of the recorded cell outputs of '
+                    '`/root/reference/ddl_nyiso_hdi.ipynb`, produced by `examples/ddl_nyiso.py` '
+                    f'(`{" ".join(sys.argv[1:])}`) on {num_workers} x {where}.  Synthetic hourly series '
+                    '(the NYISO blob is not reachable), so MAPE is not comparable with the notebook; update counts are.\n')
+            for title, text in rec:
+                f.write(f'\n## {title}\n\n```\n{text}\n```\n')
+        print('run record written to ' + a.report)
 
 
 if __name__ == '__main__':
