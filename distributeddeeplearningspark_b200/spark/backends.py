@@ -244,9 +244,10 @@ class InProcessBackend:
 
 
 # ----------------------------------------------------------------------------
-# real PySpark adapter (import-guarded; not testable on this image)
+# real PySpark adapter (import-guarded: no pyspark / JVM on this image; tests/test_launcher.py drives it against a fake
+# ``pyspark`` module that implements the six calls used here with threads)
 # ----------------------------------------------------------------------------
-class PySparkBarrierBackend:  # pragma: no cover - needs pyspark + JVM
+class PySparkBarrierBackend:
     def __init__(self, spark_context=None):
         try:
             import pyspark  # noqa: F401

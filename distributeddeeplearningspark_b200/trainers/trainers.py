@@ -41,21 +41,51 @@ def _feature_dtype(a: np.ndarray) -> np.dtype:
     return np.uint8 if a.dtype == np.uint8 else np.float32
 
 
+def partition_format() -> str:
+    """'npy' (memory-mapped arrays, whole-partition random access: needed for shuffling) or 'arrow' (Arrow IPC record
+    batches streamed through ``data.arrow_feed.ArrowStreamFeeder`` — the form a Spark ``mapInArrow`` stage delivers)."""
+    return os.environ.get('DDLS_PARTITION_FORMAT', 'npy').lower()
+
+
 def stage_partitions(df: DataFrame, features_col: str, label_col: str, n: int, root: Optional[str] = None) -> str:
-    """Write partition i's feature/label columns as ``.npy`` files ranks can mmap (driver side)."""
+    """Write partition i's feature/label columns where the ranks can map them (driver side): ``x{i}.npy`` / ``y{i}.npy``,
+    or one Arrow IPC file ``part{i}.arrow`` per partition with ``DDLS_PARTITION_FORMAT=arrow``."""
     base = root or ('/dev/shm' if os.path.isdir('/dev/shm') else None)
     d = tempfile.mkdtemp(prefix='ddls_parts_', dir=base)
+    arrow = partition_format() == 'arrow'
     for i in range(n):
         idx = df.partition_indices(i, n)
         x = np.asarray(df[features_col])[idx]
         y = np.asarray(df[label_col])[idx]
-        np.save(os.path.join(d, f'x{i}.npy'), np.ascontiguousarray(x, dtype=_feature_dtype(x)))
-        np.save(os.path.join(d, f'y{i}.npy'), np.ascontiguousarray(y, dtype=np.float32))
+        x = np.ascontiguousarray(x, dtype=_feature_dtype(x)); y = np.ascontiguousarray(y, dtype=np.float32)
+        if arrow:
+            from ..data.arrow_feed import write_partition_file
+            write_partition_file(os.path.join(d, f'part{i}.arrow'), {'x': x, 'y': y.reshape(len(y), -1)},
+                                 rows_per_batch=int(os.environ.get('DDLS_ARROW_BATCH_ROWS', '2048')))
+        else:
+            np.save(os.path.join(d, f'x{i}.npy'), x)
+            np.save(os.path.join(d, f'y{i}.npy'), y)
     return d
 
 
 def load_partition(d: str, i: int):
     return np.load(os.path.join(d, f'x{i}.npy'), mmap_mode='r'), np.load(os.path.join(d, f'y{i}.npy'), mmap_mode='r')
+
+
+def open_feeder(spec: Dict, rank: int, dev):
+    """The rank's minibatch feeder over its staged partition (pinned ring + copy stream in both formats)."""
+    arrow_path = os.path.join(spec['parts'], f'part{rank}.arrow')
+    if os.path.exists(arrow_path):
+        from ..data.arrow_feed import ArrowStreamFeeder, ipc_file_source
+        if spec.get('shuffle'):
+            raise ValueError('shuffle=True needs random access: stage partitions with DDLS_PARTITION_FORMAT=npy')
+        source, rows, cols = ipc_file_source(arrow_path)
+        return ArrowStreamFeeder(source, {k: (k, shape, dt) for k, (shape, dt) in cols.items()}, spec['batch_size'], dev,
+                                 num_epoch=spec['num_epoch'], total_rows=rows)
+    x, y = load_partition(spec['parts'], rank)
+    return DeviceFeeder({'x': np.asarray(x), 'y': np.asarray(y)}, spec['batch_size'], dev,
+                        num_epoch=spec['num_epoch'], shuffle=spec.get('shuffle', False),
+                        seed=spec.get('seed') or 0, carry_over=True)
 
 
 # ----------------------------------------------------------------------------
@@ -80,7 +110,7 @@ def _worker(spec: Dict) -> Dict:
         torch.manual_seed(spec['seed'] + rank)
     with phases.phase('load'), timeline.span('load model + partition', cat='setup'):
         model = deserialize_model(spec['model']).to(dev)
-        x, y = load_partition(spec['parts'], rank)
+        feeder = open_feeder(spec, rank, dev)
     mode = spec['mode']
     engine = StepEngine(model, optimizer=spec['worker_optimizer'], loss=spec['loss'], device=dev,
                         comm=comm if mode == 'allreduce' else None, distributed=(mode == 'allreduce'),
@@ -88,9 +118,6 @@ def _worker(spec: Dict) -> Dict:
     flat = engine.optimizer.flat if hasattr(engine.optimizer, 'flat') else engine.optimizer.inner.flat
     if size > 1:
         comm.broadcast_(flat.flat_params, 0)
-    feeder = DeviceFeeder({'x': np.asarray(x), 'y': np.asarray(y)}, spec['batch_size'], dev,
-                          num_epoch=spec['num_epoch'], shuffle=spec.get('shuffle', False),
-                          seed=spec.get('seed') or 0, carry_over=True)
     window = int(spec.get('communication_window', 1))
     center = None
     async_center = False

@@ -148,3 +148,23 @@ def test_distkeras_utils_surface():
     assert U.history_executor([[1.0], [2.0]], 1) == [2.0]
     t = ddls.trainers.ADAG(m, 'adagrad', 'mean_squared_error', num_workers=2)
     assert t.master_port == 5000 and t.parallelism_factor == 1 and t.communication_window == 12
+
+
+def test_arrow_stream_feeder_cuts_the_same_minibatches_as_the_array_feeder(tmp_path):
+    """Arrow record batches -> pinned ring: minibatches straddle record batches and epochs exactly like the array feeder's
+    dist-keras-style carry-over batching; uint8 pixels stay uint8; the final partial minibatch is dropped."""
+    import torch
+    from distributeddeeplearningspark_b200.data import ArrowStreamFeeder, DeviceFeeder, ipc_file_source, write_partition_file
+    rng = np.random.default_rng(0)
+    x = rng.integers(0, 255, size=(103, 28, 28, 1), dtype=np.uint8)
+    y = rng.random((103, 10)).astype(np.float32)
+    path = str(tmp_path / 'part0.arrow')
+    assert write_partition_file(path, {'x': x, 'y': y}, rows_per_batch=17) == 7
+    source, rows, cols = ipc_file_source(path)
+    assert rows == 103 and cols['x'] == ((28, 28, 1), np.dtype('uint8')) and cols['y'][0] == (10,)
+    fa = ArrowStreamFeeder(source, {k: (k, s, d) for k, (s, d) in cols.items()}, 16, 'cpu', num_epoch=3, total_rows=rows)
+    fb = DeviceFeeder({'x': x, 'y': y}, 16, 'cpu', num_epoch=3, carry_over=True)
+    a, b = list(fa), [{k: v.clone() for k, v in d.items()} for d in fb]
+    assert len(a) == len(b) == len(fa) == (103 * 3) // 16
+    for da, db in zip(a, b):
+        assert da['x'].dtype == torch.uint8 and torch.equal(da['x'], db['x']) and torch.equal(da['y'], db['y'])

@@ -238,3 +238,20 @@ def test_trainer_observability_phase_times_metrics_jsonl_and_timeline(tmp_path, 
     assert all(r['samples_per_s'] > 0 for r in rows)
     ev = json.load(open(tmp_path / 'timeline.json'))['traceEvents']
     assert sum(1 for e in ev if e['name'] == 'step') == steps and any(e['ph'] == 'i' for e in ev)
+
+
+def test_trainer_streams_arrow_partitions_with_the_same_result_as_arrays(monkeypatch):
+    """DDLS_PARTITION_FORMAT=arrow: partitions are staged as Arrow IPC record batches and streamed through the pinned ring
+    (the mapInArrow-shaped feed); the training run is the same as with memory-mapped arrays."""
+    monkeypatch.setenv('DDLS_FORCE_CPU', '1')
+    tr, _, _, _ = _nyiso_frames(420)
+    hist = {}
+    for fmt in ('npy', 'arrow'):
+        monkeypatch.setenv('DDLS_PARTITION_FORMAT', fmt)
+        monkeypatch.setenv('DDLS_ARROW_BATCH_ROWS', '50')
+        t = SingleTrainer(keras_model=nyiso_lstm(units=4, seed=1), worker_optimizer='adam', loss='mean_squared_error',
+                          num_epoch=2, batch_size=16, features_col='feature_matrix', label_col='labels', seed=0)
+        t.train(tr)
+        hist[fmt] = (t.get_history()[0], t.parameter_server.num_updates)
+    assert hist['npy'][1] == hist['arrow'][1] and len(hist['npy'][0]) == (tr.count() * 2) // 16
+    np.testing.assert_allclose(hist['arrow'][0], hist['npy'][0], rtol=1e-6, atol=1e-7)
