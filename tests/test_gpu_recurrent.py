@@ -179,3 +179,41 @@ def test_stacked_big_lstm_direct_step_matches_autograd_reference(seq, monkeypatc
     with torch.no_grad():
         pred = m(x)
     assert float((pred - (h @ m.layers[-1].kernel + m.layers[-1].bias)).abs().max()) < 2e-2
+
+
+def test_stacked_lstm_at_its_benchmark_size_tracks_fp32_over_168_steps():
+    """BASELINE.json config 4 at full size (2 x LSTM(1024), T = 168, batch 512): bf16 recurrent state and bf16 GEMM operands
+    against the fp32 restatement of the Keras equations over all 168 dependent steps.  Stated drift tolerance: loss within
+    3 %, every gradient within 10 % relative L2 (measured: see gpurun_out/stacked_lstm_drift.json written by this test)."""
+    import json, os
+    import distributeddeeplearningspark_b200 as ddls
+    from distributeddeeplearningspark_b200.ops.fused import DirectStep
+    from distributeddeeplearningspark_b200.trainers import mean_squared_error
+    dev = torch.device('cuda', 0)
+    torch.manual_seed(0)
+    B, T = 512, 168
+    m = ddls.models.stacked_lstm(units=1024, len_seq=T, num_layers=2, seed=5).to(dev)
+    x = torch.rand(B, T, 1, device=dev); y = torch.rand(B, 1, device=dev)
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False                      # a true fp32 reference
+    try:
+        h = x
+        for l in m.layers[:-1]:
+            h = L.lstm_reference(h, l.kernel, l.recurrent_kernel, l.bias, l.return_sequences)
+        ref = mean_squared_error(h @ m.layers[-1].kernel + m.layers[-1].bias, y)
+        ref.backward()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32 = prev
+    gref = [p.grad.clone() for p in m.parameters()]
+    del h
+    torch.cuda.empty_cache()
+    opt = ddls.optim.KerasAdam(m.parameters())
+    assert DirectStep.supported(m, opt, 'mean_squared_error', x)
+    loss = DirectStep(m, opt, 'mean_squared_error').run(x, y)
+    torch.cuda.synchronize()
+    drift = {'loss': float(loss), 'loss_fp32': float(ref), 'loss_rel': abs(float(loss) - float(ref)) / abs(float(ref)),
+             'grad_rel_l2': {n: float((p.grad - g).norm() / (g.norm() + 1e-20)) for (n, p), g in zip(m.named_parameters(), gref)}}
+    os.makedirs('gpurun_out', exist_ok=True)
+    json.dump(drift, open('gpurun_out/stacked_lstm_drift.json', 'w'), indent=1)
+    assert drift['loss_rel'] < 3e-2, drift
+    assert max(drift['grad_rel_l2'].values()) < 0.10, drift

@@ -6,6 +6,7 @@ import torch
 import distributeddeeplearningspark_b200 as ddls
 from distributeddeeplearningspark_b200.trainers import StepEngine
 from torch.profiler import profile, ProfilerActivity
+from distributeddeeplearningspark_b200.utils import ClockSampler
 
 name = sys.argv[1] if len(sys.argv) > 1 else 'mnist_cnn'
 B = int(sys.argv[2]) if len(sys.argv) > 2 else (128 if name == 'mnist_cnn' else 32)
@@ -21,6 +22,7 @@ for _ in range(10):
     eng.step(x, y)
 torch.cuda.synchronize()
 N = 20
+sampler = ClockSampler(gpu_index=0, period_ms=20).start()
 with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as prof:
     for _ in range(N):
         eng.step(x, y)
@@ -38,4 +40,7 @@ for t, c, k in rows:
     print(f'{t:9.2f} us/step  x{c:4.1f}  {k[:100]}')
 print(f'{tot:9.2f} us/step total kernel time')
 os.makedirs('gpurun_out', exist_ok=True)
-json.dump([{'us_per_step': t, 'calls_per_step': c, 'kernel': k} for t, c, k in rows], open(f'gpurun_out/kernel_times_{name}.json', 'w'), indent=1)
+json.dump({'model': name, 'batch': B, 'how': 'CUPTI device times of 20 warm CUDA-graph replays (profiler attached: guidance, not bench values)',
+           'clocks': sampler.stop(), 'total_us_per_step': tot,
+           'kernels': [{'us_per_step': t, 'calls_per_step': c, 'kernel': k} for t, c, k in rows]},
+          open(f'gpurun_out/kernel_times_{name}.json', 'w'), indent=1)
