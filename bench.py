@@ -211,6 +211,7 @@ def measure(args, model_name, ddls, K, W, with_e2e=True, with_clocks=True):
     clocks = sampler.stop() if sampler is not None else None
     value = B * size * K / (ms / 1e3)
     pub = PUBLISHED.get(model_name)
+    dopt = engine.optimizer                      # (a lone rank: the engine wraps the optimizer for per-bucket updates)
     fused = bool(getattr(dopt, '_fused', False))
     return {
         'metric': md['metric'], 'value': value, 'unit': md['unit'], 'n_gpus': size, 'steps': K, 'warmup': W,

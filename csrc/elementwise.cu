@@ -29,13 +29,15 @@ __global__ void __launch_bounds__(EW_THREADS) refresh_shadows_kernel(const float
 
 // step[0] = completed steps, step[1] = arrival ticket.  Every block reads step[0] on entry; the last
 // block to finish publishes step[0]+1, so no block can observe the new value mid-kernel.
-DDLS_DEVINL void publish_step(int* step, int t) {
+// `advance` = 0: a range call that is not the last of its training step (per-bucket updates launched while backward is
+// still running) leaves the step count alone; every call still consumes and resets the ticket.
+DDLS_DEVINL void publish_step(int* step, int t, int advance) {
   __syncthreads();
   if (threadIdx.x == 0) {
     __threadfence();
     unsigned ticket = atomicAdd(reinterpret_cast<unsigned*>(step + 1), 1u);
     if (ticket == gridDim.x - 1) {
-      step[0] = t;
+      if (advance) step[0] = t;
       step[1] = 0;
       __threadfence();
     }
@@ -45,7 +47,7 @@ DDLS_DEVINL void publish_step(int* step, int t) {
 __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p, float4* __restrict__ g,
                                                           float4* __restrict__ m, float4* __restrict__ v, int* step,
                                                           size_t n4, float lr, float b1, float b2, float eps,
-                                                          float gs, int zero_grads, ShadowSet sh) {
+                                                          float gs, int zero_grads, ShadowSet sh, size_t elem0, int advance) {
   pdl_wait();
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   __shared__ float s_lr_t;                 // two powf per thread cost more than the update itself: one thread computes
@@ -64,14 +66,14 @@ __global__ void __launch_bounds__(EW_THREADS) adam_kernel(float4* __restrict__ p
     m[i] = mi; v[i] = vi; p[i] = pi;
     if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
-    write_shadows(sh, 4 * i, pv);
+    write_shadows(sh, elem0 + 4 * i, pv);
   }
-  publish_step(step, t);
+  publish_step(step, t, advance);
 }
 
 __global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict__ p, float4* __restrict__ g,
                                                              float4* __restrict__ a, int* step, size_t n4, float lr,
-                                                             float eps, float gs, int zero_grads, ShadowSet sh) {
+                                                             float eps, float gs, int zero_grads, ShadowSet sh, size_t elem0, int advance) {
   pdl_wait();
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
@@ -83,13 +85,14 @@ __global__ void __launch_bounds__(EW_THREADS) adagrad_kernel(float4* __restrict_
     a[i] = ai; p[i] = pi;
     if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
-    write_shadows(sh, 4 * i, pv);
+    write_shadows(sh, elem0 + 4 * i, pv);
   }
-  publish_step(step, t);
+  publish_step(step, t, advance);
 }
 
 __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(float4* __restrict__ p, float4* __restrict__ g, int* step,
-                                                         size_t n4, float lr, float gs, int zero_grads, ShadowSet sh) {
+                                                         size_t n4, float lr, float gs, int zero_grads, ShadowSet sh, size_t elem0,
+                                                         int advance) {
   pdl_wait();
   const int t = *reinterpret_cast<volatile int*>(step) + 1;
   const float a = lr * gs;
@@ -99,9 +102,9 @@ __global__ void __launch_bounds__(EW_THREADS) sgd_kernel(float4* __restrict__ p,
     p[i] = pi;
     if (zero_grads) g[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     const float pv[4] = {pi.x, pi.y, pi.z, pi.w};
-    write_shadows(sh, 4 * i, pv);
+    write_shadows(sh, elem0 + 4 * i, pv);
   }
-  publish_step(step, t);
+  publish_step(step, t, advance);
 }
 
 __global__ void __launch_bounds__(EW_THREADS) mnist_preprocess_kernel(const uint8_t* __restrict__ pix,
@@ -140,40 +143,59 @@ static int check_flat(const void* a, size_t n, const char* who) {
 
 using namespace ddls;
 
+extern "C" int ddls_adam_step_range(float* params, float* grads, float* m, float* v, int* step, size_t n, size_t elem0,
+                                    int advance, float lr, float beta1, float beta2, float eps, float grad_scale,
+                                    int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
+  if (n == 0) return 0;
+  if (check_flat(params, n, "ddls_adam_step") || check_flat(grads, n, "ddls_adam_step") || (elem0 & 3)) return 1;
+  DDLS_CUDA_OK(launch_k(adam_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream),
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(m),
+      reinterpret_cast<float4*>(v), step, n / 4, lr, beta1, beta2, eps, grad_scale, zero_grads,
+      make_shadows(shadows, n_shadows), elem0, advance));
+  count_launch(1);
+  return check_cuda(cudaGetLastError(), "adam_kernel launch");
+}
+
 extern "C" int ddls_adam_step(float* params, float* grads, float* m, float* v, int* step, size_t n, float lr,
                               float beta1, float beta2, float eps, float grad_scale, int zero_grads,
                               const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
+  return ddls_adam_step_range(params, grads, m, v, step, n, 0, 1, lr, beta1, beta2, eps, grad_scale, zero_grads, shadows,
+                              n_shadows, stream);
+}
+
+extern "C" int ddls_adagrad_step_range(float* params, float* grads, float* acc, int* step, size_t n, size_t elem0,
+                                       int advance, float lr, float eps, float grad_scale, int zero_grads,
+                                       const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
   if (n == 0) return 0;
-  if (check_flat(params, n, "ddls_adam_step") || check_flat(grads, n, "ddls_adam_step")) return 1;
-  launch_k(adam_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
-      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(m),
-      reinterpret_cast<float4*>(v), step, n / 4, lr, beta1, beta2, eps, grad_scale, zero_grads,
-      make_shadows(shadows, n_shadows));
+  if (check_flat(params, n, "ddls_adagrad_step") || check_flat(grads, n, "ddls_adagrad_step") || (elem0 & 3)) return 1;
+  DDLS_CUDA_OK(launch_k(adagrad_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream),
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(acc), step, n / 4,
+      lr, eps, grad_scale, zero_grads, make_shadows(shadows, n_shadows), elem0, advance));
   count_launch(1);
-  return check_cuda(cudaGetLastError(), "adam_kernel launch");
+  return check_cuda(cudaGetLastError(), "adagrad_kernel launch");
 }
 
 extern "C" int ddls_adagrad_step(float* params, float* grads, float* acc, int* step, size_t n, float lr, float eps,
                                  float grad_scale, int zero_grads, const DdlsShadowSpec* shadows, int n_shadows,
                                  void* stream) {
+  return ddls_adagrad_step_range(params, grads, acc, step, n, 0, 1, lr, eps, grad_scale, zero_grads, shadows, n_shadows, stream);
+}
+
+extern "C" int ddls_sgd_step_range(float* params, float* grads, int* step, size_t n, size_t elem0, int advance, float lr,
+                                   float grad_scale, int zero_grads, const DdlsShadowSpec* shadows, int n_shadows,
+                                   void* stream) {
   if (n == 0) return 0;
-  if (check_flat(params, n, "ddls_adagrad_step") || check_flat(grads, n, "ddls_adagrad_step")) return 1;
-  launch_k(adagrad_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
-      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), reinterpret_cast<float4*>(acc), step, n / 4,
-      lr, eps, grad_scale, zero_grads, make_shadows(shadows, n_shadows));
+  if (check_flat(params, n, "ddls_sgd_step") || check_flat(grads, n, "ddls_sgd_step") || (elem0 & 3)) return 1;
+  DDLS_CUDA_OK(launch_k(sgd_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream),
+      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), step, n / 4, lr, grad_scale, zero_grads,
+      make_shadows(shadows, n_shadows), elem0, advance));
   count_launch(1);
-  return check_cuda(cudaGetLastError(), "adagrad_kernel launch");
+  return check_cuda(cudaGetLastError(), "sgd_kernel launch");
 }
 
 extern "C" int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, float grad_scale,
                              int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream) {
-  if (n == 0) return 0;
-  if (check_flat(params, n, "ddls_sgd_step") || check_flat(grads, n, "ddls_sgd_step")) return 1;
-  launch_k(sgd_kernel, dim3(ew_grid(n / 4)), dim3(EW_THREADS), 0, static_cast<cudaStream_t>(stream), 
-      reinterpret_cast<float4*>(params), reinterpret_cast<float4*>(grads), step, n / 4, lr, grad_scale, zero_grads,
-      make_shadows(shadows, n_shadows));
-  count_launch(1);
-  return check_cuda(cudaGetLastError(), "sgd_kernel launch");
+  return ddls_sgd_step_range(params, grads, step, n, 0, 1, lr, grad_scale, zero_grads, shadows, n_shadows, stream);
 }
 
 namespace ddls {

@@ -22,6 +22,9 @@ N.register('ddls_adam_step', [P, P, P, P, P, Z, F, F, F, F, F, I, SP, I, P])
 N.register('ddls_adagrad_step', [P, P, P, P, Z, F, F, F, I, SP, I, P])
 N.register('ddls_sgd_step', [P, P, P, Z, F, F, I, SP, I, P])
 N.register('ddls_refresh_shadows', [P, Z, SP, I, P])
+N.register('ddls_adam_step_range', [P, P, P, P, P, Z, Z, I, F, F, F, F, F, I, SP, I, P])
+N.register('ddls_adagrad_step_range', [P, P, P, P, Z, Z, I, F, F, F, I, SP, I, P])
+N.register('ddls_sgd_step_range', [P, P, P, Z, Z, I, F, F, I, SP, I, P])
 
 
 def make_specs(shadows: List[Tuple[int, int, int, int, torch.Tensor]]):
@@ -62,3 +65,21 @@ def sgd_step(p, g, step_count, lr, grad_scale=1.0, zero_grads=False, specs=None,
 def refresh_shadows(p, specs, nspecs):
     if nspecs:
         N.call('ddls_refresh_shadows', p.data_ptr(), p.numel(), specs, nspecs, N.stream_ptr(p.device))
+
+
+def step_range(kind: str, lo: int, hi: int, advance: bool, p, g, s1, s2, step_count, lr, b1, b2, eps, grad_scale=1.0,
+               zero_grads=False, specs=None, nspecs=0):
+    """Keras update of flat elements [lo, hi) only (one gradient bucket); ``advance``: publish step+1 (the last range call
+    of a training step).  ``p`` / ``g`` / ``s1`` / ``s2`` are the FULL flat buffers."""
+    st, sp = N.stream_ptr(p.device), _step_ptr(step_count)
+    ptr = lambda t: t[lo:].data_ptr()
+    n = hi - lo
+    if kind == 'adam':
+        N.call('ddls_adam_step_range', ptr(p), ptr(g), ptr(s1), ptr(s2), sp, n, lo, int(advance), lr, b1, b2, eps, grad_scale,
+               int(zero_grads), specs, nspecs, st)
+    elif kind == 'adagrad':
+        N.call('ddls_adagrad_step_range', ptr(p), ptr(g), ptr(s1), sp, n, lo, int(advance), lr, eps, grad_scale,
+               int(zero_grads), specs, nspecs, st)
+    else:
+        N.call('ddls_sgd_step_range', ptr(p), ptr(g), sp, n, lo, int(advance), lr, grad_scale, int(zero_grads), specs,
+               nspecs, st)

@@ -105,6 +105,19 @@ class _FlatOptimizer:
     def _update(self) -> None:  # pragma: no cover - interface
         raise NotImplementedError
 
+    def can_update_range(self) -> bool:
+        return self._native is not None and self.kind in ('adam', 'adagrad', 'sgd') and not getattr(self, 'momentum', 0.0)
+
+    def update_range(self, lo: int, hi: int, advance: bool) -> None:
+        """Apply the update to flat elements [lo, hi) only (CUDA): lets a caller update each gradient bucket as soon as
+        its gradients are final instead of one pass over everything at the end of backward."""
+        f = self.flat
+        s1 = getattr(self, 'm', None) if self.kind == 'adam' else getattr(self, 'acc', None)
+        self._native.step_range(self.kind, lo, hi, advance, f.flat_params, f.flat_grads, s1, getattr(self, 'v', None),
+                                self.step_count, self.lr, getattr(self, 'beta_1', 0.0), getattr(self, 'beta_2', 0.0),
+                                getattr(self, 'epsilon', 0.0), self.grad_scale, self.zero_grads_in_step, self._specs,
+                                self._nspecs)
+
     # checkpoint -------------------------------------------------------------
     def state_dict(self) -> Dict:
         return {'kind': self.kind, 'hyper': self.hyper(), 'step': int(self.step_count.item()),

@@ -126,6 +126,18 @@ class DistributedOptimizer:
         self._fused = (self.size > 1 and not self._generic and env_int('DDLS_FUSED_OPT', 1) != 0
                        and hasattr(self.comm, 'allreduce_opt_') and getattr(self.inner, 'kind', '') in ('adam', 'adagrad', 'sgd')
                        and not getattr(self.inner, 'momentum', 0.0) and self._plan_fused())
+        # One rank, several buckets, CUDA: there is nothing to reduce, but the same machinery runs the optimizer bucket by
+        # bucket on the side stream as gradients become final ('local' mode) — the update of the big Dense bucket then
+        # overlaps the convolution backward and only the small tail bucket's update is left at the end of the step.
+        self._local = (self.size == 1 and not self._generic and self.device.type == 'cuda' and len(self.buckets) > 1
+                       and env_int('DDLS_LOCAL_BUCKETS', 1) != 0 and self.backward_passes_per_step == 1
+                       and hasattr(self.inner, 'can_update_range') and self.inner.can_update_range())
+        if self._local:
+            self._fused = True
+            self.overlap = overlap
+            self._comm_stream = torch.cuda.Stream(device=self.device)
+            for p in self.flat.params:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._on_grad))
         self._n_launched = 0
         if self._fused:
             self.inner._shard_gather = self.gather_slots
@@ -146,7 +158,10 @@ class DistributedOptimizer:
         return True
 
     def _bucket_mode(self, b) -> str:
-        """'ll' or 'dp' for bucket ``b`` (decided at launch time: bf16 shadows are registered after construction)."""
+        """'ll' or 'dp' for bucket ``b`` (decided at launch time: bf16 shadows are registered after construction);
+        'local' on a single rank."""
+        if self._local:
+            return 'local'
         shadowed = any(beg < b.hi and beg + rows * cols > b.lo for beg, rows, cols, _, _ in getattr(self.inner, '_shadows', ()))
         if b.ll_ok and not shadowed and ((b.hi - b.lo) * 4 <= self._dp_min_bytes or not self._dp_ok):
             return 'll'
@@ -157,6 +172,9 @@ class DistributedOptimizer:
 
     def _fused_bucket(self, b) -> None:
         advance = self._n_launched == len(self.buckets)      # the last bucket of the step publishes step+1
+        if self._local:
+            self.inner.update_range(b.lo, min(b.hi, self.flat.numel), advance)
+            return
         if self._bucket_mode(b) == 'll':
             n_opt = max(0, min(b.hi, self.flat.numel) - b.lo)
             self.comm.allreduce_opt_(self.flat.flat_grads[b.lo:b.hi], self.inner, self.op, wire_bf16=self._bf16 is not None,
@@ -190,7 +208,7 @@ class DistributedOptimizer:
 
     # ------------------------------------------------------------------ hooks
     def _on_grad(self, p: torch.Tensor) -> None:
-        if self.size == 1 or self._passes + 1 < self.backward_passes_per_step:
+        if (self.size == 1 and not self._local) or self._passes + 1 < self.backward_passes_per_step:
             return  # nothing to reduce / keep accumulating locally
         b = self._bucket_of.get(id(p))
         if b is None or b.launched:
@@ -232,7 +250,7 @@ class DistributedOptimizer:
     # -------------------------------------------------------------- public API
     def synchronize(self) -> None:
         """Launch any bucket whose hook did not fire (unused parameters) and wait for all."""
-        if self.size > 1:
+        if self.size > 1 or self._local:
             if self._generic:
                 self.flat.pack()
             for b in self.buckets:

@@ -64,6 +64,13 @@ class StepEngine:
         if distributed and not hasattr(base, 'synchronize'):
             from ..parallel import DistributedOptimizer
             base = DistributedOptimizer(base, **(dist_kwargs or {}))
+        elif self._wants_local_buckets(base):
+            # a lone CUDA rank: the same bucket machinery updates each gradient bucket as soon as it is final, on a side
+            # stream, instead of one optimizer pass after backward (DistributedOptimizer 'local' mode)
+            from ..parallel import DistributedOptimizer
+            wrapped = DistributedOptimizer(base)
+            if getattr(wrapped, '_local', False):
+                base = wrapped
         self.optimizer = base
         self.cuda = self.device.type == 'cuda'
         if use_cuda_graph is None:
@@ -83,6 +90,16 @@ class StepEngine:
         self.use_direct = self.cuda and env_flag('DDLS_DIRECT_STEP', True)
         # the fused optimizer kernels can clear the gradient buffer after consuming it
         self._skip_zero = self.cuda and bool(getattr(inner, 'zero_grads_in_step', False))
+
+    def _wants_local_buckets(self, base) -> bool:
+        import os
+        from .. import runtime
+        from ..optim.keras_optimizers import _FlatOptimizer
+        if not (self.device.type == 'cuda' and isinstance(base, _FlatOptimizer)) or os.environ.get('DDLS_LOCAL_BUCKETS', '1') == '0':
+            return False
+        if runtime.is_initialized():
+            return runtime.size() == 1
+        return int(os.environ.get('WORLD_SIZE', '1')) == 1 and int(os.environ.get('DDLS_SIZE', '1')) == 1
 
     # -- one eager step ------------------------------------------------------
     def _loss(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:

@@ -67,6 +67,17 @@ int ddls_adagrad_step(float* params, float* grads, float* acc, int* step, size_t
                       float grad_scale, int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream);
 int ddls_sgd_step(float* params, float* grads, int* step, size_t n, float lr, float grad_scale, int zero_grads,
                   const DdlsShadowSpec* shadows, int n_shadows, void* stream);
+/* Range forms: params / grads / slots point at flat element `elem0` of the parameter space (shadow specs use flat indices)
+ * and cover n elements; `advance` = 0 leaves the step count alone (every range call of a training step but the last).
+ * Used to update each gradient bucket as soon as it is final, on a side stream, while backward is still running. */
+int ddls_adam_step_range(float* params, float* grads, float* m, float* v, int* step, size_t n, size_t elem0, int advance,
+                         float lr, float beta1, float beta2, float eps, float grad_scale, int zero_grads,
+                         const DdlsShadowSpec* shadows, int n_shadows, void* stream);
+int ddls_adagrad_step_range(float* params, float* grads, float* acc, int* step, size_t n, size_t elem0, int advance,
+                            float lr, float eps, float grad_scale, int zero_grads, const DdlsShadowSpec* shadows,
+                            int n_shadows, void* stream);
+int ddls_sgd_step_range(float* params, float* grads, int* step, size_t n, size_t elem0, int advance, float lr,
+                        float grad_scale, int zero_grads, const DdlsShadowSpec* shadows, int n_shadows, void* stream);
 int ddls_refresh_shadows(const float* params, size_t n, const DdlsShadowSpec* shadows, int n_shadows, void* stream);
 
 /* ---- on-device preprocessing (MinMax + reshape + one-hot, ddl_mnist_aztk.py:126-144) ---------- */

@@ -184,7 +184,7 @@ def test_stacked_big_lstm_direct_step_matches_autograd_reference(seq, monkeypatc
 def test_stacked_lstm_at_its_benchmark_size_tracks_fp32_over_168_steps():
     """BASELINE.json config 4 at full size (2 x LSTM(1024), T = 168, batch 512): bf16 recurrent state and bf16 GEMM operands
     against the fp32 restatement of the Keras equations over all 168 dependent steps.  Stated drift tolerance: loss within
-    3 %, every gradient within 10 % relative L2 (measured: see gpurun_out/stacked_lstm_drift.json written by this test)."""
+    0.1 %, every gradient within 2 % relative L2 (measured on B200: 0.003 % and <= 0.5 %, profiles/stacked_lstm_drift.json)."""
     import json, os
     import distributeddeeplearningspark_b200 as ddls
     from distributeddeeplearningspark_b200.ops.fused import DirectStep
@@ -215,5 +215,5 @@ def test_stacked_lstm_at_its_benchmark_size_tracks_fp32_over_168_steps():
              'grad_rel_l2': {n: float((p.grad - g).norm() / (g.norm() + 1e-20)) for (n, p), g in zip(m.named_parameters(), gref)}}
     os.makedirs('gpurun_out', exist_ok=True)
     json.dump(drift, open('gpurun_out/stacked_lstm_drift.json', 'w'), indent=1)
-    assert drift['loss_rel'] < 3e-2, drift
-    assert max(drift['grad_rel_l2'].values()) < 0.10, drift
+    assert drift["loss_rel"] < 1e-3, drift
+    assert max(drift["grad_rel_l2"].values()) < 2e-2, drift
