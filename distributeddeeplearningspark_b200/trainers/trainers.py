@@ -247,6 +247,12 @@ class Trainer:
     def get_training_time(self) -> float:
         return self.training_time_end - self.training_time_start
 
+    def get_loop_time(self) -> float:
+        """Seconds the slowest rank spent in its training loop (first minibatch to last update, device drained) — what is
+        left of ``get_training_time()`` (driver wall clock, as in the reference) without process start, CUDA context
+        creation, heap exchange and partition staging."""
+        return max(getattr(self, 'loop_times', [0.0]) or [0.0])
+
     def get_history(self):
         return self.history
 
@@ -292,6 +298,7 @@ class Trainer:
         self.worker_results = results
         self.history = [r['history'] for r in results]
         self.phase_times = [r.get('phases', {}) for r in results]
+        self.loop_times = [float(r.get('elapsed', 0.0)) for r in results]
         model = deserialize_model(self.master_model)
         model.set_weights(results[0]['weights'])
         self.parameter_server = ParameterServerView(self._count_updates(results), model)

@@ -132,7 +132,7 @@ def main():
     trainer = make_trainer(net, cfg)
     trained = trainer.train(train)
     print('-' * 52)
-    print('Training time: ', trainer.get_training_time())
+    print('Training time: ', trainer.get_training_time(), ' (training loop on the slowest rank: ', trainer.get_loop_time(), ')')
     print('Accuracy: ', accuracy(trained, test, cfg))
     print('Number of parameter server updates: ', trainer.parameter_server.num_updates)
     for r, ph in enumerate(trainer.get_phase_times()[:1]):
