@@ -132,9 +132,10 @@ class _HeapBase:
 
     def ll_max_bytes(self, world: int) -> int:
         """Largest message the flag-in-data one-shot still wins at ``world`` ranks.  Every rank receives (world-1) packets
-        per element, the in-switch reduction one: measured crossovers (profiles/sweep_n{2,8}.json, graph-timed) are
-        above 256 KB at 2 GPUs and ~64 KB at 8, i.e. about 512 KB of inbound payload."""
-        return min(self._ll_elems * 4, env_int('DDLS_LL_INBOUND_BYTES', 512 << 10) // max(1, world - 1))
+        per element, the in-switch reduction one: measured crossovers (profiles/sweep_n{2,4,8}.json, graph-timed) are
+        above 256 KB at 2 and at 4 GPUs (NYISO LSTM step at 4 GPUs: 89.1 us with the flag-in-data kernel, 93.7 us with the
+        sharded one) and ~64-100 KB at 8, i.e. about 800 KB of inbound payload."""
+        return min(self._ll_elems * 4, env_int('DDLS_LL_INBOUND_BYTES', 800 << 10) // max(1, world - 1))
 
     def select_algo(self, nbytes: int, symmetric_out: bool, have_mc: bool) -> int:
         """Measured selection (profiles/sweep_n{2,4,8}.json): flag-in-data one-shot while its (world-1)-fold inbound
