@@ -4,6 +4,7 @@
     python bench.py --gpus 1 --steps 200 --warmup 20
     python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P \
         bench.py --gpus 8 --steps 200 --warmup 20
+    python bench.py --gpus 8 --steps 200 --warmup 20     # same, ranks started by this framework's spark.run launcher
 
 Default model/config = BASELINE.json config 2: the MNIST Keras-style CNN of
 /root/reference/ddl_mnist_aztk.py:180-196, synthetic 28x28 images, per-rank batch 128, Adam,
@@ -293,26 +294,9 @@ def _log(msg):
         print(f'[bench] {msg}', file=sys.stderr, flush=True)
 
 
-def main():
-    args = parse()
-    if args.impl == 'reference':
-        return reference_arm(args)
-    import faulthandler
-    # a hung collective must not hang the caller for ever: dump every thread's stack and exit after DDLS_BENCH_WATCHDOG_S
-    faulthandler.dump_traceback_later(int(os.environ.get('DDLS_BENCH_WATCHDOG_S', '900')), exit=True)
-
-    import torch
+def run_rank(args):
+    """One rank of the benchmark (this process is rank RANK of WORLD_SIZE): returns the result dict on rank 0."""
     import distributeddeeplearningspark_b200 as ddls
-
-    if not torch.cuda.is_available():
-        print(json.dumps({'impl': args.impl, 'unavailable': 'no CUDA device visible'}))
-        return 0
-    world = int(os.environ.get('WORLD_SIZE', '1'))
-    if world != args.gpus:
-        if world == 1 and args.gpus > 1:
-            print(json.dumps({'impl': args.impl, 'unavailable':
-                              f'--gpus {args.gpus} must be launched with torch.distributed.run (one rank per GPU)'}))
-            return 0
     if args.comm:
         os.environ['DDLS_COMM'] = args.comm
     ddls.init()
@@ -323,7 +307,8 @@ def main():
         sys.path.insert(0, os.path.join(ROOT, 'baseline'))
         import standin
         md = MODEL_DEFAULTS[args.model]
-        return standin.run(args, ddls, md, args.batch_per_rank or md['batch'], K, W)
+        standin.run(args, ddls, md, args.batch_per_rank or md['batch'], K, W)
+        return None
 
     out = measure(args, args.model, ddls, K, W)
     _log(f'{args.model}: {out["value"]:.0f} {out["unit"]}, {out["ms_per_step"] * 1e3:.1f} us/step')
@@ -340,9 +325,46 @@ def main():
         out['secondary']['config'] = sec['config']
         if ddls.size() > 1:
             out['allreduce_us'] = allreduce_latency(ddls, with_nccl=args.nccl_compare)
-    if rank == 0:
-        print(json.dumps(out))
     ddls.shutdown()
+    return out if rank == 0 else None
+
+
+def _spark_rank(argv):
+    """Entry of a rank started by ``ddls.spark.run`` (BASELINE.json config 2: "via Spark launcher")."""
+    sys.argv = ['bench.py'] + list(argv)
+    return run_rank(parse())
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        return reference_arm(args)
+    import faulthandler
+    # a hung collective must not hang the caller for ever: dump every thread's stack and exit after DDLS_BENCH_WATCHDOG_S
+    faulthandler.dump_traceback_later(int(os.environ.get('DDLS_BENCH_WATCHDOG_S', '900')), exit=True)
+
+    import torch
+    if not torch.cuda.is_available():
+        print(json.dumps({'impl': args.impl, 'unavailable': 'no CUDA device visible'}))
+        return 0
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    if world == 1 and args.gpus > 1:
+        # not started by torch.distributed.run: start the ranks through this framework's own Spark-style launcher
+        # (barrier stage, one rank per GPU) — the path BASELINE.json config 2 names
+        if args.impl != 'ours':
+            print(json.dumps({'impl': args.impl, 'unavailable':
+                              f'--gpus {args.gpus} must be launched with torch.distributed.run (one rank per GPU)'}))
+            return 0
+        import distributeddeeplearningspark_b200 as ddls
+        results = ddls.spark.run(_spark_rank, args=(sys.argv[1:],), num_proc=args.gpus)
+        out = results[0]
+        out['config']['launcher'] = 'spark.run (local barrier backend)'
+        print(json.dumps(out))
+        return 0
+    out = run_rank(args)
+    if out is not None:
+        out['config']['launcher'] = 'torch.distributed.run' if world > 1 else 'single process'
+        print(json.dumps(out))
     return 0
 
 
