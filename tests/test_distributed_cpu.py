@@ -119,3 +119,53 @@ def test_collective_functions_gloo():
     for avg, tot, g, b, objs in out:
         assert avg == [1.5] * 5 and tot == [3.0] * 5
         assert g == [[0, 0], [1, 10]] and b == [8.0] and objs == [{'r': 0}, {'r': 1}]
+
+
+def test_allreduce_algorithm_selection_follows_the_measured_crossovers(monkeypatch):
+    """select_algo / ll_max_bytes (host logic, no GPU needed): flag-in-data while (ranks-1) x bytes <= 800 KB, then NVLS;
+    two-shot at two ranks from 2 MB; fenced one-shot / two-shot without multicast (profiles/sweep_n{2,4,8}.json)."""
+    from distributeddeeplearningspark_b200.parallel import peer
+    for k in ('DDLS_ALLREDUCE_ALGO', 'DDLS_LL_INBOUND_BYTES', 'DDLS_LL_MAX_BYTES', 'DDLS_ONESHOT_MAX_BYTES'):
+        monkeypatch.delenv(k, raising=False)
+
+    class Heap(peer._HeapBase):
+        def __init__(self, size):
+            self.size = size
+            self._init_heap(1 << 30)
+            self._init_ll_stage(size)
+
+    KB, MB = 1 << 10, 1 << 20
+    h2, h4, h8 = Heap(2), Heap(4), Heap(8)
+    assert h2.ll_max_bytes(2) == 512 * KB and h4.ll_max_bytes(4) == 800 * KB // 3 and h8.ll_max_bytes(8) == 800 * KB // 7
+    lstm = 66692 * 4                                   # the NYISO LSTM gradient bucket
+    assert h2.select_algo(lstm, True, True) == peer.AR_ONESHOT_LL
+    assert h4.select_algo(lstm, True, True) == peer.AR_ONESHOT_LL
+    assert h8.select_algo(lstm, True, True) == peer.AR_NVLS
+    assert h8.select_algo(64 * KB, True, True) == peer.AR_ONESHOT_LL
+    assert h8.select_algo(4 * MB, True, True) == peer.AR_NVLS and h4.select_algo(64 * MB, True, True) == peer.AR_NVLS
+    assert h2.select_algo(1 * MB, True, True) == peer.AR_NVLS and h2.select_algo(4 * MB, True, True) == peer.AR_TWOSHOT
+    assert h8.select_algo(1 * MB, True, False) == peer.AR_ONESHOT and h8.select_algo(4 * MB, True, False) == peer.AR_TWOSHOT
+    assert h8.select_algo(4 * MB, False, True) == peer.AR_ONESHOT          # output not symmetric: push into staging only
+    monkeypatch.setenv('DDLS_ALLREDUCE_ALGO', 'twoshot')
+    assert h8.select_algo(4 * KB, True, True) == peer.AR_TWOSHOT
+
+
+def test_shard_bounds_match_the_kernels_slice_partition():
+    """Rank r owns vectors [r*ceil(nvec/N), ...) of a bucket (csrc/comm.cu dp_step_kernel): the host-side bounds used to
+    gather the sharded optimizer slots tile the bucket exactly, whatever the bucket size."""
+    from distributeddeeplearningspark_b200.parallel.distributed_optimizer import DistributedOptimizer, _Bucket
+
+    class Fake:
+        shard_bounds = DistributedOptimizer.shard_bounds
+
+    for size in (2, 3, 8):
+        for lo, hi, numel in ((0, 4, 4), (128, 128 + 50008, 128 + 50000), (0, 1037252, 1037252), (64, 64 + 36, 64 + 36)):
+            f = Fake(); f.size = size
+            f.flat = type('F', (), {'numel': numel})()
+            f.comm = type('C', (), {'rank': 0})()
+            b = _Bucket(lo, hi, [])
+            spans = [f.shard_bounds(b, r) for r in range(size)]
+            assert spans[0][0] == lo
+            for (a0, a1), (b0, b1) in zip(spans[:-1], spans[1:]):
+                assert a1 == min(b0, numel) or (a1 == numel and b0 >= numel)   # contiguous up to the optimizer's range
+            assert max(s[1] for s in spans) == min(hi, numel) and all(s[0] % 4 == 0 for s in spans)
