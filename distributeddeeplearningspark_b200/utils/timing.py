@@ -1,4 +1,4 @@
-"""Device timing, phase timers, Chrome-trace timeline and clock sampling.
+"""Phase timers, Chrome-trace timeline, clock sampling and L2 flushing.
 
 ``trainer.get_training_time()`` is the reference's only timer (driver wall
 clock, /root/reference/ddl_mnist_aztk.py:222).  Here every throughput number is
@@ -16,37 +16,6 @@ from contextlib import contextmanager
 from typing import Dict, List, Optional
 
 import torch
-
-
-class CudaTimer:
-    """CUDA-event stopwatch on the current stream (falls back to perf_counter on CPU)."""
-
-    def __init__(self, device: Optional[torch.device] = None):
-        self.cuda = torch.cuda.is_available() and (device is None or torch.device(device).type == 'cuda')
-        if self.cuda:
-            self._a = torch.cuda.Event(enable_timing=True)
-            self._b = torch.cuda.Event(enable_timing=True)
-        self._t0 = 0.0
-        self._ms = 0.0
-
-    def start(self):
-        if self.cuda:
-            self._a.record()
-        else:
-            self._t0 = time.perf_counter()
-
-    def stop(self) -> float:
-        if self.cuda:
-            self._b.record()
-            self._b.synchronize()
-            self._ms = self._a.elapsed_time(self._b)
-        else:
-            self._ms = (time.perf_counter() - self._t0) * 1e3
-        return self._ms
-
-    @property
-    def ms(self) -> float:
-        return self._ms
 
 
 class PhaseTimers:
