@@ -118,7 +118,7 @@ def measure(args, model_name, ddls, K, W, with_e2e=True, with_clocks=True):
     # ---- data: a device pool larger than L2 for the kernel-only number; pinned host for e2e ------------
     is_mnist = model_name == 'mnist_cnn'
     bytes_per_batch = B * (784 * 4 + 10 * 4) if is_mnist else B * (md['seq'] + 1) * 4
-    pool_n = max(8, min(4096, (160 << 20) // bytes_per_batch + 1))
+    pool_n = max(8, min(65536, (160 << 20) // bytes_per_batch + 1))      # > 126 MB of L2 for every model
     host = make_batches(model_name, B, pool_n, seed=rank, device=dev)
     if is_mnist:
         px = host['pixels'].to(dev); lab = host['labels'].to(dev)
