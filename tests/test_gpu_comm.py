@@ -97,6 +97,28 @@ def test_emulated_allreduce_bf16_wire_and_back_to_back_calls():
         assert float(bufs2[2][0]) == sum(r + it for r in range(world))
 
 
+def test_emulated_flag_protocol_stress_100k_back_to_back_calls():
+    """Race / reuse stress of the flag protocols: 10^5 back-to-back small allreduces with no host
+    synchronisation in between, alternating two buffers and the three small-message algorithms, so every flag word,
+    both staging parities and both packet halves are reused ~10^4 times; results are checked every 10,000 calls."""
+    dev = torch.device('cuda', 0)
+    world, n = 4, 1024
+    g = EmulatedPeerGroup(world, dev)
+    sets = [g.alloc(n) for _ in range(2)]
+    src = [torch.full((n,), float(r + 1), device=dev) for r in range(world)]
+    want = float(sum(range(1, world + 1)))
+    algos = (AR_ONESHOT_LL, AR_ONESHOT, AR_TWOSHOT)
+    for it in range(100000):
+        off, bufs = sets[it & 1]
+        for b, s_ in zip(bufs, src):
+            b.copy_(s_, non_blocking=True)
+        g.allreduce(off, n, algos[it % 3], scale=1.0)
+        if it % 10000 == 9999:
+            torch.cuda.synchronize()
+            for b in bufs:
+                assert float(b.min()) == want == float(b.max()), (it, float(b.min()), float(b.max()))
+
+
 @pytest.mark.parametrize('world', [2, 8])
 def test_emulated_broadcast_every_root_and_allgather(world):
     dev = torch.device('cuda', 0)
